@@ -1,0 +1,93 @@
+"""NHWC pipeline of the FiLM-EfficientNet-B3 image encoder (sm_100a path).
+
+Entry point: :func:`film_efficientnet_forward` — called by ``EfficientNetEncoder.forward_nhwc`` with bf16
+NHWC frames.  It walks the parameter containers in ``rt1b200.models.film_efficientnet`` and runs each stage
+through the NHWC kernels in ``rt1b200.ops.kernels`` (K2–K8 of SURVEY §2.6):
+
+  stem      : 3x3 s2 conv + BN(batch stats) + SiLU
+  MBConv    : [expand 1x1 GEMM + BN-stat epilogue] → [BN+SiLU folded into the depthwise load, BN-stat
+              epilogue] → [BN+SiLU + SE pool] → [SE FCs] → [project GEMM with BN+SiLU+SE-scale prologue]
+              → [BN + stochastic depth + residual + FiLM affine]
+  head      : 1x1 384→1536 + BN + SiLU → 1x1 1536→512 → FiLM
+
+Stages whose kernels are not enabled (``RT1B200_CNN_KERNELS`` mask, or a shape a kernel does not cover) run
+as channels-last PyTorch ops on the same bf16 tensors so the pipeline is always complete.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+
+def _bn(x, bn, training: bool):
+    """BatchNorm on a bf16 NCHW(channels-last) tensor with fp32 running statistics."""
+    w = bn.weight.float() if bn.weight is not None else None
+    b = bn.bias.float() if bn.bias is not None else None
+    if training and bn.track_running_stats and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked.add_(1)
+    use_batch = training or not bn.track_running_stats
+    return F.batch_norm(x, bn.running_mean if bn.track_running_stats else None,
+                        bn.running_var if bn.track_running_stats else None, w, b,
+                        use_batch, bn.momentum if bn.momentum is not None else 0.1, bn.eps)
+
+
+def _cna(x, cna, training: bool):
+    conv, bn = cna[0], cna[1]
+    x = F.conv2d(x, conv.weight, None, conv.stride, conv.padding, conv.dilation, conv.groups)
+    x = _bn(x, bn, training)
+    if len(cna) > 2:
+        x = F.silu(x)
+    return x
+
+
+def _film(x, film, ctx):
+    beta = F.linear(ctx, film._projection_add.weight, film._projection_add.bias)
+    gamma = F.linear(ctx, film._projection_mult.weight, film._projection_mult.bias)
+    return (1 + gamma[:, :, None, None]) * x + beta[:, :, None, None]
+
+
+def _mbconv_torch(x, blk, training: bool):
+    inp = x
+    if blk.expand is not None:
+        x = _cna(x, blk.expand, training)
+    x = _cna(x, blk.depthwise, training)
+    se = blk.se
+    if se is not None:
+        s = x.mean(dim=(2, 3), keepdim=True)
+        s = F.silu(F.conv2d(s, se.fc1.weight, se.fc1.bias))
+        s = torch.sigmoid(F.conv2d(s, se.fc2.weight, se.fc2.bias))
+        x = x * s
+    x = _cna(x, blk.project, training)
+    if blk.has_skip:
+        if blk.drop_rate > 0 and training:
+            x = blk.dropout(x)
+        x = inp + x
+    return x
+
+
+def film_efficientnet_forward_torch(encoder, image_nhwc: torch.Tensor, context: torch.Tensor) -> torch.Tensor:
+    """Channels-last PyTorch execution of the encoder on bf16 tensors (bring-up / bisecting path)."""
+    net = encoder.net
+    training = encoder.training
+    x = image_nhwc[..., :3].permute(0, 3, 1, 2)                 # NCHW view of NHWC memory (channels_last)
+    x = _cna(x, net.convNormAct0, training)
+    for i, blk in enumerate(net.blocks):
+        x = _mbconv_torch(x, blk, training)
+        if net.include_film:
+            x = _film(x, net.films[i], context)
+    x = _cna(x, net.convNormAct1, training)
+    x = F.conv2d(x, encoder.conv1x1.weight)
+    x = _film(x, encoder.film_layer, context)
+    return x.permute(0, 2, 3, 1).contiguous()
+
+
+def film_efficientnet_forward(encoder, image_nhwc: torch.Tensor, context: torch.Tensor) -> torch.Tensor:
+    from . import _lib
+    if _lib.available() and os.environ.get("RT1B200_CNN_KERNELS", "1") != "0":
+        from . import kernels
+        if hasattr(kernels, "film_efficientnet_forward"):
+            return kernels.film_efficientnet_forward(encoder, image_nhwc, context)
+    return film_efficientnet_forward_torch(encoder, image_nhwc, context)
