@@ -1,0 +1,313 @@
+"""Training loop, RT-1 training module, checkpointing and logging.
+
+What it covers of the reference (``distribute_train.py``):
+  * ``RT1Module``       ≙ ``RT1_Lightning`` (``:19-180``): builds the Language-Table RT-1, ``training_step`` /
+                          ``validation_step`` / ``test_step`` (``set_actions`` → forward → mean of the ``[b,t]``
+                          actor loss), ``debug()``.
+  * ``Trainer``         ≙ Lightning ``Trainer(strategy=DDPStrategy(find_unused_parameters=True))`` +
+                          ``ModelCheckpoint`` + ``LearningRateMonitor`` + CSV/TensorBoard loggers (``:192-247``):
+                          fit (train epoch → validation → MultiStepLR step → checkpoint) and test.
+  * checkpoints          Lightning layout (``state_dict`` with ``model.`` prefix, ``optimizer_states``,
+                          ``lr_schedulers``, ``epoch``, ``global_step``), file name
+                          ``{epoch}-{eval_loss:.6f}-{train_loss_epoch:.6f}.ckpt`` + ``last.ckpt`` (``:214-220``),
+                          and — unlike the reference, where resume is a commented hint (``:240``) — ``resume``.
+
+The step itself is the B200 design: bf16 model, flat fp32 master/optimizer state, one fused reduce+AdamW per
+bucket overlapped with backward (:class:`rt1b200.parallel.engine.DataParallelEngine`); the loss scalar for
+logging is averaged over ranks without leaving the device until a log interval is reached.
+"""
+from __future__ import annotations
+
+import csv
+import os
+import time
+from argparse import Namespace
+from dataclasses import asdict
+from bisect import bisect_right
+from typing import Dict, Iterable, List, Optional
+
+import torch
+import torch.nn as nn
+
+from ..models.factory import RT1Config, build_rt1
+from ..models.tokenizers import batched_space_sampler, np_to_tensor
+from ..parallel.engine import DataParallelEngine
+
+
+class RT1Module(nn.Module):
+    """The RT-1 policy plus its train/val/test step bodies. ``args`` needs ``height, width, seq_len``."""
+
+    def __init__(self, args, cfg: Optional[RT1Config] = None):
+        super().__init__()
+        self.args = args
+        self.HEIGHT, self.WIDTH, self.TIME_SEQUENCE_LENGTH = args.height, args.width, args.seq_len
+        cfg = cfg or RT1Config.language_table(height=args.height, width=args.width, seq_len=args.seq_len)
+        self.cfg = cfg
+        self.model = build_rt1(cfg)
+        self.state_space = self.model._input_tensor_space
+        self.action_space = self.model._output_tensor_space
+
+    def loss_fn(self, x: torch.Tensor) -> torch.Tensor:
+        return torch.mean(x.float())
+
+    def _step(self, batch) -> torch.Tensor:
+        obs, labels = batch["train_observation"], batch["action_label"]
+        self.model.set_actions(labels)
+        # the reference samples a throw-away random network_state on the CPU and ships it to the GPU every
+        # step (distribute_train.py:64-65); training never reads it, so none is built here
+        self.model(obs, None)
+        return self.loss_fn(self.model.get_actor_loss())
+
+    def training_step(self, batch, batch_idx: int = 0) -> torch.Tensor:
+        return self._step(batch)
+
+    @torch.no_grad()
+    def validation_step(self, batch, batch_idx: int = 0) -> torch.Tensor:
+        return self._step(batch)
+
+    @torch.no_grad()
+    def test_step(self, batch, batch_idx: int = 0) -> torch.Tensor:
+        return self._step(batch)
+
+    def debug(self, training: bool = True, device=None):
+        """Constant-input forward, as the reference's ``RT1_Lightning.debug`` (``:126-180``)."""
+        device = device or next(self.parameters()).device
+        T, H, W = self.TIME_SEQUENCE_LENGTH, self.HEIGHT, self.WIDTH
+        if training:
+            B = 2
+            obs = {"image": torch.full((B, T, 3, H, W), 0.5, device=device),
+                   "natural_language_embedding": torch.full((B, T, 512), 1.0, device=device)}
+            labels = {"terminate_episode": torch.ones(B, T, dtype=torch.long, device=device),
+                      "action": torch.zeros(B, T, 2, device=device)}
+            self.model.set_actions(labels)
+            state = np_to_tensor(batched_space_sampler(self.model._state_space, B), device)
+            pred, _ = self.model(obs, state)
+            loss = self.model.get_actor_loss()
+            return pred, loss, self.loss_fn(loss)
+        obs = {"image": torch.full((1, 3, H, W), 0.5, device=device),
+               "natural_language_embedding": torch.full((1, 512), 1.0, device=device)}
+        state = self.model.initial_state(1, device=device)
+        with torch.no_grad():
+            pred, _ = self.model(obs, state)
+        return pred
+
+
+class MultiStepLR:
+    """``lr * gamma ** (#milestones <= epoch)``, stepped once per epoch (reference ``:101``)."""
+
+    def __init__(self, base_lr: float, milestones: Iterable[int], gamma: float = 0.1, last_epoch: int = 0):
+        self.base_lr, self.milestones, self.gamma, self.last_epoch = base_lr, sorted(milestones), gamma, last_epoch
+
+    def get_lr(self) -> float:
+        return self.base_lr * self.gamma ** bisect_right(self.milestones, self.last_epoch)
+
+    def step(self):
+        self.last_epoch += 1
+
+    def state_dict(self):
+        return {"base_lrs": [self.base_lr], "milestones": {m: 1 for m in self.milestones}, "gamma": self.gamma,
+                "last_epoch": self.last_epoch, "_last_lr": [self.get_lr()]}
+
+    def load_state_dict(self, sd):
+        self.last_epoch = sd.get("last_epoch", self.last_epoch)
+
+
+class CSVLogger:
+    def __init__(self, save_dir: str, name: str):
+        self.dir = os.path.join(save_dir, name)
+        os.makedirs(self.dir, exist_ok=True)
+        self.path = os.path.join(self.dir, "metrics.csv")
+        self._keys: List[str] = []
+        self._rows: List[Dict] = []
+
+    def log(self, metrics: Dict[str, float], step: int):
+        row = {"step": step, **metrics}
+        self._rows.append(row)
+        new = [k for k in row if k not in self._keys]
+        self._keys.extend(new)
+        with open(self.path, "w", newline="") as f:
+            w = csv.DictWriter(f, fieldnames=self._keys)
+            w.writeheader()
+            w.writerows(self._rows)
+
+
+class TensorBoardLogger:
+    def __init__(self, save_dir: str, name: str):
+        self.writer = None
+        try:
+            from torch.utils.tensorboard import SummaryWriter
+            self.writer = SummaryWriter(os.path.join(save_dir, name))
+        except Exception:   # tensorboard is optional
+            pass
+
+    def log(self, metrics: Dict[str, float], step: int):
+        if self.writer is not None:
+            for k, v in metrics.items():
+                self.writer.add_scalar(k, v, step)
+            self.writer.flush()
+
+
+class Trainer:
+    def __init__(self, module: RT1Module, args: Namespace, device=None, backend: str = "auto",
+                 param_dtype: Optional[torch.dtype] = None, loggers=None, verbose: bool = True):
+        self.module, self.args = module, args
+        self.device = torch.device(device) if device is not None else torch.device("cpu")
+        module.to(self.device)
+        if param_dtype is None:
+            param_dtype = torch.bfloat16 if self.device.type == "cuda" else torch.float32
+        self.engine = DataParallelEngine(module.model, lr=args.lr, param_dtype=param_dtype, backend=backend)
+        self.sched = MultiStepLR(args.lr, getattr(args, "milestones", []), 0.1)
+        self.rank, self.world = self.engine.rank, self.engine.world
+        self.epoch = 0
+        self.global_step = 0
+        self.verbose = verbose and self.rank == 0
+        self.loggers = loggers if loggers is not None else (self._default_loggers() if self.rank == 0 else [])
+        self.ckpt_dir = os.path.join(args.ckpt_dir, args.exp_name)
+        self.log_every = max(1, getattr(args, "log_every_n_steps", 50))
+        self.last_metrics: Dict[str, float] = {}
+
+    def _default_loggers(self):
+        a = self.args
+        return [CSVLogger(os.path.join(a.log_dir, "csv"), a.exp_name),
+                TensorBoardLogger(os.path.join(a.log_dir, "tb"), a.exp_name)]
+
+    def _log(self, metrics: Dict[str, float], step: int):
+        self.last_metrics.update(metrics)
+        for lg in self.loggers:
+            lg.log(metrics, step)
+
+    def _to_device(self, batch):
+        from ..data.dataset import to_device
+        return to_device(batch, self.device)
+
+    # ------------------------------------------------------------------------------------------ steps
+    def train_step(self, batch) -> torch.Tensor:
+        """One optimisation step; returns the (device-resident, rank-local) loss."""
+        batch = self._to_device(batch)
+        self.module.train()
+        lr = self.sched.get_lr()
+        loss = self.module.training_step(batch, self.global_step)
+        self.engine.begin_step(lr)
+        loss.backward()
+        self.engine.step(lr)
+        self.global_step += 1
+        return loss.detach()
+
+    def _run_eval(self, loader, step_fn) -> float:
+        self.module.eval()
+        total = torch.zeros((), device=self.device)
+        n = 0
+        for i, batch in enumerate(loader):
+            total += step_fn(self._to_device(batch), i).float()
+            n += 1
+        mean = total / max(n, 1)
+        return float(self.engine.all_reduce_mean(mean.reshape(1)).item())
+
+    def fit(self, train_loader, eval_loader=None, max_epochs: Optional[int] = None,
+            max_steps: Optional[int] = None, resume: Optional[str] = None):
+        if resume:
+            self.load_checkpoint(resume)
+        max_epochs = max_epochs if max_epochs is not None else self.args.max_epochs
+        every = max(1, getattr(self.args, "ckpt_every_n_epochs", 1))
+        while self.epoch < max_epochs:
+            if hasattr(train_loader, "sampler") and hasattr(train_loader.sampler, "set_epoch"):
+                train_loader.sampler.set_epoch(self.epoch)
+            if hasattr(train_loader, "batch_sampler") and hasattr(train_loader.batch_sampler, "set_epoch"):
+                train_loader.batch_sampler.set_epoch(self.epoch)
+            t0 = time.time()
+            acc = torch.zeros((), device=self.device)
+            window = torch.zeros((), device=self.device)
+            n = 0
+            for batch in train_loader:
+                loss = self.train_step(batch).float()
+                acc += loss
+                window += loss
+                n += 1
+                if self.global_step % self.log_every == 0:
+                    m = float(self.engine.all_reduce_mean((window / self.log_every).reshape(1)).item())
+                    window.zero_()
+                    self._log({"train_loss_step": m, "lr": self.sched.get_lr()}, self.global_step)
+                    if self.verbose:
+                        print(f"[epoch {self.epoch} step {self.global_step}] train_loss={m:.6f} "
+                              f"lr={self.sched.get_lr():.2e}", flush=True)
+                if max_steps is not None and self.global_step >= max_steps:
+                    break
+            train_loss_epoch = float(self.engine.all_reduce_mean((acc / max(n, 1)).reshape(1)).item())
+            metrics = {"train_loss_epoch": train_loss_epoch, "epoch": self.epoch, "lr-Adam": self.sched.get_lr(),
+                       "epoch_time_s": time.time() - t0}
+            if eval_loader is not None:
+                metrics["eval_loss"] = self._run_eval(eval_loader, self.module.validation_step)
+            self._log(metrics, self.global_step)
+            if self.verbose:
+                print(f"[epoch {self.epoch}] " + " ".join(f"{k}={v:.6g}" for k, v in metrics.items()), flush=True)
+            self.sched.step()
+            self.epoch += 1
+            if self.epoch % every == 0:
+                self.save_checkpoint(metrics)
+            if max_steps is not None and self.global_step >= max_steps:
+                break
+        return self.last_metrics
+
+    def test(self, test_loader) -> float:
+        loss = self._run_eval(test_loader, self.module.test_step)
+        self._log({"test_loss": loss}, self.global_step)
+        if self.verbose:
+            print(f"test_loss={loss:.6f}", flush=True)
+        return loss
+
+    # ------------------------------------------------------------------------------------ checkpoints
+    def checkpoint_dict(self) -> dict:
+        return {
+            "epoch": self.epoch, "global_step": self.global_step,
+            "pytorch-lightning_version": "2.3.3", "rt1b200_version": "0.1.0",
+            "state_dict": self.engine.model_state_dict(prefix="model."),
+            "optimizer_states": [self.engine.optimizer_state_dict()],
+            "lr_schedulers": [self.sched.state_dict()],
+            "loops": {}, "callbacks": {},
+            "hyper_parameters": {**{k: v for k, v in vars(self.args).items() if isinstance(v, (int, float, str, list))},
+                                 "rt1_config": asdict(self.module.cfg)},
+        }
+
+    def save_checkpoint(self, metrics: Optional[Dict[str, float]] = None) -> Optional[str]:
+        if self.rank != 0:
+            return None
+        os.makedirs(self.ckpt_dir, exist_ok=True)
+        metrics = metrics or self.last_metrics
+        name = "epoch={}-eval_loss={:.6f}-train_loss_epoch={:.6f}.ckpt".format(
+            self.epoch - 1 if self.epoch > 0 else 0, metrics.get("eval_loss", float("nan")),
+            metrics.get("train_loss_epoch", float("nan")))
+        ck = self.checkpoint_dict()
+        path = os.path.join(self.ckpt_dir, name)
+        torch.save(ck, path)
+        torch.save(ck, os.path.join(self.ckpt_dir, "last.ckpt"))
+        return path
+
+    def load_checkpoint(self, path: str, weights_only: bool = False):
+        ck = torch.load(path, map_location="cpu", weights_only=False)
+        self.engine.load_model_state_dict(ck["state_dict"], prefix="model.")
+        if not weights_only:
+            if ck.get("optimizer_states"):
+                self.engine.load_optimizer_state_dict(ck["optimizer_states"][0])
+            if ck.get("lr_schedulers"):
+                self.sched.load_state_dict(ck["lr_schedulers"][0])
+            self.epoch = ck.get("epoch", 0)
+            self.global_step = ck.get("global_step", 0)
+        return ck
+
+
+def load_policy_from_checkpoint(path: str, args=None, device="cpu", dtype: Optional[torch.dtype] = None) -> RT1Module:
+    """``RT1_Lightning.load_from_checkpoint(path, args=args)`` equivalent (reference ``main_rt1.py:75``)."""
+    ck = torch.load(path, map_location="cpu", weights_only=False)
+    hp = ck.get("hyper_parameters", {})
+    if args is None:
+        args = Namespace(height=hp.get("height", 256), width=hp.get("width", 456), seq_len=hp.get("seq_len", 6))
+    cfg = RT1Config(**hp["rt1_config"]) if "rt1_config" in hp else None   # absent in reference-written files
+    module = RT1Module(args, cfg)
+    sd = {k[len("model."):]: v for k, v in ck["state_dict"].items() if k.startswith("model.")}
+    module.model.load_state_dict(sd, strict=True)
+    module.to(device)
+    if dtype is not None:
+        from ..parallel.engine import keep_bn_stats_fp32
+        module.to(dtype)
+        keep_bn_stats_fp32(module)
+    return module.eval()
