@@ -1,0 +1,358 @@
+// tcgen05 / TMEM GEMM fed by TMA: D[M,N] = alpha * A[M,K] · B[N,K]^T (+ bias, dropout, residual).
+//
+// Replaces the cuBLAS/cuDNN calls behind every nn.Linear of the decoder (K10, K11, K13) and every 1x1
+// convolution of the image tokenizer (K3, K6, K8) — forward, data-gradient and weight-gradient alike, which is
+// why both operands may be K-major *or* MN-major (a transposed view costs nothing: the transposition happens
+// in the TMA box shape and the UMMA descriptor, never in memory).
+//
+// Structure (one 128 x BLOCK_N output tile per CTA, 128 threads, non-persistent — several CTAs are resident
+// per SM and overlap each other's load / MMA / epilogue phases, which suits the short-K, memory-bound shapes
+// of this model):
+//   warp 0 / lane 0 : TMA producer   — cp.async.bulk.tensor 2-D boxes (128B swizzle) into a ring of stages,
+//                                       completion counted on "full" mbarriers
+//   warp 1 / lane 0 : MMA issuer     — 4 x tcgen05.mma (K = 16) per 64-wide k-block, accumulator in TMEM,
+//                                       tcgen05.commit releases the stage ("empty") and finally signals the
+//                                       epilogue ("tmem_full")
+//   warps 0-3       : epilogue       — tcgen05.ld 32x32b (thread ↔ accumulator row), fused bias / dropout /
+//                                       residual / scale, bf16 or fp32 stores, or fp32 atomics for split-K
+// Partial tiles need no special code on the load side: TMA zero-fills out-of-bounds box elements.
+#include "sm100.cuh"
+
+using namespace sm100;
+
+struct GemmParams {
+  int M, N, K;
+  int a_mn, b_mn;        // 1 = operand stored MN-major (i.e. as [K, M] / [K, N] row-major)
+  int block_n;           // multiple of 16, <= 256
+  int stages;
+  int kb_per_split;      // 64-wide k-blocks handled by one CTA (grid.z splits)
+  void* out;
+  long ldo;
+  int out_fp32;
+  int atomic_out;        // fp32 atomicAdd into `out` (split-K / accumulate)
+  const bf16* bias;      // [N] or null
+  const bf16* residual;  // [M, ldr] or null
+  long ldr;
+  float alpha;
+  float dropout_p;
+  uint32_t seed;
+  // optional per-column statistics of the (post-bias) fp32 output: sum and sum of squares, atomically added
+  float* col_sum;
+  float* col_sumsq;
+};
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;
+constexpr int A_TILE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
+
+__host__ __device__ inline int b_tile_bytes(int block_n, int b_mn) {
+  return b_mn ? ((block_n + 63) / 64) * (BLOCK_K * 128) : block_n * 128;
+}
+
+__global__ void __launch_bounds__(128) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
+                                                           const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // dynamic smem base is only guaranteed 16B-aligned by the ABI: align up to 1024 (swizzle-128B atom)
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BLOCK_M, n0 = blockIdx.y * p.block_n;
+  const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int kb_end = min(total_kb, kb_begin + p.kb_per_split);
+  const int num_kb = kb_end - kb_begin;
+  const int b_bytes = b_tile_bytes(p.block_n, p.b_mn);
+  const int stage_bytes = A_TILE_BYTES + b_bytes;
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * stage_bytes);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + p.stages), tmem_full = smem_u32(bars + 2 * p.stages);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 1);
+  const uint32_t smem_base = smem_u32(smem);
+
+  uint32_t tmem_cols = 32;
+  while ((int)tmem_cols < p.block_n) tmem_cols <<= 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (num_kb > 0) {
+    if (warp == 0 && lane == 0) {
+      // ------------------------------------------------------------------ TMA producer
+      for (int i = 0; i < num_kb; ++i) {
+        const int s = i % p.stages;
+        const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
+        mbar_wait(empty0 + 8 * s, ph ^ 1u);
+        const uint32_t a_dst = smem_base + s * stage_bytes, b_dst = a_dst + A_TILE_BYTES;
+        const uint32_t bar = full0 + 8 * s;
+        mbar_expect_tx(bar, (uint32_t)stage_bytes);
+        const int kg = (kb_begin + i) * BLOCK_K;
+        if (!p.a_mn) {
+          tma_load_2d(a_dst, &tma_a, bar, kg, m0);
+        } else {
+          tma_load_2d(a_dst, &tma_a, bar, m0, kg);
+          tma_load_2d(a_dst + BLOCK_K * 128, &tma_a, bar, m0 + 64, kg);
+        }
+        if (!p.b_mn) {
+          tma_load_2d(b_dst, &tma_b, bar, kg, n0);
+        } else {
+          for (int j = 0; j * 64 < p.block_n; ++j) tma_load_2d(b_dst + j * (BLOCK_K * 128), &tma_b, bar, n0 + 64 * j, kg);
+        }
+      }
+    } else if (warp == 1 && lane == 0) {
+      // ------------------------------------------------------------------ MMA issuer
+      const uint32_t idesc = umma_idesc_bf16(BLOCK_M, p.block_n, p.a_mn, p.b_mn);
+      for (int i = 0; i < num_kb; ++i) {
+        const int s = i % p.stages;
+        const uint32_t ph = (uint32_t)(i / p.stages) & 1u;
+        mbar_wait(full0 + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t a_src = smem_base + s * stage_bytes, b_src = a_src + A_TILE_BYTES;
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / 16; ++k) {
+          const uint64_t da = p.a_mn ? umma_smem_desc(a_src + k * 2048, BLOCK_K * 128, 1024)
+                                     : umma_smem_desc(a_src + k * 32, 16, 1024);
+          const uint64_t db = p.b_mn ? umma_smem_desc(b_src + k * 2048, BLOCK_K * 128, 1024)
+                                     : umma_smem_desc(b_src + k * 32, 16, 1024);
+          umma_bf16(tmem_base, da, db, idesc, (i | k) != 0);
+        }
+        umma_commit(empty0 + 8 * s);               // stage reusable once these MMAs have read it
+        if (i == num_kb - 1) umma_commit(tmem_full);  // accumulator complete
+      }
+    }
+    __syncwarp();
+    // -------------------------------------------------------------------- epilogue (all 4 warps)
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+  }
+
+  const int row = m0 + warp * 32 + lane;
+  const bool row_ok = row < p.M;
+  const uint32_t thresh = rt1_drop_threshold(p.dropout_p);
+  const float keep_scale = p.dropout_p > 0.f ? 1.f / (1.f - p.dropout_p) : 1.f;
+  float* stat_sm = reinterpret_cast<float*>(smem);  // operand stages are dead once tmem_full fired
+
+  for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+    const int width = min(32, p.block_n - c0);
+    uint32_t acc[32];
+    if (num_kb > 0) {
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
+      if (width == 32) tmem_ld_32x32(taddr, acc);
+      else tmem_ld_32x16(taddr, acc);
+      tmem_ld_wait();
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc[j] = 0u;
+    }
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int col = n0 + c0 + j;
+      float x = __uint_as_float(acc[j]) * p.alpha;
+      if (p.bias != nullptr && col < p.N && j < width) x += __bfloat162float(p.bias[col]);
+      v[j] = x;
+    }
+    if (p.col_sum != nullptr) {
+      // per-column sum / sum-of-squares over the 128 rows of this tile: transpose through shared memory so
+      // each lane reduces one column, then one atomic per column per CTA
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) stat_sm[(warp * 32 + lane) * 33 + j] = (row_ok && j < width) ? v[j] : 0.f;
+      __syncthreads();
+      if (warp == 0) {
+        float s = 0.f, q = 0.f;
+        for (int r = 0; r < 128; ++r) {
+          const float t = stat_sm[r * 33 + lane];
+          s += t;
+          q += t * t;
+        }
+        const int col = n0 + c0 + lane;
+        if (lane < width && col < p.N) {
+          atomicAdd(p.col_sum + col, s);
+          atomicAdd(p.col_sumsq + col, q);
+        }
+      }
+    }
+    if (!row_ok) continue;
+    if (p.dropout_p > 0.f) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c0 + j));
+        v[j] = rt1_hash_u32(idx, p.seed) >= thresh ? v[j] * keep_scale : 0.f;
+      }
+    }
+    if (p.residual != nullptr) {
+      const bf16* rr = p.residual + (long)row * p.ldr + n0 + c0;
+#pragma unroll
+      for (int j8 = 0; j8 < 32; j8 += 8) {
+        if (j8 >= width) break;
+        const int col = n0 + c0 + j8;
+        if (col + 8 <= p.N && ((reinterpret_cast<uintptr_t>(rr + j8) & 15) == 0)) {
+          float r8[8];
+          unpack8(*reinterpret_cast<const bf16x8*>(rr + j8), r8);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[j8 + k] += r8[k];
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (col + k < p.N) v[j8 + k] += __bfloat162float(rr[j8 + k]);
+        }
+      }
+    }
+    if (p.out_fp32) {
+      float* o = reinterpret_cast<float*>(p.out) + (long)row * p.ldo + n0 + c0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        if (j < width && n0 + c0 + j < p.N) {
+          if (p.atomic_out) atomicAdd(o + j, v[j]);
+          else o[j] = v[j];
+        }
+      }
+    } else {
+      bf16* o = reinterpret_cast<bf16*>(p.out) + (long)row * p.ldo + n0 + c0;
+#pragma unroll
+      for (int j8 = 0; j8 < 32; j8 += 8) {
+        if (j8 >= width) break;
+        const int col = n0 + c0 + j8;
+        if (col + 8 <= p.N && ((reinterpret_cast<uintptr_t>(o + j8) & 15) == 0)) {
+          *reinterpret_cast<bf16x8*>(o + j8) = pack8(v + j8);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (col + k < p.N) o[j8 + k] = __float2bfloat16_rn(v[j8 + k]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+rt1_encode_tiled_fn rt1_get_encode_tiled() {
+  static rt1_encode_tiled_fn fn = nullptr;
+  if (fn) return fn;
+  void* f = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = (rt1_encode_tiled_fn)f;
+  return fn;
+}
+
+int rt1_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                          uint32_t box_cols) {
+  rt1_encode_tiled_fn enc = rt1_get_encode_tiled();
+  RT1_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  RT1_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0, "TMA operand must be 16-byte aligned (base %p, ld %llu)",
+              base, (unsigned long long)ld);
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstr[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RT1_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rows %llu cols %llu ld %llu box %ux%u)", (int)r,
+              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols);
+  return 0;
+}
+
+// D[M,N] = alpha * op(A) · op(B)^T (+bias) → dropout → (+residual)
+//   a_mn == 0: A is [M, K] row-major (lda = row stride);  a_mn == 1: A is stored as [K, M] row-major
+//   b_mn == 0: B is [N, K] row-major (ldb);               b_mn == 1: B is stored as [K, N] row-major
+//   out: bf16 (out_fp32 = 0) or fp32; split_k > 1 requires out_fp32 and pre-zeroed output (atomic accumulate)
+RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
+                          long long ldo, int out_fp32, int M, int N, int K, const void* bias, const void* residual,
+                          long long ldr, float alpha, float dropout_p, unsigned seed, int split_k, int accumulate,
+                          float* col_sum, float* col_sumsq, cudaStream_t stream) {
+  RT1_REQUIRE(M > 0 && N > 0 && K > 0, "rt1_gemm_bf16: empty problem %dx%dx%d", M, N, K);
+  RT1_REQUIRE(split_k >= 1, "rt1_gemm_bf16: split_k must be >= 1");
+  RT1_REQUIRE(split_k == 1 || out_fp32, "rt1_gemm_bf16: split-K needs an fp32 output");
+  RT1_REQUIRE(!(accumulate && !out_fp32), "rt1_gemm_bf16: accumulate needs an fp32 output");
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn;
+  // tile width: whole N when it fits in one UMMA (<= 256), else 128 — rounded up to the UMMA N granule of 16
+  int bn = N <= 256 ? ((N + 15) / 16) * 16 : 128;
+  p.block_n = bn;
+  const int total_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  p.kb_per_split = (total_kb + split_k - 1) / split_k;
+  const int splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+  const int stage_bytes = A_TILE_BYTES + b_tile_bytes(bn, b_mn);
+  int stages = p.kb_per_split < 4 ? p.kb_per_split : 4;
+  if (stages < 1) stages = 1;
+  // the column-statistics epilogue reuses the operand stages as a 128 x 33 fp32 transpose buffer
+  while (col_sum != nullptr && stages * stage_bytes < 128 * 33 * 4) ++stages;
+  p.stages = stages;
+  p.out = out; p.ldo = ldo; p.out_fp32 = out_fp32; p.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
+  p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
+  p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed;
+  p.col_sum = col_sum; p.col_sumsq = col_sumsq;
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn) rc = rt1_make_tmap_bf16_2d(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BLOCK_M, BLOCK_K);
+  else rc = rt1_make_tmap_bf16_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BLOCK_K, 64);
+  if (rc) return rc;
+  if (!b_mn) rc = rt1_make_tmap_bf16_2d(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, (uint32_t)bn, BLOCK_K);
+  else rc = rt1_make_tmap_bf16_2d(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BLOCK_K, 64);
+  if (rc) return rc;
+
+  const size_t smem = (size_t)stages * stage_bytes + (2 * stages + 2) * 8 + 1024;
+  static size_t configured = 0;
+  if (smem > configured) {
+    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  dim3 grid((M + BLOCK_M - 1) / BLOCK_M, (N + bn - 1) / bn, splits);
+  gemm_tcgen05_kernel<<<grid, 128, smem, stream>>>(ta, tb, p);
+  return rt1_check_launch("rt1_gemm_bf16");
+}
+
+// column sums of a bf16 [M, N] matrix → bf16 [N] (bias gradients)
+__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, long ld, int M, int N, bf16* __restrict__ out) {
+  __shared__ float sm[8][33];
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31), r0 = threadIdx.x >> 5;
+  float s = 0.f;
+  if (col < N)
+    for (int r = r0; r < M; r += 8) s += __bfloat162float(x[(long)r * ld + col]);
+  sm[r0][threadIdx.x & 31] = s;
+  __syncthreads();
+  if (r0 == 0 && col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sm[i][threadIdx.x & 31];
+    out[col] = __float2bfloat16_rn(t);
+  }
+}
+RT1_API int rt1_colsum_bf16(const void* x, long long ld, int M, int N, void* out, cudaStream_t stream) {
+  colsum_kernel<<<rt1_cdiv(N, 32), 256, 0, stream>>>((const bf16*)x, ld, M, N, (bf16*)out);
+  return rt1_check_launch("rt1_colsum_bf16");
+}
+
+// fp32 → bf16 cast of a small buffer (split-K weight-gradient workspace → gradient slot)
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long n) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = __float2bfloat16_rn(in[i]);
+}
+RT1_API int rt1_cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t stream) {
+  cast_f32_bf16_kernel<<<rt1_cdiv(n, 256), 256, 0, stream>>>(in, (bf16*)out, n);
+  return rt1_check_launch("rt1_cast_f32_bf16");
+}

@@ -1,0 +1,167 @@
+// LayerNorm forward/backward over bf16 rows (decoder pre-LN; replaces ATen layer_norm in K11).
+//
+// Forward: one warp per row, the row lives in registers (D <= 2048), two-pass mean/variance in fp32, writes
+// y (bf16) and per-row mean / rstd (fp32) for the backward.
+// Backward: one warp per row for dx; per-column dgamma/dbeta partials are accumulated per CTA in shared
+// memory over the rows that CTA owns and written to a [grid, 2, D] fp32 scratch, which a second kernel folds
+// and stores as bf16 straight into the parameter-gradient slots.
+#include "common.cuh"
+
+#define LN_MAX_PER_LANE 64  // D <= 2048
+
+template <int VPL>  // 8-element vectors per lane
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                     const bf16* __restrict__ b, bf16* __restrict__ y,
+                                                     float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
+                                                     int D, float eps) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int row = blockIdx.x * wpb + warp;
+  if (row >= rows) return;
+  const bf16x8* xr = reinterpret_cast<const bf16x8*>(x + (size_t)row * D);
+  float v[VPL * 8];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    unpack8(xr[lane + 32 * i], v + 8 * i);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[8 * i + k];
+  }
+  const float mean = warp_sum(s) / D;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < VPL * 8; ++i) {
+    float d = v[i] - mean;
+    q += d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) / D + eps);
+  bf16x8* yr = reinterpret_cast<bf16x8*>(y + (size_t)row * D);
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    float wv[8], bv[8], o[8];
+    unpack8(reinterpret_cast<const bf16x8*>(w)[lane + 32 * i], wv);
+    unpack8(reinterpret_cast<const bf16x8*>(b)[lane + 32 * i], bv);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = (v[8 * i + k] - mean) * rstd * wv[k] + bv[k];
+    yr[lane + 32 * i] = pack8(o);
+  }
+  if (lane == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                     const bf16* __restrict__ dy, const float* __restrict__ mean_in,
+                                                     const float* __restrict__ rstd_in, bf16* __restrict__ dx,
+                                                     float* __restrict__ partial, int rows, int D) {
+  extern __shared__ float sm[];  // [2][D] per-CTA dgamma / dbeta partials
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  float wv[VPL * 8];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) unpack8(reinterpret_cast<const bf16x8*>(w)[lane + 32 * i], wv + 8 * i);
+  float dg[VPL * 8], db[VPL * 8];
+#pragma unroll
+  for (int i = 0; i < VPL * 8; ++i) dg[i] = db[i] = 0.f;
+  for (int row = blockIdx.x * wpb + warp; row < rows; row += gridDim.x * wpb) {
+    const bf16x8* xr = reinterpret_cast<const bf16x8*>(x + (size_t)row * D);
+    const bf16x8* gr = reinterpret_cast<const bf16x8*>(dy + (size_t)row * D);
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float xh[VPL * 8], g[VPL * 8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      unpack8(xr[lane + 32 * i], xh + 8 * i);
+      unpack8(gr[lane + 32 * i], g + 8 * i);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int j = 8 * i + k;
+        xh[j] = (xh[j] - mean) * rstd;
+        dg[j] += g[j] * xh[j];
+        db[j] += g[j];
+        g[j] *= wv[j];
+        s1 += g[j];
+        s2 += g[j] * xh[j];
+      }
+    }
+    s1 = warp_sum(s1) / D;
+    s2 = warp_sum(s2) / D;
+    bf16x8* dr = reinterpret_cast<bf16x8*>(dx + (size_t)row * D);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = rstd * (g[8 * i + k] - s1 - xh[8 * i + k] * s2);
+      dr[lane + 32 * i] = pack8(o);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < VPL; ++i)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int col = (lane + 32 * i) * 8 + k;
+      atomicAdd(&sm[col], dg[8 * i + k]);
+      atomicAdd(&sm[D + col], db[8 * i + k]);
+    }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) partial[(size_t)blockIdx.x * 2 * D + i] = sm[i];
+}
+
+__global__ void ln_param_grad_kernel(const float* __restrict__ partial, int nblk, int D, bf16* __restrict__ dw,
+                                     bf16* __restrict__ db) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= D) return;
+  float a = 0.f, c = 0.f;
+  for (int i = 0; i < nblk; ++i) {
+    a += partial[(size_t)i * 2 * D + col];
+    c += partial[(size_t)i * 2 * D + D + col];
+  }
+  dw[col] = __float2bfloat16_rn(a);
+  db[col] = __float2bfloat16_rn(c);
+}
+
+RT1_API int rt1_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean, float* rstd, int rows,
+                              int D, float eps, cudaStream_t stream) {
+  RT1_REQUIRE(D % 256 == 0 && D <= 2048, "rt1_layernorm_fwd: D=%d must be a multiple of 256 and <= 2048", D);
+  const int wpb = 8, grid = rt1_cdiv(rows, wpb);
+#define LN_F(V) ln_fwd_kernel<V><<<grid, wpb * 32, 0, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)b, (bf16*)y, mean, rstd, rows, D, eps)
+  switch (D / 256) {
+    case 1: LN_F(1); break;
+    case 2: LN_F(2); break;
+    case 4: LN_F(4); break;
+    case 8: LN_F(8); break;
+    default: RT1_REQUIRE(false, "rt1_layernorm_fwd: unsupported D=%d", D);
+  }
+#undef LN_F
+  return rt1_check_launch("rt1_layernorm_fwd");
+}
+
+// scratch: fp32 [rt1_layernorm_bwd_scratch_floats(rows, D)]
+RT1_API long long rt1_layernorm_bwd_scratch_floats(int rows, int D) {
+  int grid = rt1_cdiv(rows, 8);
+  if (grid > 148) grid = 148;
+  return (long long)grid * 2 * D;
+}
+
+RT1_API int rt1_layernorm_bwd(const void* x, const void* w, const void* dy, const float* mean, const float* rstd,
+                              void* dx, void* dw, void* db, float* scratch, int rows, int D, cudaStream_t stream) {
+  RT1_REQUIRE(D % 256 == 0 && D <= 2048, "rt1_layernorm_bwd: D=%d must be a multiple of 256 and <= 2048", D);
+  int grid = rt1_cdiv(rows, 8);
+  if (grid > 148) grid = 148;
+  const size_t smem = 2 * (size_t)D * sizeof(float);
+#define LN_B(V) ln_bwd_kernel<V><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D)
+  switch (D / 256) {
+    case 1: LN_B(1); break;
+    case 2: LN_B(2); break;
+    case 4: LN_B(4); break;
+    case 8: LN_B(8); break;
+    default: RT1_REQUIRE(false, "rt1_layernorm_bwd: unsupported D=%d", D);
+  }
+#undef LN_B
+  int rc = rt1_check_launch("rt1_layernorm_bwd");
+  if (rc) return rc;
+  ln_param_grad_kernel<<<rt1_cdiv(D, 128), 128, 0, stream>>>(scratch, grid, D, (bf16*)dw, (bf16*)db);
+  return rt1_check_launch("rt1_layernorm_param_grad");
+}

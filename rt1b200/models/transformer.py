@@ -80,7 +80,9 @@ class TF_MultiHeadAttention(nn.Module):
             wqkv, bqkv = self._fused_qkv()
             x2 = q.reshape(bs * sl, self.d_model)
             if wqkv is not None:
-                qkv = ops.linear(x2, wqkv, bqkv)                       # [bs*sl, 3*h*dk]
+                qkv = ops.linear(x2, wqkv, bqkv, wgrad=self._qkv_w_grad, bgrad=self._qkv_b_grad,
+                                 notify=[self.q_linear.weight, self.k_linear.weight, self.v_linear.weight,
+                                         self.q_linear.bias, self.k_linear.bias, self.v_linear.bias])   # [bs*sl, 3*h*dk]
             else:
                 qkv = torch.cat([ops.linear(x2, self.q_linear.weight, self.q_linear.bias),
                                  ops.linear(x2, self.k_linear.weight, self.k_linear.bias),

@@ -64,11 +64,14 @@ def _k():
 
 
 # ----------------------------------------------------------------------------------------------- decoder
-def linear(x, w, b=None, residual=None, act: Optional[str] = None, dropout_p: float = 0.0):
+def linear(x, w, b=None, residual=None, act: Optional[str] = None, dropout_p: float = 0.0, wgrad=None, bgrad=None,
+           notify=None):
     """``residual + dropout(act(x @ w.T + b))``; ``x [M,K]``, ``w [N,K]`` → ``[M,N]``.
-    Kernel: tcgen05/TMEM GEMM fed by TMA with the bias/activation/dropout/residual epilogue fused."""
+    Kernel: tcgen05/TMEM GEMM fed by TMA with the bias/activation/dropout/residual epilogue fused.
+    ``wgrad``/``bgrad``/``notify`` (kernel path only): explicit gradient destinations for fused operand views
+    such as the concatenated q/k/v projection, and the parameters to announce as gradient-ready."""
     if use_kernels(x):
-        return _k().linear(x, w, b, residual, act, dropout_p)
+        return _k().linear(x, w, b, residual, act, dropout_p, wgrad=wgrad, bgrad=bgrad, notify=notify)
     seed = int(torch.randint(0, 2 ** 31 - 1, ()).item()) if dropout_p > 0 else 0
     return reference.linear(x, w, b, residual, act, dropout_p, seed)
 

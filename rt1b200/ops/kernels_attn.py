@@ -1,0 +1,93 @@
+"""Autograd wrappers for the fused masked-attention and TokenLearner kernels (``csrc/attention.cu``,
+``csrc/token_learner.cu``)."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+from torch.autograd import Function
+
+from . import _lib
+from ._lib import call, f32, i32, i64, ptr, stream
+
+BF16 = torch.bfloat16
+
+
+def _u32(v):
+    return ctypes.c_uint(int(v) & 0xFFFFFFFF)
+
+
+class _Attention(Function):
+    @staticmethod
+    def forward(ctx, qkv, mask, p_drop, seed):
+        b, s, three, h, dk = qkv.shape
+        assert three == 3
+        qkv = qkv if qkv.is_contiguous() else qkv.contiguous()
+        if mask is not None:
+            mask = mask.to(device=qkv.device, dtype=torch.uint8).contiguous()
+        out = torch.empty(b, s, h * dk, dtype=BF16, device=qkv.device)
+        call("rt1_attention_fwd", ptr(qkv), ptr(mask), ptr(out), i32(b), i32(s), i32(h), i32(dk), f32(p_drop), _u32(seed),
+             stream())
+        ctx.save_for_backward(qkv, mask)
+        ctx.meta = (p_drop, seed)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, mask = ctx.saved_tensors
+        p_drop, seed = ctx.meta
+        b, s, _, h, dk = qkv.shape
+        dout = dout if dout.is_contiguous() else dout.contiguous()
+        dqkv = torch.empty_like(qkv)
+        call("rt1_attention_bwd", ptr(qkv), ptr(mask), ptr(dout), ptr(dqkv), i32(b), i32(s), i32(h), i32(dk), f32(p_drop),
+             _u32(seed), stream())
+        return dqkv, None, None, None
+
+
+def rt1_attention(qkv, mask, p_drop: float = 0.0, seed: Optional[int] = None):
+    from . import kernels
+    if seed is None:
+        seed = kernels.next_seed() if p_drop > 0 else 0
+    return _Attention.apply(qkv, mask, float(p_drop), int(seed))
+
+
+class _TokenLearner(Function):
+    @staticmethod
+    def forward(ctx, feats, ln_w, ln_b, w1, b1, w2, b2, eps, params):
+        n, P, C = feats.shape
+        T = w2.shape[0]
+        feats = feats if feats.is_contiguous() else feats.contiguous()
+        w1m = w1.reshape(w1.shape[0], -1)
+        w2m = w2.reshape(T, -1)
+        assert w1m.shape == (64, C) and w2m.shape == (T, 64), "TokenLearner kernel expects a 64-wide bottleneck"
+        tokens = torch.empty(n, T, C, dtype=BF16, device=feats.device)
+        call("rt1_token_learner_fwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(tokens),
+             i64(T * C), i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
+        ctx.save_for_backward(feats, ln_w, ln_b, w1m, b1, w2m, b2)
+        ctx.meta = (eps, params)
+        return tokens
+
+    @staticmethod
+    def backward(ctx, dtok):
+        from .kernels import _grad_slot, _ready
+        feats, ln_w, ln_b, w1m, b1, w2m, b2 = ctx.saved_tensors
+        eps, params = ctx.meta
+        n, P, C = feats.shape
+        T = w2m.shape[0]
+        dtok = dtok if dtok.is_contiguous() else dtok.contiguous()
+        dfeats = torch.empty_like(feats)
+        ns = 64 * C + 64 + T * 64 + T + 2 * C
+        scratch = torch.empty(ns, dtype=torch.float32, device=feats.device)
+        g = [_grad_slot(p) for p in params]     # order: ln_w, ln_b, w1, b1, w2, b2
+        call("rt1_token_learner_bwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(dtok),
+             i64(T * C), ptr(dfeats), ptr(scratch), ptr(g[0]), ptr(g[1]), ptr(g[2]), ptr(g[3]), ptr(g[4]), ptr(g[5]),
+             i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
+        _ready(params)
+        return (dfeats,) + (None,) * 8
+
+
+def token_learner(feats, ln_w, ln_b, w1, b1, w2, b2, eps: float = 1e-5):
+    params = (ln_w, ln_b, w1, b1, w2, b2)
+    return _TokenLearner.apply(feats, ln_w.detach(), ln_b.detach(), w1.detach(), b1.detach(), w2.detach(), b2.detach(),
+                               float(eps), params)

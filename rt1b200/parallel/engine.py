@@ -134,6 +134,20 @@ class DataParallelEngine:
                 _self._ready_count[b] += 1
                 _self._maybe_launch_ready()
             self._hook_handles.append(p.register_post_accumulate_grad_hook(hook))
+        # gradients written directly by the sm_100a backward kernels never pass through autograd's accumulate
+        # step; the kernel wrappers announce them through this callback instead
+        from ..ops import kernels as _kernels
+
+        def on_ready(params, _self=self):
+            if not _self._eager:
+                return
+            for prm in params:
+                b = _self._bucket_of.get(id(prm))
+                if b is not None:
+                    _self._ready_count[b] += 1
+            _self._maybe_launch_ready()
+        if self.device.type == "cuda" and _lib.available():
+            _kernels.GRAD_READY = on_ready
 
     # --------------------------------------------------------------------------------------- stepping
     def zero_grad(self):
