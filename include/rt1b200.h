@@ -1,0 +1,92 @@
+/* rt1b200 — C ABI of the sm_100a kernel library (rt1b200/lib/librt1b200.so).
+ *
+ * Conventions: every function returns 0 on success, otherwise a CUDA error code or -1 (argument/shape error) and
+ * rt1_last_error() holds a message (thread-local).  All pointers are device pointers unless stated otherwise;
+ * bf16 tensors are passed as void*; every launch goes to the given stream and returns without synchronising.
+ * No entry point allocates device memory: scratch buffers are caller-provided (their sizes are given per call).
+ *
+ * "Reference" citations name the file:line of tanhuajie/Pytorch-RT1-for-Distributed-Training whose behaviour
+ * the kernel reproduces (the reference itself has no native code; it reaches these ops through ATen/cuDNN/
+ * cuBLAS/NCCL).
+ */
+#ifndef RT1B200_H_
+#define RT1B200_H_
+
+#include <cuda_runtime.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ------------------------------------------------------------------------------------------- */
+const char* rt1_last_error(void);
+int rt1_abi_version(void);
+int rt1_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* smem_optin);
+/* Benchmark helper: stream `bytes` of writes through `buf` (use a buffer larger than the 126 MB L2). */
+int rt1_l2_flush(void* buf, long long bytes, unsigned tag, cudaStream_t stream);
+
+/* ---- GEMM: tcgen05.mma + TMEM accumulator + TMA operand loads ---------------------------------------------
+ * out[M,N] = alpha * op(A) . op(B)^T (+ bias[N]) -> dropout(p, seed) -> (+ residual[M,N]).
+ * a_mn = 0: A is [M,K] row-major (lda);  a_mn = 1: A is stored [K,M] row-major (a transposed view, free).
+ * b_mn = 0: B is [N,K] row-major (ldb);  b_mn = 1: B is stored [K,N] row-major.
+ * out is bf16 (out_fp32 = 0) or fp32; split_k > 1 / accumulate need fp32 `out` (atomic accumulation; zero it first).
+ * col_sum / col_sumsq (optional, fp32 [N], caller-zeroed): per-column sum and sum of squares of the fp32 result
+ * (BatchNorm batch statistics fused into the producing GEMM).
+ * Replaces: nn.Linear of the decoder (reference transformer.py:45-49,126,171-173) and every 1x1 convolution of
+ * the image tokenizer (film_efficientnet_encoder.py:185-224,329-336; pretrained_efficientnet_encoder.py:45-51). */
+int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
+                  long long ldo, int out_fp32, int M, int N, int K, const void* bias, const void* residual,
+                  long long ldr, float alpha, float dropout_p, unsigned seed, int split_k, int accumulate,
+                  float* col_sum, float* col_sumsq, cudaStream_t stream);
+int rt1_colsum_bf16(const void* x, long long ld, int M, int N, void* out_bf16, cudaStream_t stream);
+int rt1_cast_f32_bf16(const float* in, void* out_bf16, long long n, cudaStream_t stream);
+int rt1_dropout_apply(const void* in, void* out, long long n, float p, unsigned seed, cudaStream_t stream);
+
+/* ---- LayerNorm (reference transformer.py:123,129,132-141) ------------------------------------------------ */
+int rt1_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean, float* rstd, int rows,
+                      int D, float eps, cudaStream_t stream);
+long long rt1_layernorm_bwd_scratch_floats(int rows, int D);
+/* scratch: fp32 [rt1_layernorm_bwd_scratch_floats(rows, D)] of per-CTA dgamma/dbeta partials */
+int rt1_layernorm_bwd(const void* x, const void* w, const void* dy, const float* mean, const float* rstd, void* dx,
+                      void* dw, void* db, float* scratch, int rows, int D, cudaStream_t stream);
+
+/* ---- fused masked attention over the RT-1 token window (reference transformer.py:82-109) ------------------
+ * qkv [B,S,3,H,DK] bf16 -> out [B,S,H*DK]; mask uint8 [S,S] (0 = blocked) or NULL. */
+int rt1_attention_fwd(const void* qkv, const unsigned char* mask, void* out, int B, int S, int H, int DK, float p_drop,
+                      unsigned seed, cudaStream_t stream);
+int rt1_attention_bwd(const void* qkv, const unsigned char* mask, const void* dout, void* dqkv, int B, int S, int H,
+                      int DK, float p_drop, unsigned seed, cudaStream_t stream);
+
+/* ---- action-token cross-entropy (reference transformer_network.py:304-322) -------------------------------
+ * logits [R,A,V] bf16, labels int64 [R,A] -> loss[r] = mean_a CE / num_items, pred = argmax.  row_ce / row_lse: fp32 [R*A]. */
+int rt1_action_ce_fwd(const void* logits, const long long* labels, float* loss, float* row_ce, float* row_lse,
+                      long long* pred, int R, int A, int V, float num_items, cudaStream_t stream);
+int rt1_action_ce_bwd(const void* logits, const long long* labels, const float* row_lse, const float* dloss,
+                      void* dlogits, int R, int A, int V, float num_items, cudaStream_t stream);
+
+/* ---- TokenLearner (reference tokenizers/token_learner.py:64-95) --------------------------------------------
+ * feats [n,P,C] bf16 -> tokens (row n at tokens + n*out_stride, [T,C]). 64-wide bottleneck. */
+int rt1_token_learner_fwd(const void* feats, const void* ln_w, const void* ln_b, const void* w1, const void* b1,
+                          const void* w2, const void* b2, void* tokens, long long out_stride, int n, int P, int C, int T,
+                          float eps, cudaStream_t stream);
+long long rt1_token_learner_scratch_floats(int C, int T);
+/* scratch: fp32 [rt1_token_learner_scratch_floats(C, T)]; cleared by the call, holds the parameter-gradient sums */
+int rt1_token_learner_bwd(const void* feats, const void* ln_w, const void* ln_b, const void* w1, const void* b1,
+                          const void* w2, const void* b2, const void* dtokens, long long dtok_stride, void* dfeats,
+                          float* scratch, void* dln_w, void* dln_b, void* dw1, void* db1, void* dw2, void* db2, int n, int P,
+                          int C, int T, float eps, cudaStream_t stream);
+
+/* ---- frame pre-processing (reference film_efficientnet/preprocessors.py:37-56) ---------------------------
+ * in [N,3,H,W] uint8|f32 -> out [N,H,W,8] bf16 NHWC with the pad-and-shift crop (one offset per batch). */
+int rt1_preprocess_nhwc(const void* in, int in_is_uint8, void* out, int N, int H, int W, int shift_h, int shift_w,
+                        int pad_h, int pad_w, cudaStream_t stream);
+
+/* ---- optimizer: flat fused AdamW (reference distribute_train.py:100 torch.optim.Adam) ---------------------- */
+int rt1_fused_adamw(void* param_bf16, float* master, void* grad, int grad_is_bf16, float* exp_avg, float* exp_avg_sq,
+                    long long n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
+                    float bias_corr2, float grad_scale, int zero_grad, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT1B200_H_ */

@@ -6,18 +6,7 @@
 // 572 tensors plus a separate zero_grad).  Decoupled weight decay; with wd == 0 this is exactly torch.optim.Adam.
 #include "common.cuh"
 
-struct AdamHyper {
-  float lr, beta1, beta2, eps, wd, inv_bc1, inv_sqrt_bc2, grad_scale;
-};
-
-__device__ __forceinline__ void adam_update(float& p, float g, float& m, float& v, const AdamHyper& h) {
-  g *= h.grad_scale;
-  p *= (1.f - h.lr * h.wd);
-  m = h.beta1 * m + (1.f - h.beta1) * g;
-  v = h.beta2 * v + (1.f - h.beta2) * g * g;
-  float denom = sqrtf(v) * h.inv_sqrt_bc2 + h.eps;
-  p -= h.lr * h.inv_bc1 * (m / denom);
-}
+#include "adam.cuh"
 
 template <bool GRAD_BF16>
 __global__ void __launch_bounds__(256) adamw_flat_kernel(bf16* __restrict__ p_lp, float* __restrict__ p, void* __restrict__ g_,

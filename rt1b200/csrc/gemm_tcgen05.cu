@@ -259,6 +259,13 @@ rt1_encode_tiled_fn rt1_get_encode_tiled() {
 
 int rt1_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
                           uint32_t box_cols) {
+  // The driver-API encoder needs a current context on the calling thread; autograd's backward threads may not
+  // have touched the runtime yet, so bind the primary context once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    RT1_CHECK_CUDA(cudaFree(0));
+    ctx_bound = true;
+  }
   rt1_encode_tiled_fn enc = rt1_get_encode_tiled();
   RT1_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
   RT1_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0, "TMA operand must be 16-byte aligned (base %p, ld %llu)",

@@ -248,8 +248,35 @@ class DataParallelEngine:
         return t / self.world
 
     # ------------------------------------------------------------------------------------ checkpoints
+    def _owned_ranges(self, rank: int) -> List[Tuple[int, int]]:
+        """Element ranges of the flat buffers whose fp32 state rank ``rank`` updates under the sharded P2P step
+        (mirrors ``shard_bounds`` in csrc/p2p.cu)."""
+        out = []
+        for lo, hi in self.buckets:
+            n = hi - lo
+            chunk = ((n + self.world - 1) // self.world + 7) & ~7
+            a = min(n, chunk * rank)
+            b = min(n, a + chunk)
+            out.append((lo + a, lo + b))
+        return out
+
+    def gather_sharded_state(self):
+        """P2P backend: every rank updates only its 1/W shard of master/exp_avg/exp_avg_sq; before a checkpoint
+        (or any read of the full fp32 state) the owners' shards are combined on all ranks.  Rare, so it uses the
+        bootstrap process group rather than a dedicated kernel."""
+        if self.backend != "p2p" or self.world == 1 or self.step_count == 0:
+            return
+        dist = _dist()
+        for buf in (self.flat.master, self.flat.exp_avg, self.flat.exp_avg_sq):
+            tmp = torch.zeros_like(buf)
+            for a, b in self._owned_ranges(self.rank):
+                tmp[a:b] = buf[a:b]
+            dist.all_reduce(tmp, group=self.group)
+            buf.copy_(tmp)
+
     def model_state_dict(self, prefix: str = "") -> Dict[str, torch.Tensor]:
-        """fp32 state dict with the model's own keys (master weights substituted for bf16 parameters)."""
+        """fp32 state dict with the model's own keys (master weights substituted for bf16 parameters).
+        With the P2P backend call :meth:`gather_sharded_state` on ALL ranks first (it is a collective)."""
         sd = {}
         masters = {s.name: self.flat.view(self.flat.master, s.name) for s in self.flat.slots}
         for k, v in self.model.state_dict().items():

@@ -82,6 +82,9 @@ class FlatParams:
             self.master[s.offset:s.offset + s.numel].copy_(p.detach().reshape(-1).to(self.device, torch.float32))
         if self.param_dtype == torch.float32:
             self.param = self.master                      # fp32 training: parameters ARE the master copy
+        elif grad_alloc is not None:                       # peer-visible parameter buffer (P2P all-gather target)
+            self.param = grad_alloc(self.numel, self.param_dtype, self.device)
+            self.param.copy_(self.master)
         else:
             self.param = self.master.to(self.param_dtype)
         alloc = grad_alloc or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))

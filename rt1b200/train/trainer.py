@@ -269,6 +269,7 @@ class Trainer:
         }
 
     def save_checkpoint(self, metrics: Optional[Dict[str, float]] = None) -> Optional[str]:
+        self.engine.gather_sharded_state()      # collective: every rank contributes the fp32 shards it owns
         if self.rank != 0:
             return None
         os.makedirs(self.ckpt_dir, exist_ok=True)

@@ -1,0 +1,170 @@
+"""Multi-process worker: symmetric memory, P2P all-reduce and the fused all-reduce+AdamW vs NCCL + reference Adam,
+then a full RT-1 training step through the engine with backend='p2p'.  Optionally a bandwidth sweep (--sweep)."""
+import json
+import os
+import sys
+import time
+from argparse import Namespace
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from rt1b200.ops import reference as ref  # noqa: E402
+from rt1b200.parallel.symm import SymmetricComm  # noqa: E402
+
+
+def timed(fn, iters, world, dev):
+    torch.cuda.synchronize(); dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    comm = SymmetricComm(ctas_per_rank=int(os.environ.get("RT1_P2P_CTAS", "32")))
+
+    # 1. all-reduce, both schedules, both dtypes
+    for dtype in (torch.bfloat16, torch.float32):
+        for n in (8 * 16, 8 * 12345, 8 * 1024 * 128):
+            for two_shot in (True, False):
+                buf = comm.alloc_tensor(2 * n, dtype)
+                torch.manual_seed(7 + rank)
+                x = torch.randn(n, device=dev).to(dtype)
+                buf[:n].copy_(x)
+                want = x.float().clone()
+                dist.all_reduce(want)
+                torch.cuda.synchronize(); dist.barrier()
+                out = comm.allreduce_(buf, scale=1.0, two_shot=two_shot, n=n)
+                torch.cuda.synchronize()
+                tol = 3e-2 if dtype == torch.bfloat16 else 1e-5
+                torch.testing.assert_close(out.float(), want.to(dtype).float(), rtol=tol, atol=tol)
+    s = comm.allreduce_small(torch.tensor([float(rank + 1), 2.0], device=dev))
+    assert s.tolist() == [world * (world + 1) / 2, 2.0 * world], s
+
+    # 2. fused all-reduce + AdamW on a flat buffer vs NCCL + reference Adam
+    n = 64 * 4096
+    grad = comm.alloc_tensor(n, torch.bfloat16)
+    param = comm.alloc_tensor(n, torch.bfloat16)
+    comm.register_grad_buffer(grad); comm.register_param_buffer(param)
+    torch.manual_seed(0)
+    master = torch.randn(n, device=dev)
+    param.copy_(master)
+    m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    want_p, want_m, want_v = master.clone(), m.clone(), v.clone()
+    flat = Namespace(master=master, exp_avg=m, exp_avg_sq=v)
+    for step in range(1, 4):
+        torch.manual_seed(100 * step + rank)
+        g = (torch.randn(n, device=dev) * 0.1).to(torch.bfloat16)
+        grad.copy_(g)
+        gs = g.float().clone(); dist.all_reduce(gs)
+        h = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, bc1=1 - 0.9 ** step, bc2=1 - 0.999 ** step)
+        for lo, hi in ((0, n // 2), (n // 2, n)):            # two buckets
+            comm.allreduce_adamw(lo, hi, flat, h)
+        torch.cuda.synchronize()
+        ref.adamw_step(want_p, gs, want_m, want_v, 1e-3, 0.9, 0.999, 1e-8, 0.0, step, grad_scale=1.0 / world)
+        torch.testing.assert_close(param.float(), want_p.to(torch.bfloat16).float(), rtol=0, atol=0)
+        assert float(grad.abs().max()) == 0.0
+    dist.barrier()
+
+    # 3. a real RT-1 training step through the engine
+    from rt1b200.data.dataset import SyntheticBatchSource
+    from rt1b200.models.factory import RT1Config
+    from rt1b200.train.trainer import RT1Module, Trainer
+    args = Namespace(height=64, width=96, seq_len=3, lr=1e-3, milestones=[], exp_name="p2p", log_dir="/tmp/rt1_p2p/logs",
+                     ckpt_dir="/tmp/rt1_p2p/ckpt", log_every_n_steps=1000, ckpt_every_n_epochs=1, max_epochs=1)
+    cfg = RT1Config(height=64, width=96, seq_len=3, num_layers=2, layer_size=128, num_heads=8, dropout_rate=0.0)
+    torch.manual_seed(1234 + rank)
+    tr = Trainer(RT1Module(args, cfg), args, device=dev, backend="p2p", param_dtype=torch.bfloat16, loggers=[], verbose=False)
+    assert tr.engine.backend == "p2p"
+    src = SyntheticBatchSource(2, 3, 64, 96, pool=2, seed=10 + rank, image_dtype=torch.uint8, pin=False)
+    losses = [float(tr.train_step(next(src))) for _ in range(3)]
+    torch.cuda.synchronize()
+    assert all(l == l for l in losses), losses
+    # parameters identical on every rank after the fused exchange
+    p = tr.engine.flat.param.float()
+    ref_p = p.clone(); dist.broadcast(ref_p, 0)
+    assert torch.equal(p, ref_p), "bf16 parameters diverged across ranks"
+    tr.engine.gather_sharded_state()
+    mast = tr.engine.flat.master.clone(); dist.broadcast(mast, 0)
+    assert torch.equal(tr.engine.flat.master, mast)
+    torch.testing.assert_close(tr.engine.flat.master.to(torch.bfloat16).float(), p, rtol=0, atol=0)
+
+    # 4. optional sweep: bus bandwidth of P2P two-shot / one-shot vs NCCL, and the fused step's roofline fraction
+    if "--sweep" in sys.argv:
+        rows = []
+        sizes = [1 << k for k in range(10, 29)]          # 1 KB .. 256 MB
+        big = comm.alloc_tensor((256 << 20) // 2 * 2, torch.bfloat16)
+        nccl_buf = torch.zeros((256 << 20) // 2, dtype=torch.bfloat16, device=dev)
+        for nbytes in sizes:
+            n_el = max(8, nbytes // 2)
+            iters = 50 if nbytes <= (1 << 22) else 10
+            row = {"bytes": n_el * 2, "world": world}
+            for name, fn in (("p2p_two_shot_us", lambda: comm.allreduce_(big, two_shot=True, n=n_el)),
+                             ("p2p_one_shot_us", (lambda: comm.allreduce_(big, two_shot=False, n=n_el)) if nbytes <= (64 << 20) else None),
+                             ("nccl_us", lambda: dist.all_reduce(nccl_buf[:n_el]))):
+                if fn is None:
+                    continue
+                for _ in range(3):
+                    fn()
+                row[name] = timed(fn, iters, world, dev) * 1e3
+            best = min(row.get("p2p_two_shot_us", 1e30), row.get("p2p_one_shot_us", 1e30))
+            row["p2p_busbw_gbs"] = 2 * (world - 1) / world * row["bytes"] / (best * 1e-6) / 1e9
+            row["nccl_busbw_gbs"] = 2 * (world - 1) / world * row["bytes"] / (row["nccl_us"] * 1e-6) / 1e9
+            rows.append(row)
+        # fused all-reduce + AdamW over an RT-1 sized flat buffer (35.3M elements) and the scaled variant (143M)
+        fused = []
+        for n_par in (35_324_352, 142_976_000):
+            n_par = n_par // 64 * 64
+            g2 = comm.alloc_tensor(n_par, torch.bfloat16); p2 = comm.alloc_tensor(n_par, torch.bfloat16)
+            comm.register_grad_buffer(g2); comm.register_param_buffer(p2)
+            fl = Namespace(master=torch.zeros(n_par, device=dev), exp_avg=torch.zeros(n_par, device=dev),
+                           exp_avg_sq=torch.zeros(n_par, device=dev))
+            h = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, bc1=0.1, bc2=0.001)
+            bucket = 16 * 1024 * 1024
+            bounds = [(a, min(n_par, a + bucket)) for a in range(0, n_par, bucket)]
+
+            def fused_step():
+                for lo, hi in bounds:
+                    comm.allreduce_adamw(lo, hi, fl, h)
+
+            def nccl_step():
+                dist.all_reduce(g2)
+                from rt1b200.ops import kernels
+                kernels.fused_adamw(p2, fl.master, g2, fl.exp_avg, fl.exp_avg_sq, h, grad_scale=1.0 / world, zero_grad=True)
+            for _ in range(3):
+                fused_step()
+            t_f = timed(fused_step, 10, world, dev)
+            for _ in range(3):
+                nccl_step()
+            t_n = timed(nccl_step, 10, world, dev)
+            link_bytes = 2 * (world - 1) / world * n_par * 2            # per direction per GPU: pull grads + push params
+            t_link = link_bytes / 770e9 * 1e3
+            hbm_bytes = n_par * (2 + 2) + n_par / world * (2 * world + 24 + 2)   # zero+incoming params, shard state
+            t_hbm = hbm_bytes / 6551e9 * 1e3
+            fused.append({"params": n_par, "world": world, "fused_ms": t_f, "nccl_plus_fused_adam_ms": t_n,
+                          "roof_link_ms": t_link, "roof_hbm_ms": t_hbm, "roofline_fraction": max(t_link, t_hbm) / t_f})
+        if rank == 0:
+            os.makedirs("gpurun_out", exist_ok=True)
+            with open(f"gpurun_out/p2p_sweep_w{world}.json", "w") as f:
+                json.dump({"allreduce": rows, "fused_allreduce_adamw": fused}, f, indent=1)
+            print(json.dumps(fused))
+    dist.barrier()
+    if rank == 0:
+        print("P2P_WORKER_OK", flush=True)
+    tr.engine.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -184,6 +184,9 @@ def test_token_learner_fwd_bwd():
     _close(tok, tokr, msg="tokens")
     _close(feats.grad, fr.grad, rtol=3e-2, atol=3e-2, msg="dfeats")
     for p, r, name in zip(params, pr, ["ln_w", "ln_b", "w1", "b1", "w2", "b2"]):
+        if name == "b2":      # softmax over positions: d(logit) sums to zero per token, so this gradient is ~0
+            assert float(p.grad.float().abs().max()) < 2e-2 and float(r.grad.abs().max()) < 1e-3
+            continue
         scale = float(r.grad.abs().max()) + 1e-6
         _close(p.grad.reshape(r.grad.shape) / scale, r.grad / scale, rtol=5e-2, atol=3e-2, msg=name)
 
