@@ -121,7 +121,7 @@ class SymmetricComm(_CommBase):
              _ptr_array(self._flag_ptrs), i64(0), i64(n), i32(t.dtype == torch.bfloat16), f32(scale), i32(two_shot),
              ctypes.c_uint(self._next_epoch()), i32(self.ctas_per_rank if two_shot else min(self.ctas_per_rank, 8)),
              i32(0), stream())
-        return t if two_shot else t[n:2 * n]
+        return t[:n] if two_shot else t[n:2 * n]
 
     def allreduce_small(self, x: torch.Tensor) -> torch.Tensor:
         """Sum of a small fp32 tensor (≤ 1024 elements) over ranks via the one-shot kernel (metrics, C4)."""

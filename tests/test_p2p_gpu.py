@@ -38,8 +38,9 @@ def test_emulated_allreduce_adamw_matches_mean_gradient_adam(world):
                        1e-8, 0.0, step, grad_scale=1.0 / world)
         # every rank's bf16 parameters agree with the oracle, inside the bucket only
         for r in range(world):
+            # bf16 rounding of two fp32 values one ulp apart may differ: allow one bf16 ulp
             torch.testing.assert_close(params[r][off:off + n].float(), want_p[off:off + n].to(torch.bfloat16).float(),
-                                       rtol=0, atol=0, msg=lambda m: f"rank {r} step {step}: {m}")
+                                       rtol=8e-3, atol=1e-6, msg=lambda m: f"rank {r} step {step}: {m}")
             assert torch.equal(params[r][:off], master0[:off].to(torch.bfloat16))
             assert float(grads[r][off:off + n].abs().max()) == 0.0           # bucket cleared
             assert torch.equal(grads[r][:off], keep[r][:off])                # outside untouched
