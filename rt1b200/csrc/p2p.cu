@@ -103,13 +103,27 @@ __global__ void __launch_bounds__(P2P_THREADS) p2p_allreduce_adamw_kernel(P2PCom
   float* m = loc.exp_avg[rank] + off;
   float* v = loc.exp_avg_sq[rank] + off;
   const long nvec = (hi - lo) >> 3;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
-    const long e = lo + (i << 3);
-    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    uint4 raw[P2P_MAX_WORLD];
+  const long tstride = (long)gridDim.x * blockDim.x;
+  // Software-pipelined by one vector: the peers' loads for iteration i+1 are in flight (NVLink round trip
+  // ~2 us) while iteration i does its fp32 optimizer math and pushes parameters.
+  uint4 raw[P2P_MAX_WORLD], nxt[P2P_MAX_WORLD];
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nvec) {
 #pragma unroll
     for (int p = 0; p < P2P_MAX_WORLD; ++p)
-      if (p < W) raw[p] = ld_peer_v4(reinterpret_cast<const bf16*>(c.grad[(rank + p) % W]) + off + e);
+      if (p < W) nxt[p] = ld_peer_v4(reinterpret_cast<const bf16*>(c.grad[(rank + p) % W]) + off + lo + (i << 3));
+  }
+  for (; i < nvec; i += tstride) {
+    const long e = lo + (i << 3);
+    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int p = 0; p < P2P_MAX_WORLD; ++p)
+      if (p < W) raw[p] = nxt[p];
+    if (i + tstride < nvec) {
+#pragma unroll
+      for (int p = 0; p < P2P_MAX_WORLD; ++p)
+        if (p < W) nxt[p] = ld_peer_v4(reinterpret_cast<const bf16*>(c.grad[(rank + p) % W]) + off + lo + ((i + tstride) << 3));
+    }
 #pragma unroll
     for (int p = 0; p < P2P_MAX_WORLD; ++p)
       if (p < W) {
@@ -166,13 +180,30 @@ __global__ void __launch_bounds__(P2P_THREADS) p2p_allreduce_kernel(P2PComm c, i
   const size_t esz = IS_BF16 ? 2 : 4;
   // one-shot: every rank reads all of [0, n) from every peer, so nobody may overwrite the inputs while a peer
   // could still be reading them — the result goes to elements [n, 2n) of the rank's own buffer instead.
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long)gridDim.x * blockDim.x) {
+  const long tstride = (long)gridDim.x * blockDim.x;
+  uint4 nxt[P2P_MAX_WORLD];
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nvec) {
+#pragma unroll
+    for (int p = 0; p < P2P_MAX_WORLD; ++p)
+      if (p < W) nxt[p] = ld_peer_v4(reinterpret_cast<const char*>(c.grad[(rank + p) % W]) + off_bytes + (lo + i * EPV) * esz);
+  }
+  for (; i < nvec; i += tstride) {
     const long e = lo + i * EPV;
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint4 cur[P2P_MAX_WORLD];
+#pragma unroll
+    for (int p = 0; p < P2P_MAX_WORLD; ++p)
+      if (p < W) cur[p] = nxt[p];
+    if (i + tstride < nvec) {   // prefetch the next vector from every peer before reducing this one
+#pragma unroll
+      for (int p = 0; p < P2P_MAX_WORLD; ++p)
+        if (p < W) nxt[p] = ld_peer_v4(reinterpret_cast<const char*>(c.grad[(rank + p) % W]) + off_bytes + (e + tstride * EPV) * esz);
+    }
 #pragma unroll
     for (int p = 0; p < P2P_MAX_WORLD; ++p)
       if (p < W) {
-        const uint4 raw = ld_peer_v4(reinterpret_cast<const char*>(c.grad[(rank + p) % W]) + off_bytes + e * esz);
+        const uint4 raw = cur[p];
         if (IS_BF16) {
           float f[8];
           unpack8(*reinterpret_cast<const bf16x8*>(&raw), f);

@@ -291,6 +291,20 @@ class EfficientNetEncoder(nn.Module):
         self.early_film = early_film
         self._pooling = pooling
 
+    def film_layers(self) -> List[FilmConditioning]:
+        """All FiLM layers in execution order: one per MBConv block (early FiLM), then the final one."""
+        early = list(self.net.films) if (self.early_film and self.net.include_film) else []
+        return early + [self.film_layer]
+
+    def flat_groups(self):
+        # every FiLM projection of the encoder is consumed by ONE GEMM on the sm_100a path:
+        # [gamma|beta for all layers] = context @ _film_w.T + _film_b ; per layer the rows are [add (beta) | mult (gamma)]
+        ws, bs = [], []
+        for f in self.film_layers():
+            ws += [f._projection_add.weight, f._projection_mult.weight]
+            bs += [f._projection_add.bias, f._projection_mult.bias]
+        return {"_film_w": ws, "_film_b": bs}
+
     def forward(self, image: torch.Tensor, context: torch.Tensor) -> torch.Tensor:
         feats = self.net(image, context) if self.early_film else self.net(image)
         feats = self.film_layer(self.conv1x1(feats), context)

@@ -62,9 +62,9 @@ class TF_MultiHeadAttention(nn.Module):
     # one [3*h*dk, d] GEMM on the sm_100a path (see rt1b200.parallel.flat).
     def flat_groups(self):
         if self.value_dim != self.key_dim:
-            return []
-        return [[self.q_linear.weight, self.k_linear.weight, self.v_linear.weight],
-                [self.q_linear.bias, self.k_linear.bias, self.v_linear.bias]]
+            return {}
+        return {"_qkv_w": [self.q_linear.weight, self.k_linear.weight, self.v_linear.weight],
+                "_qkv_b": [self.q_linear.bias, self.k_linear.bias, self.v_linear.bias]}
 
     def _fused_qkv(self):
         w = getattr(self, "_qkv_w", None)
@@ -80,7 +80,7 @@ class TF_MultiHeadAttention(nn.Module):
             wqkv, bqkv = self._fused_qkv()
             x2 = q.reshape(bs * sl, self.d_model)
             if wqkv is not None:
-                qkv = ops.linear(x2, wqkv, bqkv, wgrad=self._qkv_w_grad, bgrad=self._qkv_b_grad,
+                qkv = ops.linear(x2, wqkv, bqkv, wgrad=self._qkv_w_grad, bgrad=getattr(self, "_qkv_b_grad", None),
                                  notify=[self.q_linear.weight, self.k_linear.weight, self.v_linear.weight,
                                          self.q_linear.bias, self.k_linear.bias, self.v_linear.bias])   # [bs*sl, 3*h*dk]
             else:

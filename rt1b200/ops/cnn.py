@@ -87,7 +87,6 @@ def film_efficientnet_forward_torch(encoder, image_nhwc: torch.Tensor, context: 
 def film_efficientnet_forward(encoder, image_nhwc: torch.Tensor, context: torch.Tensor) -> torch.Tensor:
     from . import _lib
     if _lib.available() and os.environ.get("RT1B200_CNN_KERNELS", "1") != "0":
-        from . import kernels
-        if hasattr(kernels, "film_efficientnet_forward"):
-            return kernels.film_efficientnet_forward(encoder, image_nhwc, context)
+        from . import kernels_cnn
+        return kernels_cnn.film_efficientnet_forward(encoder, image_nhwc, context)
     return film_efficientnet_forward_torch(encoder, image_nhwc, context)

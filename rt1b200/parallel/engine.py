@@ -277,6 +277,9 @@ class DataParallelEngine:
     def model_state_dict(self, prefix: str = "") -> Dict[str, torch.Tensor]:
         """fp32 state dict with the model's own keys (master weights substituted for bf16 parameters).
         With the P2P backend call :meth:`gather_sharded_state` on ALL ranks first (it is a collective)."""
+        if self.device.type == "cuda" and _lib.available():
+            from ..ops.kernels_cnn import flush_bn_counters
+            flush_bn_counters(self.model)
         sd = {}
         masters = {s.name: self.flat.view(self.flat.master, s.name) for s in self.flat.slots}
         for k, v in self.model.state_dict().items():

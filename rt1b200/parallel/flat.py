@@ -7,12 +7,17 @@ so that
     "buckets" instead of 572 small per-tensor kernels (the reference pays per-tensor ``foreach`` Adam plus
     DDP's 25 MB bucket copies, SURVEY §2.5 C1 / §2.6 K14);
   * the gradient buffer can live in NVLink-visible symmetric memory and be read by peer GPUs directly;
-  * q/k/v projection weights of an attention layer sit back to back and are consumed as one GEMM operand.
+  * groups of tensors that one kernel consumes together (the q/k/v projections of an attention layer, all 54
+    FiLM projection matrices of the image encoder) sit back to back and are used as ONE GEMM operand.
 
 ``FlatParams`` keeps ``nn.Parameter`` objects (and therefore ``state_dict`` keys, autograd, hooks) intact:
 each ``p.data`` becomes a view into the flat parameter buffer and ``p.grad`` a view into the flat gradient
 buffer.  With ``param_dtype=torch.bfloat16`` the model computes in bf16 while fp32 master weights and the
 Adam moments live here (mixed precision with the master copy owned by the optimizer).
+
+``flat_groups()`` protocol: a module may return ``{attr_name: [params...]}``; the listed parameters are packed
+back to back (no alignment padding between members) and the module receives ``attr_name`` — a view over all of
+them stacked along dim 0 — and ``attr_name + '_grad'``, the same view of the gradient buffer.
 """
 from __future__ import annotations
 
@@ -22,7 +27,7 @@ from typing import Callable, Dict, List, Optional, Tuple
 import torch
 import torch.nn as nn
 
-ALIGN = 64  # elements; keeps every tensor 128-byte aligned in bf16 (TMA/vector-load friendly)
+ALIGN = 64  # elements; every tensor / group starts 128-byte aligned in bf16 (TMA/vector-load friendly)
 
 
 @dataclass
@@ -33,15 +38,22 @@ class Slot:
     shape: torch.Size
 
 
-def _ordered_params(model: nn.Module) -> List[Tuple[str, nn.Parameter]]:
-    """Registration order, except that tensors named in a module's ``flat_groups()`` are made adjacent."""
+def _groups_of(mod) -> Dict[str, List[nn.Parameter]]:
+    fg = getattr(mod, "flat_groups", None)
+    if not callable(fg):
+        return {}
+    groups = fg()
+    return groups if isinstance(groups, dict) else {}
+
+
+def _ordered_params(model: nn.Module) -> List[Tuple[str, nn.Parameter, Optional[int]]]:
+    """(name, param, group id) in registration order, except that members of a group are made adjacent."""
     named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
     by_id = {id(p): n for n, p in named}
     grouped: Dict[int, List[nn.Parameter]] = {}
     for mod in model.modules():
-        fg = getattr(mod, "flat_groups", None)
-        if callable(fg):
-            for group in fg():
+        for group in _groups_of(mod).values():
+            if all(id(p) in by_id and p.numel() % 8 == 0 for p in group):
                 for p in group:
                     grouped[id(p)] = group
     out, done = [], set()
@@ -49,12 +61,13 @@ def _ordered_params(model: nn.Module) -> List[Tuple[str, nn.Parameter]]:
         if id(p) in done:
             continue
         if id(p) in grouped:
-            for q in grouped[id(p)]:
-                if id(q) not in done and id(q) in by_id:
-                    out.append((by_id[id(q)], q))
+            g = grouped[id(p)]
+            for q in g:
+                if id(q) not in done:
+                    out.append((by_id[id(q)], q, id(g)))
                     done.add(id(q))
         else:
-            out.append((n, p))
+            out.append((n, p, None))
             done.add(id(p))
     return out
 
@@ -69,12 +82,18 @@ class FlatParams:
         self.device = torch.device(device) if device is not None else first.device
         self.param_dtype = param_dtype or first.dtype
         self.slots: List[Slot] = []
-        off = 0
-        for name, p in params:
+        self._cuts: List[int] = []        # aligned offsets where a bucket may end (never inside a packed group)
+        off, prev_gid = 0, None
+        for name, p, gid in params:
+            if not (gid is not None and gid == prev_gid):
+                off = (off + ALIGN - 1) // ALIGN * ALIGN
+                self._cuts.append(off)
             self.slots.append(Slot(name, off, p.numel(), p.shape))
-            off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
-        self.numel = off
-        self.params: List[nn.Parameter] = [p for _, p in params]
+            off += p.numel()
+            prev_gid = gid
+        self.numel = (off + ALIGN - 1) // ALIGN * ALIGN
+        self._cuts.append(self.numel)
+        self.params: List[nn.Parameter] = [p for _, p, _ in params]
         self.by_name: Dict[str, Slot] = {s.name: s for s in self.slots}
 
         self.master = torch.zeros(self.numel, dtype=torch.float32, device=self.device)
@@ -102,31 +121,18 @@ class FlatParams:
     def _install_fused_views(self, model: nn.Module):
         ids = {id(p): s for s, p in zip(self.slots, self.params)}
         for mod in model.modules():
-            fg = getattr(mod, "flat_groups", None)
-            if not callable(fg):
-                continue
-            groups = fg()
-            if len(groups) == 2 and all(id(p) in ids for g in groups for p in g):
-                views = []
-                for g in groups:
-                    s0 = ids[id(g[0])]
-                    total = sum(p.numel() for p in g)
-                    contiguous = all(ids[id(g[i + 1])].offset == ids[id(g[i])].offset + g[i].numel()
-                                     for i in range(len(g) - 1))
-                    if not contiguous:
-                        views = []
-                        break
-                    lead = sum(p.shape[0] for p in g)
-                    views.append(self.param[s0.offset:s0.offset + total].view(lead, *g[0].shape[1:]))
-                if views:
-                    mod._qkv_w, mod._qkv_b = views
-                    gviews = []
-                    for g in groups:
-                        s0 = ids[id(g[0])]
-                        total = sum(p.numel() for p in g)
-                        lead = sum(p.shape[0] for p in g)
-                        gviews.append(self.grad[s0.offset:s0.offset + total].view(lead, *g[0].shape[1:]))
-                    mod._qkv_w_grad, mod._qkv_b_grad = gviews
+            for attr, g in _groups_of(mod).items():
+                if not all(id(p) in ids for p in g):
+                    continue
+                contiguous = all(ids[id(g[i + 1])].offset == ids[id(g[i])].offset + g[i].numel()
+                                 for i in range(len(g) - 1))
+                if not contiguous:
+                    continue
+                s0 = ids[id(g[0])]
+                total = sum(p.numel() for p in g)
+                shape = (sum(p.shape[0] for p in g), *g[0].shape[1:])
+                setattr(mod, attr, self.param[s0.offset:s0.offset + total].view(shape))
+                setattr(mod, attr + "_grad", self.grad[s0.offset:s0.offset + total].view(shape))
 
     # -- helpers ---------------------------------------------------------------------------------------
     def rebind_grads(self):
@@ -148,13 +154,13 @@ class FlatParams:
             self.param.copy_(self.master)
 
     def buckets(self, bucket_elems: int) -> List[Tuple[int, int]]:
-        """Contiguous [start, end) element ranges cut at tensor boundaries, each about ``bucket_elems`` long."""
+        """Contiguous [start, end) element ranges cut at aligned tensor/group boundaries, each about
+        ``bucket_elems`` long."""
         out, start = [], 0
-        for s in self.slots:
-            end = s.offset + (s.numel + ALIGN - 1) // ALIGN * ALIGN
-            if end - start >= bucket_elems:
-                out.append((start, end))
-                start = end
+        for cut in self._cuts[1:]:
+            if cut - start >= bucket_elems:
+                out.append((start, cut))
+                start = cut
         if start < self.numel:
             out.append((start, self.numel))
         return out

@@ -58,7 +58,7 @@ class _CommBase:
 class SymmetricComm(_CommBase):
     """One process per GPU.  All ranks must make the same sequence of ``alloc_tensor`` calls."""
 
-    def __init__(self, process_group=None, ctas_per_rank: int = 32):
+    def __init__(self, process_group=None, ctas_per_rank: int = 96):
         super().__init__()
         import torch.distributed as dist
         self.dist, self.group = dist, process_group
@@ -109,7 +109,11 @@ class SymmetricComm(_CommBase):
              _ptr_array(self._param_ptrs), _ptr_array(self._flag_ptrs), one(flat.master), one(flat.exp_avg),
              one(flat.exp_avg_sq), i64(lo), i64(hi - lo), ctypes.c_uint(self._next_epoch()), f32(h["lr"]), f32(h["beta1"]),
              f32(h["beta2"]), f32(h["eps"]), f32(h["weight_decay"]), f32(h["bc1"]), f32(h["bc2"]),
-             i32(self.ctas_per_rank), i32(0), stream())
+             i32(self._ctas_for((hi - lo) * 2 // self.world)), i32(0), stream())
+
+    def _ctas_for(self, bytes_per_rank: int) -> int:
+        """Enough CTAs to keep ~2 MB of peer loads in flight (NVLink latency x bandwidth), never more than asked."""
+        return max(1, min(self.ctas_per_rank, bytes_per_rank // 16384))
 
     def allreduce_(self, t: torch.Tensor, scale: float = 1.0, two_shot: Optional[bool] = None, n: Optional[int] = None):
         """In-place sum over ranks of a tensor allocated by :meth:`alloc_tensor` (bf16 or fp32)."""
@@ -119,8 +123,8 @@ class SymmetricComm(_CommBase):
             two_shot = nbytes >= 256 * 1024
         call("rt1_p2p_allreduce", i32(self.world), i32(self.rank), _ptr_array(t._rt1_peer_ptrs),
              _ptr_array(self._flag_ptrs), i64(0), i64(n), i32(t.dtype == torch.bfloat16), f32(scale), i32(two_shot),
-             ctypes.c_uint(self._next_epoch()), i32(self.ctas_per_rank if two_shot else min(self.ctas_per_rank, 8)),
-             i32(0), stream())
+             ctypes.c_uint(self._next_epoch()),
+             i32(self._ctas_for(nbytes // self.world if two_shot else nbytes)), i32(0), stream())
         return t[:n] if two_shot else t[n:2 * n]
 
     def allreduce_small(self, x: torch.Tensor) -> torch.Tensor:

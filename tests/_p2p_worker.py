@@ -32,7 +32,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
-    comm = SymmetricComm(ctas_per_rank=int(os.environ.get("RT1_P2P_CTAS", "32")))
+    comm = SymmetricComm(ctas_per_rank=int(os.environ.get("RT1_P2P_CTAS", "128")))
 
     # 1. all-reduce, both schedules, both dtypes
     for dtype in (torch.bfloat16, torch.float32):
