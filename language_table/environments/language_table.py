@@ -1,0 +1,190 @@
+"""``LanguageTable``: the single-board environment with the reference's interface
+(``language_table/environments/language_table.py:45``: ``reset / step / render / succeeded / compute_state /
+get_pybullet_state / set_pybullet_state``), on top of the PyBullet-free board in :mod:`rt1b200.envs.board`.
+
+Observation (``:407-416``): ``effector_translation f32[2]``, ``effector_target_translation f32[2]``,
+``instruction int32[512]`` (zero-padded utf-8 bytes), ``rgb uint8[180,320,3]``.  ``compute_state`` adds per-block
+``block_<name>_translation / _orientation / _mask`` entries used by the rewards and oracles.  Rendering is the
+z-buffer rasteriser of :mod:`rt1b200.envs.raster` (CUDA when the board lives on a GPU, numpy otherwise); PyBullet's
+TinyRenderer / GUI paths are unavailable on this box and have no counterpart here.
+"""
+from __future__ import annotations
+
+import collections
+import copy
+from typing import Any, Dict, Optional
+
+import numpy as np
+import torch
+
+from language_table.environments import blocks as blocks_module
+from language_table.environments import constants
+from language_table.environments.rewards import task_info
+
+from rt1b200 import spaces
+from rt1b200.envs.board import BatchedLanguageTable
+
+
+class LanguageTable:
+    metadata = {"render.modes": ["rgb_array"]}
+
+    def __init__(self, block_mode, reward_factory=None, control_frequency=10.0, shared_memory=False, seed=None,
+                 delay_reward_steps=0, render_text_in_image=True, training=True, device="cpu"):
+        if shared_memory:
+            raise NotImplementedError("the PyBullet GUI / shared-memory visualiser is unavailable on this box")
+        self._block_mode = blocks_module.LanguageTableBlockVariants(block_mode) if isinstance(block_mode, str) else block_mode
+        self._training = training
+        self._rng = np.random.RandomState(seed=seed)
+        self._control_frequency = control_frequency
+        self._render_text_in_image = render_text_in_image
+        self._board = BatchedLanguageTable(1, self._block_mode if self._block_mode in (
+            blocks_module.LanguageTableBlockVariants.BLOCK_1, blocks_module.LanguageTableBlockVariants.BLOCK_4,
+            blocks_module.LanguageTableBlockVariants.BLOCK_8, blocks_module.LanguageTableBlockVariants.N_CHOOSE_K)
+            else blocks_module.LanguageTableBlockVariants.BLOCK_8, device=device, seed=seed or 0, max_episode_steps=10 ** 9)
+        self._all_blocks = self._board.block_names
+        self._blocks_on_table = list(self._all_blocks)
+        self._reward_calculator = None
+        if reward_factory is not None:
+            self._reward_calculator = reward_factory(goal_reward=100.0, rng=self._rng, delay_reward_steps=delay_reward_steps,
+                                                     block_mode=self._block_mode)
+        self._instruction = np.zeros(constants.INSTRUCTION_LENGTH, np.int32)
+        self._instruction_str = None
+        self._task_info = None
+        self.action_space = spaces.Box(low=-0.1, high=0.1, shape=(2,), dtype=np.float32)
+        self.observation_space = spaces.Dict(collections.OrderedDict(
+            effector_translation=spaces.Box(low=constants.WORKSPACE_BOUNDS[0] - 0.1, high=constants.WORKSPACE_BOUNDS[1] + 0.1),
+            effector_target_translation=spaces.Box(low=constants.WORKSPACE_BOUNDS[0] - 0.1, high=constants.WORKSPACE_BOUNDS[1] + 0.1),
+            instruction=spaces.Box(low=0, high=2147483647, shape=(constants.INSTRUCTION_LENGTH,), dtype=np.int32),
+            rgb=spaces.Box(low=0, high=255, shape=(constants.IMAGE_HEIGHT, constants.IMAGE_WIDTH, 3), dtype=np.uint8)))
+
+    # ------------------------------------------------------------------------------------------- helpers
+    @staticmethod
+    def encode_instruction(instruction: str) -> np.ndarray:
+        raw = np.frombuffer(instruction.encode("utf-8"), dtype=np.uint8).astype(np.int32)[:constants.INSTRUCTION_LENGTH]
+        out = np.zeros(constants.INSTRUCTION_LENGTH, np.int32)
+        out[:len(raw)] = raw
+        return out
+
+    @staticmethod
+    def decode_instruction(bytes_array) -> str:
+        arr = np.asarray(bytes_array).astype(np.uint8)
+        return bytes(arr[arr != 0].tolist()).decode("utf-8")
+
+    def seed(self, seed=None):
+        self._rng = np.random.RandomState(seed=seed)
+        if self._reward_calculator is not None:
+            self._reward_calculator.seed(self._rng)
+
+    @property
+    def succeeded(self) -> bool:
+        if self._reward_calculator is None:
+            return bool(self._board.succeeded[0])
+        return bool(self._reward_calculator.reward(self._compute_state(request_task_update=False))[1])
+
+    @property
+    def instruction_str(self):
+        return self._instruction_str
+
+    def get_control_frequency(self):
+        return self._control_frequency
+
+    # ----------------------------------------------------------------------------------------- state / obs
+    def _compute_state(self, request_task_update=True) -> Dict[str, Any]:
+        b = self._board
+        st = collections.OrderedDict(
+            effector_translation=b.effector[0].cpu().numpy().astype(np.float32),
+            effector_target_translation=b.effector_target[0].cpu().numpy().astype(np.float32),
+            instruction=self._instruction)
+        xy, yaw, mask = b.block_xy[0].cpu().numpy(), b.block_yaw[0].cpu().numpy(), b.block_mask[0].cpu().numpy()
+        for i, name in enumerate(self._all_blocks):
+            st["block_%s_translation" % name] = xy[i].astype(np.float32)
+            st["block_%s_orientation" % name] = np.array([yaw[i]], np.float32)
+            st["block_%s_mask" % name] = np.array([1.0 if mask[i] else 0.0], np.float32)
+        return st
+
+    def compute_state(self, request_task_update=True):
+        st = self._compute_state(request_task_update)
+        st["rgb"] = self._render_camera()
+        return st
+
+    def _compute_observation(self, state=None):
+        st = state or self.compute_state()
+        return collections.OrderedDict((k, st[k]) for k in ("effector_translation", "effector_target_translation",
+                                                              "instruction", "rgb"))
+
+    def _render_camera(self) -> np.ndarray:
+        return self._board.render()[0].cpu().numpy()
+
+    def render(self, mode="rgb_array"):
+        frame = self._render_camera()
+        if self._render_text_in_image and self._instruction_str:
+            try:
+                import cv2
+                frame = np.ascontiguousarray(frame)
+                cv2.putText(frame, self._instruction_str[:60], (4, 12), cv2.FONT_HERSHEY_SIMPLEX, 0.35, (0, 0, 0), 1, cv2.LINE_AA)
+            except Exception:
+                pass
+        return frame
+
+    # -------------------------------------------------------------------------------------- reset / step
+    def reset(self, reset_poses=True):
+        for _ in range(100):
+            if reset_poses:
+                subsets = blocks_module.get_all_block_subsets(self._block_mode, self._training) \
+                    if self._block_mode == blocks_module.LanguageTableBlockVariants.N_CHOOSE_K else None
+                self._board.gen.manual_seed(int(self._rng.randint(2 ** 31 - 1)))
+                self._board.reset()
+                if subsets is not None:
+                    chosen = set(subsets[int(self._rng.randint(len(subsets)))])
+                    self._board.block_mask[0] = torch.tensor([n in chosen for n in self._all_blocks])
+                    # absent blocks are parked far off the board
+                    self._board.block_xy[0][~self._board.block_mask[0]] = torch.tensor([5.0, 5.0])
+                self._blocks_on_table = [n for n, m in zip(self._all_blocks, self._board.block_mask[0].tolist()) if m]
+            state = self._compute_state()
+            if self._reward_calculator is None:
+                self._set_instruction("")
+                break
+            info = self._reward_calculator.reset(state, self._blocks_on_table)
+            if info != task_info.FAILURE:
+                self._task_info = info
+                self._set_instruction(info.instruction)
+                break
+        else:
+            raise ValueError("could not sample a valid task for this board")
+        return self._compute_observation()
+
+    def _set_instruction(self, text: str):
+        self._instruction_str = text
+        self._instruction = self.encode_instruction(text)
+
+    def step(self, action):
+        action = torch.as_tensor(np.asarray(action, np.float32)).reshape(1, 2)
+        self._board.step(action)
+        state = self._compute_state()
+        reward, done = (0.0, False)
+        if self._reward_calculator is not None:
+            reward, done = self._reward_calculator.reward(state)
+        state["rgb"] = self._render_camera()
+        return self._compute_observation(state), reward, done, {}
+
+    # ------------------------------------------------------------------------------------ save / restore
+    def get_pybullet_state(self):
+        """Full board state (name kept from the reference, ``:234-300``); nothing Bullet-specific is inside."""
+        b = self._board
+        return {"effector": b.effector.clone(), "effector_target": b.effector_target.clone(), "block_xy": b.block_xy.clone(),
+                "block_yaw": b.block_yaw.clone(), "block_mask": b.block_mask.clone(), "instruction": self._instruction.copy(),
+                "instruction_str": self._instruction_str, "blocks_on_table": list(self._blocks_on_table),
+                "reward": copy.deepcopy(self._reward_calculator), "task_info": copy.deepcopy(self._task_info)}
+
+    def set_pybullet_state(self, state):
+        b = self._board
+        b.effector, b.effector_target = state["effector"].clone(), state["effector_target"].clone()
+        b.block_xy, b.block_yaw, b.block_mask = state["block_xy"].clone(), state["block_yaw"].clone(), state["block_mask"].clone()
+        self._instruction, self._instruction_str = state["instruction"].copy(), state["instruction_str"]
+        self._blocks_on_table = list(state["blocks_on_table"])
+        if state.get("reward") is not None:
+            self._reward_calculator = copy.deepcopy(state["reward"])
+            self._reward_calculator.seed(self._rng)
+        self._task_info = copy.deepcopy(state.get("task_info"))
+
+    get_board_state, set_board_state = get_pybullet_state, set_pybullet_state

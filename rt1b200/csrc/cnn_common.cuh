@@ -48,7 +48,7 @@ __device__ __forceinline__ void cta_rows(int HW, int& begin, int& end) {
 }
 static inline int cnn_ctas_per_frame(int N, int HW, int C) {
   // aim for >= ~4 CTAs per SM overall, but keep at least 32 rows per CTA
-  int want = (148 * 4 + N - 1) / N;
+  int want = (148 * 8 + N - 1) / N;
   int maxc = (HW + 31) / 32;
   if (want > maxc) want = maxc;
   if (want < 1) want = 1;

@@ -280,7 +280,7 @@ __global__ void dw_wgrad_cast_kernel(const float* __restrict__ scratch, bf16* __
 }
 
 static int dw_items_ctas(int N, int items) {
-  int want = (148 * 4 + N - 1) / N;
+  int want = (148 * 8 + N - 1) / N;
   int maxc = (items + 15) / 16;
   if (want > maxc) want = maxc;
   return want < 1 ? 1 : want;

@@ -49,13 +49,16 @@ __host__ __device__ inline int b_tile_bytes(int block_n, int b_mn) {
   return b_mn ? ((block_n + 63) / 64) * (BLOCK_K * 128) : block_n * 128;
 }
 
-__global__ void __launch_bounds__(128) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
+__global__ void __launch_bounds__(128, 8) gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                            const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // dynamic smem base is only guaranteed 16B-aligned by the ABI: align up to 1024 (swizzle-128B atom)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BLOCK_M, n0 = blockIdx.y * p.block_n;
+  // 1-D grid over (m-tile, n-tile) with the n-tile index fastest: the CTAs that share an A tile run back to back,
+  // so A is fetched from HBM once and re-read from L2
+  const int n_tiles = (p.N + p.block_n - 1) / p.block_n;
+  const int m0 = (blockIdx.x / n_tiles) * BLOCK_M, n0 = (blockIdx.x % n_tiles) * p.block_n;
   const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
   const int kb_begin = blockIdx.z * p.kb_per_split;
   const int kb_end = min(total_kb, kb_begin + p.kb_per_split);
@@ -146,51 +149,65 @@ __global__ void __launch_bounds__(128) gemm_tcgen05_kernel(const __grid_constant
   const float keep_scale = p.dropout_p > 0.f ? 1.f / (1.f - p.dropout_p) : 1.f;
   float* stat_sm = reinterpret_cast<float*>(smem);  // operand stages are dead once tmem_full fired
 
-  for (int c0 = 0; c0 < p.block_n; c0 += 32) {
-    const int width = min(32, p.block_n - c0);
-    uint32_t acc[32];
+  // 16 accumulator columns at a time: keeps the kernel at <= 64 registers/thread so 8 CTAs fit on an SM
+  // (with 32-column chunks ptxas used 128 registers → 4 CTAs/SM and the epilogue latency was exposed).
+  for (int c0 = 0; c0 < p.block_n; c0 += 16) {
+    uint32_t acc[16];
     if (num_kb > 0) {
-      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0;
-      if (width == 32) tmem_ld_32x32(taddr, acc);
-      else tmem_ld_32x16(taddr, acc);
+      tmem_ld_32x16(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, acc);
       tmem_ld_wait();
     } else {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) acc[j] = 0u;
+      for (int j = 0; j < 16; ++j) acc[j] = 0u;
     }
-    float v[32];
+    float v[16];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
+    for (int j = 0; j < 16; ++j) {
       const int col = n0 + c0 + j;
       float x = __uint_as_float(acc[j]) * p.alpha;
-      if (p.bias != nullptr && col < p.N && j < width) x += __bfloat162float(p.bias[col]);
+      if (p.bias != nullptr && col < p.N) x += __bfloat162float(p.bias[col]);
       v[j] = x;
     }
     if (p.col_sum != nullptr) {
-      // per-column sum / sum-of-squares over the 128 rows of this tile: transpose through shared memory so
-      // each lane reduces one column, then one atomic per column per CTA
+      // per-column sum / sum-of-squares over the 128 rows of this tile: transpose through shared memory
+      // (17-float pitch: conflict-free), 8 row-groups x 16 columns reduce in parallel, then 16 threads fold the
+      // partials and issue one atomic pair per column per CTA
       __syncthreads();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) stat_sm[(warp * 32 + lane) * 33 + j] = (row_ok && j < width) ? v[j] : 0.f;
+      for (int j = 0; j < 16; ++j) stat_sm[threadIdx.x * 17 + j] = row_ok ? v[j] : 0.f;
       __syncthreads();
-      if (warp == 0) {
+      {
+        const int col_l = threadIdx.x & 15, grp = threadIdx.x >> 4;  // 8 groups of 16 rows
         float s = 0.f, q = 0.f;
-        for (int r = 0; r < 128; ++r) {
-          const float t = stat_sm[r * 33 + lane];
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          const float t = stat_sm[(grp * 16 + r) * 17 + col_l];
           s += t;
-          q += t * t;
+          q = fmaf(t, t, q);
         }
-        const int col = n0 + c0 + lane;
-        if (lane < width && col < p.N) {
-          atomicAdd(p.col_sum + col, s);
-          atomicAdd(p.col_sumsq + col, q);
+        float* part = stat_sm + 128 * 17;
+        part[grp * 32 + col_l] = s;
+        part[grp * 32 + 16 + col_l] = q;
+        __syncthreads();
+        if (threadIdx.x < 16) {
+          s = q = 0.f;
+#pragma unroll
+          for (int g8 = 0; g8 < 8; ++g8) {
+            s += part[g8 * 32 + threadIdx.x];
+            q += part[g8 * 32 + 16 + threadIdx.x];
+          }
+          const int col = n0 + c0 + threadIdx.x;
+          if (col < p.N) {
+            atomicAdd(p.col_sum + col, s);
+            atomicAdd(p.col_sumsq + col, q);
+          }
         }
       }
     }
     if (!row_ok) continue;
     if (p.dropout_p > 0.f) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
+      for (int j = 0; j < 16; ++j) {
         const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c0 + j));
         v[j] = rt1_hash_u32(idx, p.seed) >= thresh ? v[j] * keep_scale : 0.f;
       }
@@ -198,8 +215,7 @@ __global__ void __launch_bounds__(128) gemm_tcgen05_kernel(const __grid_constant
     if (p.residual != nullptr) {
       const bf16* rr = p.residual + (long)row * p.ldr + n0 + c0;
 #pragma unroll
-      for (int j8 = 0; j8 < 32; j8 += 8) {
-        if (j8 >= width) break;
+      for (int j8 = 0; j8 < 16; j8 += 8) {
         const int col = n0 + c0 + j8;
         if (col + 8 <= p.N && ((reinterpret_cast<uintptr_t>(rr + j8) & 15) == 0)) {
           float r8[8];
@@ -216,8 +232,8 @@ __global__ void __launch_bounds__(128) gemm_tcgen05_kernel(const __grid_constant
     if (p.out_fp32) {
       float* o = reinterpret_cast<float*>(p.out) + (long)row * p.ldo + n0 + c0;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (j < width && n0 + c0 + j < p.N) {
+      for (int j = 0; j < 16; ++j) {
+        if (n0 + c0 + j < p.N) {
           if (p.atomic_out) atomicAdd(o + j, v[j]);
           else o[j] = v[j];
         }
@@ -225,8 +241,7 @@ __global__ void __launch_bounds__(128) gemm_tcgen05_kernel(const __grid_constant
     } else {
       bf16* o = reinterpret_cast<bf16*>(p.out) + (long)row * p.ldo + n0 + c0;
 #pragma unroll
-      for (int j8 = 0; j8 < 32; j8 += 8) {
-        if (j8 >= width) break;
+      for (int j8 = 0; j8 < 16; j8 += 8) {
         const int col = n0 + c0 + j8;
         if (col + 8 <= p.N && ((reinterpret_cast<uintptr_t>(o + j8) & 15) == 0)) {
           *reinterpret_cast<bf16x8*>(o + j8) = pack8(v + j8);
@@ -297,7 +312,16 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   GemmParams p;
   p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn;
   // tile width: whole N when it fits in one UMMA (<= 256), else 128 — rounded up to the UMMA N granule of 16
-  int bn = N <= 256 ? ((N + 15) / 16) * 16 : 128;
+  // Tile width: at most 64 accumulator columns per CTA.  These GEMMs are short-K and memory-bound; what hides
+  // the TMA → MMA → epilogue latency of a tile is the number of CTAs resident per SM, and TMEM allows
+  // 512 / (allocated columns) of them — 64 columns → 8 CTAs/SM (a 144-wide tile would allocate 256 → 2 CTAs/SM,
+  // measured 9x slower).  A is re-read N/64 times, from L2.
+  int bn;
+  if (N <= 64) bn = ((N + 15) / 16) * 16;
+  else {
+    const int parts = (N + 63) / 64;
+    bn = (((N + parts - 1) / parts) + 15) / 16 * 16;
+  }
   p.block_n = bn;
   const int total_kb = (K + BLOCK_K - 1) / BLOCK_K;
   p.kb_per_split = (total_kb + split_k - 1) / split_k;
@@ -306,7 +330,7 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   int stages = p.kb_per_split < 4 ? p.kb_per_split : 4;
   if (stages < 1) stages = 1;
   // the column-statistics epilogue reuses the operand stages as a 128 x 33 fp32 transpose buffer
-  while (col_sum != nullptr && stages * stage_bytes < 128 * 33 * 4) ++stages;
+  while (col_sum != nullptr && stages * stage_bytes < (128 * 17 + 256) * 4) ++stages;
   p.stages = stages;
   p.out = out; p.ldo = ldo; p.out_fp32 = out_fp32; p.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
   p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
@@ -328,7 +352,7 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
     RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  dim3 grid((M + BLOCK_M - 1) / BLOCK_M, (N + bn - 1) / bn, splits);
+  dim3 grid(((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn), 1, splits);
   gemm_tcgen05_kernel<<<grid, 128, smem, stream>>>(ta, tb, p);
   return rt1_check_launch("rt1_gemm_bf16");
 }

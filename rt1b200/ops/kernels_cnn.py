@@ -60,7 +60,7 @@ def _wgrad_gemm(g: torch.Tensor, x: torch.Tensor, param: torch.nn.Parameter, n_o
     """param.grad[n_out, k_out] = g[m_red, n_out]^T @ x[m_red, k_out] — both operands read as MN-major views.
     Short outputs with a long reduction (1x1 convs over ~1M pixels) use split-K into an fp32 scratch."""
     slot = _grad_slot(param)
-    tiles = ((n_out + 127) // 128) * (1 if k_out <= 256 else (k_out + 127) // 128)
+    tiles = ((n_out + 127) // 128) * ((k_out + 63) // 64)
     kb = (m_red + 63) // 64
     split = 1
     if tiles < 148 and kb >= 16:
@@ -137,8 +137,13 @@ class _EncoderFn(Function):
                 gemm(x.view(M, Cin), _conv_w2d(blk.expand[0]), e_raw.view(M, Ce), M, Ce, Cin,
                      col_sum=bn1.sum if training else None, col_sumsq=bn1.sumsq if training else None)
                 bn1.finalize(M, training)
-                dw_in, a_in, b_in = e_raw, bn1.a, bn1.b
-                st["e_raw"], st["bn1"] = e_raw, bn1
+                # the depthwise window re-reads every input k*k/stride^2 times: activating on load would make the
+                # kernel MUFU-bound, so SiLU(BN1(.)) is materialised once (one extra read+write of the tensor)
+                e_act = _empty(N, Hc, Wc, Ce, device=dev)
+                call("rt1_bn_act_scale", ptr(e_raw), ptr(bn1.a), ptr(bn1.b), ptr(None), ptr(e_act), i32(N), i32(Hc * Wc), i32(Ce),
+                     i32(1), stream())
+                dw_in, a_in, b_in = e_act, None, None
+                st["e_raw"], st["e_act"], st["bn1"] = e_raw, e_act, bn1
             else:
                 dw_in, a_in, b_in = x, None, None
             pad = (k - 1) // 2
@@ -292,9 +297,9 @@ class _EncoderFn(Function):
             # depthwise conv
             dwc = blk.depthwise[0]
             has_exp = blk.expand is not None
-            dw_in = st["e_raw"] if has_exp else x_in
+            dw_in = st["e_act"] if has_exp else x_in
             scratch = _empty(k * k * Ce, device=dev, dtype=F32)
-            call("rt1_dwconv_wgrad", ptr(dd_raw), ptr(dw_in), ptr(bn1.a if has_exp else None), ptr(bn1.b if has_exp else None),
+            call("rt1_dwconv_wgrad", ptr(dd_raw), ptr(dw_in), ptr(None), ptr(None),
                  ptr(scratch), ptr(_grad_slot(dwc.weight)), i32(N), i32(Hin), i32(Win), i32(Ce), i32(k), i32(s), stream())
             ready.append(dwc.weight)
             dhe = _empty(Mi, Ce, device=dev)
