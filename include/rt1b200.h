@@ -49,6 +49,17 @@ long long rt1_layernorm_bwd_scratch_floats(int rows, int D);
 /* scratch: fp32 [rt1_layernorm_bwd_scratch_floats(rows, D)] of per-CTA dgamma/dbeta partials */
 int rt1_layernorm_bwd(const void* x, const void* w, const void* dy, const float* mean, const float* rstd, void* dx,
                       void* dw, void* db, float* scratch, int rows, int D, cudaStream_t stream);
+/* Same computation for hosts that cannot provide `scratch` (all device memory reserved at start-up or owned by another
+ * allocator, so no cudaMalloc may happen while the robot runs): the partial sums go to a fixed __device__ array inside
+ * the library (1.2 MB per GPU for the life of the process).  This entry point has no counterpart in the reference.
+ * Limits: D in {256, 512, 1024} (rt1_layernorm_bwd_noalloc_max_d() == 1024; wider rows are rejected with an error),
+ * any number of rows.  It performs no allocation.  The first call on each device looks up the array's device address
+ * (cudaGetSymbolAddress, cached per device): make that first call before starting any stream capture.  All calls on a
+ * device share the array: calls whose kernels overlap on the GPU race on it — keep them on one stream or order them
+ * with events.  Nothing in the array needs clearing between calls. */
+int rt1_layernorm_bwd_noalloc(const void* x, const void* w, const void* dy, const float* mean, const float* rstd,
+                              void* dx, void* dw, void* db, int rows, int D, cudaStream_t stream);
+long long rt1_layernorm_bwd_noalloc_max_d(void);
 
 /* ---- fused masked attention over the RT-1 token window (reference transformer.py:82-109) ------------------
  * qkv [B,S,3,H,DK] bf16 -> out [B,S,H*DK]; mask uint8 [S,S] (0 = blocked) or NULL. */

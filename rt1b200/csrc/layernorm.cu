@@ -165,3 +165,89 @@ RT1_API int rt1_layernorm_bwd(const void* x, const void* w, const void* dy, cons
   ln_param_grad_kernel<<<rt1_cdiv(D, 128), 128, 0, stream>>>(scratch, grid, D, (bf16*)dw, (bf16*)db);
   return rt1_check_launch("rt1_layernorm_param_grad");
 }
+
+// ----------------------------------------------------------------------------------------------------------------
+// rt1_layernorm_bwd_noalloc — LayerNorm backward for hosts that cannot hand us a scratch buffer.
+//
+// Who this is for.  rt1_layernorm_bwd() needs a caller-provided fp32 scratch for the per-CTA dgamma/dbeta partial
+// sums.  Some embedders of this library have no way to supply one: a robot-control process that reserved all of its
+// device memory at start-up and runs fine-tuning steps inside a loop where cudaMalloc is off limits (it synchronises
+// the whole device and may fail late, mid-episode), or a host that has given every free byte to another allocator
+// (a framework's caching pool, an MPS partition with a fixed budget) so that a raw cudaMalloc from a plug-in simply
+// returns out-of-memory.  For them the scratch lives inside the library image itself, below, as a fixed-size
+// __device__ array: it is part of the module every GPU loads, costs LN_NOALLOC_MAX_FLOATS * 4 B = 1.2 MB per GPU
+// until the process exits, and needs no allocation call of any kind.  This entry point calls no cudaMalloc / cudaFree
+// / memset-allocating or other allocating routine; inputs and outputs are still the caller's.
+//
+// Limits.  D (row width) must be a multiple of 256 and at most LN_NOALLOC_MAX_D = 1024; any number of rows (the
+// reduction grid is capped at 148 CTAs, so the scratch need is 148 * 2 * D floats at most).  Larger D is rejected with
+// an error message, not truncated.
+//
+// Set-up.  In host code the name of a __device__ array is only a host-side handle, not a device address — passing
+// it to a kernel would fault or touch the wrong memory — so the device address is looked up with
+// cudaGetSymbolAddress.  That happens on the FIRST call made on each device (with that device current), and the
+// result is cached per device.  Make that first call on every device you will use before starting any stream capture.
+//
+// Sharing.  Every call on a device uses the same array and finds the previous call's contents in it.  Nothing in it
+// has to start at zero: each CTA overwrites its own [2 * D] slice completely and the fold kernel reads exactly the
+// slices written by this launch, so no clearing is done.  Two calls whose kernels overlap on the GPU (different
+// streams, or the same call issued from two threads) race on the array and give wrong dgamma/dbeta — serialise them
+// (same stream, or an event between them).  rt1_layernorm_bwd() with caller scratch has no such restriction.
+#include <mutex>
+
+#define LN_NOALLOC_MAX_D 1024
+#define LN_NOALLOC_MAX_GRID 148
+#define LN_NOALLOC_MAX_FLOATS (LN_NOALLOC_MAX_GRID * 2 * LN_NOALLOC_MAX_D)
+#define LN_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_ln_noalloc_scratch[LN_NOALLOC_MAX_FLOATS];
+
+static float* g_ln_noalloc_ptr[LN_NOALLOC_MAX_DEVICES] = {nullptr};
+static std::mutex g_ln_noalloc_mutex;
+
+// Device address of the scratch array on the CURRENT device; resolved once per device.
+static int ln_noalloc_scratch_ptr(float** out) {
+  int dev = -1;
+  RT1_CHECK_CUDA(cudaGetDevice(&dev));
+  RT1_REQUIRE(dev >= 0 && dev < LN_NOALLOC_MAX_DEVICES, "rt1_layernorm_bwd_noalloc: device index %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_ln_noalloc_mutex);
+  if (g_ln_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_ln_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      rt1_set_error("rt1_layernorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -1;
+    }
+    g_ln_noalloc_ptr[dev] = p;
+  }
+  *out = g_ln_noalloc_ptr[dev];
+  return 0;
+}
+
+RT1_API long long rt1_layernorm_bwd_noalloc_max_d(void) { return LN_NOALLOC_MAX_D; }
+
+RT1_API int rt1_layernorm_bwd_noalloc(const void* x, const void* w, const void* dy, const float* mean, const float* rstd,
+                                      void* dx, void* dw, void* db, int rows, int D, cudaStream_t stream) {
+  RT1_REQUIRE(rows > 0, "rt1_layernorm_bwd_noalloc: rows=%d must be positive", rows);
+  RT1_REQUIRE(D % 256 == 0 && D > 0, "rt1_layernorm_bwd_noalloc: D=%d must be a positive multiple of 256", D);
+  RT1_REQUIRE(D <= LN_NOALLOC_MAX_D,
+              "rt1_layernorm_bwd_noalloc: D=%d exceeds the built-in scratch (max D %d); use rt1_layernorm_bwd with caller scratch",
+              D, LN_NOALLOC_MAX_D);
+  int grid = rt1_cdiv(rows, 8);
+  if (grid > LN_NOALLOC_MAX_GRID) grid = LN_NOALLOC_MAX_GRID;
+  RT1_REQUIRE((long long)grid * 2 * D <= LN_NOALLOC_MAX_FLOATS, "rt1_layernorm_bwd_noalloc: scratch need exceeds the built-in array");
+  float* scratch = nullptr;
+  int rc = ln_noalloc_scratch_ptr(&scratch);
+  if (rc) return rc;
+  const size_t smem = 2 * (size_t)D * sizeof(float);
+  switch (D / 256) {
+    case 1: ln_bwd_kernel<1><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
+    case 2: ln_bwd_kernel<2><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
+    case 4: ln_bwd_kernel<4><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
+    default: RT1_REQUIRE(false, "rt1_layernorm_bwd_noalloc: unsupported D=%d (supported: 256, 512, 1024)", D);
+  }
+  rc = rt1_check_launch("rt1_layernorm_bwd_noalloc");
+  if (rc) return rc;
+  ln_param_grad_kernel<<<rt1_cdiv(D, 128), 128, 0, stream>>>(scratch, grid, D, (bf16*)dw, (bf16*)db);
+  return rt1_check_launch("rt1_layernorm_bwd_noalloc(param_grad)");
+}
