@@ -97,6 +97,37 @@ int rt1_fused_adamw(void* param_bf16, float* master, void* grad, int grad_is_bf1
                     long long n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
                     float bias_corr2, float grad_scale, int zero_grad, cudaStream_t stream);
 
+/* ---- NVLink / NVSwitch collectives fused with the optimizer (replaces DDP + NCCL all-reduce + Adam,
+ *      reference distribute_train.py:99-110,231-238) ------------------------------------------------------------
+ * Symmetric buffers: every rank allocates the same sizes in the same order and maps every peer's allocation
+ * (rt1_symm_alloc / rt1_symm_open exchange cudaIpc handles; any allocator that yields peer-mapped pointers — and,
+ * for NVLS, a multicast alias — can be used instead).  `grad`, `param`, `flags`, `buf` are HOST arrays of `world`
+ * device pointers indexed by rank; `flags` entries are zero-initialised pads of rt1_p2p_flag_words() uint32.
+ * `epoch` must increase by one per collective, identically on all ranks. */
+int rt1_symm_alloc(long long bytes, void** ptr, unsigned char* handle64);
+int rt1_symm_open(const unsigned char* handle64, void** ptr);
+int rt1_symm_close(void* ptr);
+int rt1_symm_free(void* ptr);
+int rt1_p2p_flag_words(void);
+/* One kernel per bucket [offset, offset+n) of the flat buffers: ready barrier, reduce-scatter (P2P pulls, or
+ * multimem.ld_reduce when mc_grad/mc_param are non-null), 1/world scale, AdamW on the rank's fp32 shard, all-gather of
+ * the bf16 parameters (P2P pushes or multimem.st), done barrier, gradient bucket cleared.  master/exp_avg/exp_avg_sq
+ * are host arrays of device pointers of which only [rank] is read (all of them with emulate_all_ranks = 1, the
+ * single-GPU test mode that plays every rank in one launch).  Buckets of one step chain: [prev_offset, +prev_n) is the
+ * bucket of the previous call (0 = none), cleared here after this call's opening barrier; final = 1 on the last bucket
+ * of the step runs the closing barrier and clears this bucket too.  A lone call passes prev_n = 0, final = 1. */
+int rt1_p2p_allreduce_adamw(int world, int rank, void* const* grad, void* const* param, void* const* flags,
+                            float* const* master, float* const* exp_avg, float* const* exp_avg_sq, void* mc_grad,
+                            void* mc_param, long long offset, long long n, long long prev_offset, long long prev_n,
+                            int final, unsigned epoch, float lr, float beta1, float beta2, float eps, float weight_decay,
+                            float bias_corr1, float bias_corr2, int ctas_per_rank, int emulate_all_ranks,
+                            cudaStream_t stream);
+/* In-place sum * scale of n elements (bf16 or fp32).  algo 0 = one-shot (result lands in elements [n, 2n) of the
+ * rank's own buffer), 1 = two-shot P2P, 2 = NVLS (needs mc_buf, the multicast alias of buf). */
+int rt1_p2p_allreduce(int world, int rank, void* const* buf, void* const* flags, void* mc_buf, long long offset_bytes,
+                      long long n, int is_bf16, float scale, int algo, unsigned epoch, int ctas_per_rank,
+                      int emulate_all_ranks, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

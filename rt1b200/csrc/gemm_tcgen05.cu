@@ -16,6 +16,8 @@
 //   warps 0-3       : epilogue       — tcgen05.ld 32x32b (thread ↔ accumulator row), fused bias / dropout /
 //                                       residual / scale, bf16 or fp32 stores, or fp32 atomics for split-K
 // Partial tiles need no special code on the load side: TMA zero-fills out-of-bounds box elements.
+#include <stdlib.h>
+
 #include "sm100.cuh"
 
 using namespace sm100;
@@ -259,6 +261,269 @@ __global__ void __launch_bounds__(128, 8) gemm_tcgen05_kernel(const __grid_const
   if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
+// =================================================================================================================
+// Persistent variant for bf16 outputs (every forward and data-gradient GEMM of the model — the ones that move the
+// activation bytes).  The tile-per-CTA kernel above wrote each accumulator row straight from registers: a warp's
+// store instruction touched 32 different rows, i.e. 32 partially filled sectors, and ncu showed the 1x1-conv GEMMs at
+// 5-8 % of DRAM bandwidth with the LSU/L2 write path saturated.  Here:
+//   * one CTA per SM walks the (m-tile, n-tile) list; operand stages form ONE ring across tiles, so the TMA loads of
+//     the next tiles are in flight while the current tile is multiplied and the previous ones are written out;
+//   * two TMEM accumulators (2 x BLOCK_N columns): the MMA of tile i+1 overlaps the epilogue of tile i;
+//   * two epilogue warpgroups (4 warps each = the 4 TMEM lane quadrants) alternate tiles: tcgen05.ld → bias / alpha /
+//     dropout / residual → bf16 → 128B-swizzled staging tile in shared memory → ONE TMA store per 64-column slab
+//     (full 128-byte lines to L2, partial tiles clipped by the tensor map);
+//   * BatchNorm column statistics are taken from the staged bf16 tile (the values the consumer will actually read),
+//     accumulated per CTA in shared memory and flushed with one atomic per column per CTA at the end.
+// Warp roles: 0 = TMA producer, 1 = MMA issuer (+ TMEM alloc), 2-5 = epilogue group 0, 6-9 = epilogue group 1.
+constexpr int V2_THREADS = 320;
+constexpr int V2_EPI_THREADS = 128;
+constexpr int V2_STAGE_TILE_BYTES = BLOCK_M * 128;   // one 64-column bf16 slab of the staging tile (128B rows)
+
+struct GemmV2Smem {   // byte offsets from the 1024-aligned base
+  int stage0, staging, stats, bias, bars, total;
+};
+__host__ __device__ inline GemmV2Smem v2_smem_layout(int stages, int stage_bytes, int n_stats) {
+  GemmV2Smem L;
+  L.stage0 = 0;
+  L.staging = stages * stage_bytes;                          // 2 groups x 2 slabs x 16 KiB
+  L.stats = L.staging + 2 * 2 * V2_STAGE_TILE_BYTES;         // 2 x n_stats floats
+  L.bias = L.stats + 2 * n_stats * 4;                        // 2 groups x 128 floats
+  L.bars = (L.bias + 2 * 128 * 4 + 7) & ~7;                  // full[stages], empty[stages], tmem_full[2], tmem_empty[2], slot
+  L.total = L.bars + (2 * stages + 4) * 8 + 16;
+  return L;
+}
+
+__global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a,
+                                                                              const __grid_constant__ CUtensorMap tma_b,
+                                                                              const __grid_constant__ CUtensorMap tma_o,
+                                                                              const GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tiles = (p.N + p.block_n - 1) / p.block_n;
+  const int m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
+  const int num_tiles = n_tiles * m_tiles;
+  const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int b_bytes = b_tile_bytes(p.block_n, p.b_mn);
+  const int stage_bytes = A_TILE_BYTES + b_bytes;
+  const int n_stats = p.col_sum != nullptr ? ((p.N + 3) & ~3) : 0;
+  const GemmV2Smem L = v2_smem_layout(p.stages, stage_bytes, n_stats);
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + p.stages);
+  const uint32_t tfull0 = smem_u32(bars + 2 * p.stages), tempty0 = smem_u32(bars + 2 * p.stages + 2);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
+  const uint32_t smem_base = smem_u32(smem);
+  float* s_stats = reinterpret_cast<float*>(smem + L.stats);
+
+  const int acc_stride = (p.block_n + 31) & ~31;      // the epilogue reads 32 columns at a time
+  uint32_t tmem_cols = 32;
+  while ((int)tmem_cols < 2 * acc_stride) tmem_cols <<= 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+    tma_prefetch_desc(&tma_o);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    for (int g = 0; g < 2; ++g) {
+      mbar_init(tfull0 + 8 * g, 1);
+      mbar_init(tempty0 + 8 * g, 4);       // one arrival per epilogue warp of the group
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+    tmem_relinquish();
+  }
+  for (int i = threadIdx.x; i < 2 * n_stats; i += V2_THREADS) s_stats[i] = 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ------------------------------------------------------------------ TMA producer (one ring across tiles)
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * p.block_n;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % p.stages;
+          const uint32_t ph = (it / p.stages) & 1u;
+          mbar_wait(empty0 + 8 * s, ph ^ 1u);
+          const uint32_t a_dst = smem_base + s * stage_bytes, b_dst = a_dst + A_TILE_BYTES;
+          const uint32_t bar = full0 + 8 * s;
+          mbar_expect_tx(bar, (uint32_t)stage_bytes);
+          const int kg = kb * BLOCK_K;
+          if (!p.a_mn) {
+            tma_load_2d(a_dst, &tma_a, bar, kg, m0);
+          } else {
+            tma_load_2d(a_dst, &tma_a, bar, m0, kg);
+            tma_load_2d(a_dst + BLOCK_K * 128, &tma_a, bar, m0 + 64, kg);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(b_dst, &tma_b, bar, kg, n0);
+          } else {
+            for (int j = 0; j * 64 < p.block_n; ++j) tma_load_2d(b_dst + j * (BLOCK_K * 128), &tma_b, bar, n0 + 64 * j, kg);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ------------------------------------------------------------------ MMA issuer
+      const uint32_t idesc = umma_idesc_bf16(BLOCK_M, p.block_n, p.a_mn, p.b_mn);
+      uint32_t it = 0, li = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++li) {
+        const uint32_t g = li & 1u, use = li >> 1;
+        mbar_wait(tempty0 + 8 * g, (use & 1u) ^ 1u);       // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + g * (uint32_t)acc_stride;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % p.stages;
+          const uint32_t ph = (it / p.stages) & 1u;
+          mbar_wait(full0 + 8 * s, ph);
+          tc_fence_after();
+          const uint32_t a_src = smem_base + s * stage_bytes, b_src = a_src + A_TILE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k) {
+            const uint64_t da = p.a_mn ? umma_smem_desc(a_src + k * 2048, BLOCK_K * 128, 1024)
+                                       : umma_smem_desc(a_src + k * 32, 16, 1024);
+            const uint64_t db = p.b_mn ? umma_smem_desc(b_src + k * 2048, BLOCK_K * 128, 1024)
+                                       : umma_smem_desc(b_src + k * 32, 16, 1024);
+            umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0);
+          }
+          umma_commit(empty0 + 8 * s);
+          if (kb == num_kb - 1) umma_commit(tfull0 + 8 * g);
+        }
+      }
+    }
+  } else {
+    // -------------------------------------------------------------------- epilogue warpgroups (warps 2-5, 6-9)
+    const int grp = (warp - 2) >> 2;                       // 0 / 1: which accumulator + staging tile this group owns
+    const int quad = warp & 3;                             // TMEM lane quadrant this warp may read (warp id % 4)
+    const int tid = (((warp - 2) & 3) << 5) | lane;        // 0..127 within the group
+    const int row_l = quad * 32 + lane;                    // accumulator row handled by this thread
+    uint8_t* stage_g = smem + L.staging + grp * 2 * V2_STAGE_TILE_BYTES;
+    const uint32_t stage_u32 = smem_u32(stage_g);
+    float* s_bias = reinterpret_cast<float*>(smem + L.bias) + grp * 128;
+    const uint32_t thresh = rt1_drop_threshold(p.dropout_p);
+    const float keep_scale = p.dropout_p > 0.f ? 1.f / (1.f - p.dropout_p) : 1.f;
+    const bool issuer = tid == 0;
+    uint32_t li = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++li) {
+      if ((int)(li & 1u) != grp) continue;
+      const uint32_t use = li >> 1;
+      const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * p.block_n;
+      const int nv = min(p.block_n, p.N - n0);              // valid columns of this tile
+      const int row = m0 + row_l;
+      const bool row_ok = row < p.M;
+      // staging tile free again? (its previous TMA store must have finished reading shared memory)
+      if (issuer) tma_store_wait_read();
+      if (p.bias != nullptr && tid < p.block_n) s_bias[tid] = (n0 + tid < p.N) ? __bfloat162float(p.bias[n0 + tid]) : 0.f;
+      named_bar_sync(1 + grp, V2_EPI_THREADS);
+      mbar_wait(tfull0 + 8 * grp, use & 1u);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(grp * acc_stride);
+      for (int c0 = 0; c0 < nv; c0 += 32) {
+        uint32_t acc[32];
+        tmem_ld_32x32(t_addr + (uint32_t)c0, acc);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]) * p.alpha;
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += s_bias[c0 + j];
+        }
+        if (p.dropout_p > 0.f) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c0 + j));
+            v[j] = rt1_hash_u32(idx, p.seed) >= thresh ? v[j] * keep_scale : 0.f;
+          }
+        }
+        if (p.residual != nullptr && row_ok) {
+          const bf16* rr = p.residual + (long)row * p.ldr + n0 + c0;
+#pragma unroll
+          for (int j8 = 0; j8 < 32; j8 += 8) {
+            if (c0 + j8 + 8 <= nv && ((reinterpret_cast<uintptr_t>(rr + j8) & 15) == 0)) {
+              float r8[8];
+              unpack8(*reinterpret_cast<const bf16x8*>(rr + j8), r8);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) v[j8 + k] += r8[k];
+            } else {
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (c0 + j8 + k < nv) v[j8 + k] += __bfloat162float(rr[j8 + k]);
+            }
+          }
+        }
+        // rows past M and columns past N are staged as zeros: the TMA store clips them, the statistics ignore them
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (!row_ok || c0 + j >= nv) v[j] = 0.f;
+        // 128B-swizzled staging: 16-byte chunk c of row r lives at chunk (c ^ (r & 7)) — conflict-free for the
+        // row-per-thread writes here and exactly the layout a SWIZZLE_128B tensor map reads back
+        uint8_t* slab = stage_g + (c0 >> 6) * V2_STAGE_TILE_BYTES + row_l * 128;
+        const int cbase = (c0 & 63) >> 3;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const bf16x8 pk = pack8(v + 8 * q);
+          *reinterpret_cast<bf16x8*>(slab + (((cbase + q) ^ (row_l & 7)) << 4)) = pk;
+        }
+      }
+      // accumulator drained: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8 * grp);
+      fence_proxy_async();                                   // staged tile → visible to the TMA (async proxy)
+      named_bar_sync(1 + grp, V2_EPI_THREADS);
+      if (issuer) {
+        for (int j = 0; j * 64 < nv; ++j) tma_store_2d(&tma_o, stage_u32 + j * V2_STAGE_TILE_BYTES, n0 + 64 * j, m0);
+        tma_store_commit();
+      }
+      if (n_stats > 0) {
+        // column statistics from the staged bf16 values: thread ↔ (column pair, half of the rows)
+        const int cp = tid & 63, rh = tid >> 6;
+        if (2 * cp < nv) {
+          const uint8_t* slab = stage_g + (cp >> 5) * V2_STAGE_TILE_BYTES;
+          const int chunk = (cp & 31) >> 2, inner = (cp & 3) * 4;
+          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+          for (int r = rh * 64; r < rh * 64 + 64; ++r) {
+            const bf162 x2 = *reinterpret_cast<const bf162*>(slab + r * 128 + ((chunk ^ (r & 7)) << 4) + inner);
+            const float2 f = __bfloat1622float2(x2);
+            s0 += f.x; q0 = fmaf(f.x, f.x, q0);
+            s1 += f.y; q1 = fmaf(f.y, f.y, q1);
+          }
+          const int col = n0 + 2 * cp;
+          atomicAdd(s_stats + col, s0);
+          atomicAdd(s_stats + n_stats + col, q0);
+          if (col + 1 < p.N) {
+            atomicAdd(s_stats + col + 1, s1);
+            atomicAdd(s_stats + n_stats + col + 1, q1);
+          }
+        }
+      }
+    }
+    if (issuer) tma_store_wait_read();                       // shared memory must outlive the last bulk store's reads
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (n_stats > 0) {
+    for (int i = threadIdx.x; i < p.N; i += V2_THREADS) {
+      atomicAdd(p.col_sum + i, s_stats[i]);
+      atomicAdd(p.col_sumsq + i, s_stats[n_stats + i]);
+    }
+  }
+  if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 rt1_encode_tiled_fn rt1_get_encode_tiled() {
   static rt1_encode_tiled_fn fn = nullptr;
@@ -297,6 +562,63 @@ int rt1_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uin
   return 0;
 }
 
+static bool gemm_v2_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("RT1B200_GEMM_PERSISTENT");
+    on = (e == nullptr || e[0] != '0') ? 1 : 0;
+  }
+  return on == 1;
+}
+
+// bf16-output GEMMs: persistent kernel, one CTA per SM, TMA-store epilogue
+static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, const void* B, long long ldb, void* out,
+                                  long long ldo, const void* bias, const void* residual, long long ldr, float alpha,
+                                  float dropout_p, unsigned seed, float* col_sum, float* col_sumsq, cudaStream_t stream) {
+  const int M = p.M, N = p.N, K = p.K;
+  const int bn = N <= 128 ? ((N + 15) / 16) * 16 : 128;
+  p.block_n = bn;
+  p.kb_per_split = (K + BLOCK_K - 1) / BLOCK_K;
+  p.out = out; p.ldo = ldo; p.out_fp32 = 0; p.atomic_out = 0;
+  p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
+  p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed;
+  p.col_sum = col_sum; p.col_sumsq = col_sumsq;
+  const int stage_bytes = A_TILE_BYTES + b_tile_bytes(bn, p.b_mn);
+  const int n_stats = col_sum != nullptr ? ((N + 3) & ~3) : 0;
+  int stages = 4;
+  while (stages > 2 && v2_smem_layout(stages, stage_bytes, n_stats).total + 1024 > 227 * 1024) --stages;
+  p.stages = stages;
+  const size_t smem = (size_t)v2_smem_layout(stages, stage_bytes, n_stats).total + 1024;
+  RT1_REQUIRE(smem <= 227 * 1024, "rt1_gemm_bf16: persistent kernel needs %zu bytes of shared memory", smem);
+
+  CUtensorMap ta, tb, to;
+  int rc;
+  if (!p.a_mn) rc = rt1_make_tmap_bf16_2d(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, BLOCK_M, BLOCK_K);
+  else rc = rt1_make_tmap_bf16_2d(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BLOCK_K, 64);
+  if (rc) return rc;
+  if (!p.b_mn) rc = rt1_make_tmap_bf16_2d(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, (uint32_t)bn, BLOCK_K);
+  else rc = rt1_make_tmap_bf16_2d(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BLOCK_K, 64);
+  if (rc) return rc;
+  rc = rt1_make_tmap_bf16_2d(&to, out, (uint64_t)M, (uint64_t)N, (uint64_t)ldo, BLOCK_M, 64);
+  if (rc) return rc;
+
+  static size_t configured = 0;
+  if (smem > configured) {
+    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  static int sm_count = 0;
+  if (sm_count == 0) {
+    int dev = 0;
+    RT1_CHECK_CUDA(cudaGetDevice(&dev));
+    RT1_CHECK_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const long tiles = (long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn);
+  const int grid = (int)(tiles < sm_count ? tiles : sm_count);
+  gemm_tcgen05_persistent_kernel<<<grid, V2_THREADS, smem, stream>>>(ta, tb, to, p);
+  return rt1_check_launch("rt1_gemm_bf16(persistent)");
+}
+
 // D[M,N] = alpha * op(A) · op(B)^T (+bias) → dropout → (+residual)
 //   a_mn == 0: A is [M, K] row-major (lda = row stride);  a_mn == 1: A is stored as [K, M] row-major
 //   b_mn == 0: B is [N, K] row-major (ldb);               b_mn == 1: B is stored as [K, N] row-major
@@ -311,6 +633,8 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   RT1_REQUIRE(!(accumulate && !out_fp32), "rt1_gemm_bf16: accumulate needs an fp32 output");
   GemmParams p;
   p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn;
+  if (!out_fp32 && split_k == 1 && !accumulate && ((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0 && gemm_v2_enabled())
+    return launch_gemm_persistent(p, A, lda, B, ldb, out, ldo, bias, residual, ldr, alpha, dropout_p, seed, col_sum, col_sumsq, stream);
   // tile width: whole N when it fits in one UMMA (<= 256), else 128 — rounded up to the UMMA N granule of 16
   // Tile width: at most 64 accumulator columns per CTA.  These GEMMs are short-K and memory-bound; what hides
   // the TMA → MMA → epilogue latency of a tile is the number of CTAs resident per SM, and TMEM allows

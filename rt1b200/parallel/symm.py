@@ -46,6 +46,7 @@ class _CommBase:
 
     def __init__(self):
         self.epoch = 0
+        self._pending = None      # bucket whose clearing is deferred to the next fused call
         self._grad_ptrs: List[int] = []
         self._param_ptrs: List[int] = []
         self._flag_ptrs: List[int] = []
@@ -56,22 +57,69 @@ class _CommBase:
 
 
 class SymmetricComm(_CommBase):
-    """One process per GPU.  All ranks must make the same sequence of ``alloc_tensor`` calls."""
+    """One process per GPU.  All ranks must make the same sequence of ``alloc_tensor`` calls.
 
-    def __init__(self, process_group=None, ctas_per_rank: int = 96):
+    Allocation back ends (``RT1_SYMM=torch|ipc``, default ``torch`` with fall-back to ``ipc``):
+      * ``torch`` — ``torch.distributed._symmetric_memory`` (``cuMemCreate`` + fd exchange).  Used for the
+        plumbing only; it also binds the allocation to an NVSwitch **multicast** object when the driver exposes
+        one, which is what the NVLS kernels (``multimem.ld_reduce`` / ``multimem.st``) need;
+      * ``ipc``   — ``cudaMalloc`` + ``cudaIpc`` handles exchanged through the bootstrap group (no multicast).
+    Schedule (``RT1_P2P_ALGO=auto|p2p|nvls``): ``auto`` takes NVLS from 4 ranks up when a multicast mapping
+    exists (bytes per direction N(1+1/W) vs 2N(W-1)/W for the P2P two-shot schedule)."""
+
+    def __init__(self, process_group=None, ctas_per_rank: Optional[int] = None):
         super().__init__()
+        import os
         import torch.distributed as dist
         self.dist, self.group = dist, process_group
         self.world, self.rank = dist.get_world_size(process_group), dist.get_rank(process_group)
         self.device = torch.device("cuda", torch.cuda.current_device())
-        self.ctas_per_rank = ctas_per_rank
-        self._allocs = []          # (local ptr, peer ptr list)
+        self.ctas_per_rank = int(os.environ.get("RT1_P2P_CTAS", "148")) if ctas_per_rank is None else ctas_per_rank
+        self._allocs = []          # cudaIpc: local ptrs;  torch: (tensor, handle) kept alive
         self._opened: List[int] = []
+        self.allocator = os.environ.get("RT1_SYMM", "torch")
+        self.algo = os.environ.get("RT1_P2P_ALGO", "auto")
         nflag = _lib.lib().rt1_p2p_flag_words()
-        self.flags, self._flag_ptrs = self._alloc(nflag * 4, torch.int32, nflag)
-        self._small, self._small_ptrs = self._alloc(2 * 1024 * 4, torch.float32, 2 * 1024)   # scalar all-reduce pad
+        self.flags, self._flag_ptrs, _ = self._alloc(nflag * 4, torch.int32, nflag)
+        self._small, self._small_ptrs, _ = self._alloc(2 * 1024 * 4, torch.float32, 2 * 1024)   # scalar all-reduce pad
+        self._grad_mc = self._param_mc = 0
+
+    @property
+    def has_multicast(self) -> bool:
+        return bool(self._grad_mc and self._param_mc)
+
+    def use_nvls(self, mc_ptr: int) -> bool:
+        if self.algo == "p2p" or not mc_ptr:
+            return False
+        return self.algo == "nvls" or self.world >= 4
+
+    def _alloc_torch(self, dtype, n):
+        import torch.distributed._symmetric_memory as symm_mem
+        carrier = _DT[dtype][2]
+        t = symm_mem.empty(n, dtype=carrier, device=self.device)
+        t.zero_()
+        group = self.group if self.group is not None else self.dist.group.WORLD
+        hdl = symm_mem.rendezvous(t, group)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        self._allocs.append((t, hdl))
+        torch.cuda.synchronize()
+        self.dist.barrier(group=self.group)
+        return (t.view(dtype) if carrier != dtype else t), ptrs, mc
 
     def _alloc(self, nbytes: int, dtype, n):
+        if self.allocator == "torch":
+            ok, res = 1, None
+            try:
+                res = self._alloc_torch(dtype, n)
+            except Exception as e:                                   # noqa: BLE001
+                ok = 0
+                self._alloc_error = f"{type(e).__name__}: {e}"
+            flags = [None] * self.world
+            self.dist.all_gather_object(flags, ok, group=self.group)
+            if all(flags):
+                return res
+            self.allocator = "ipc"          # every rank falls back together
         nbytes = (nbytes + 255) // 256 * 256
         ptr = ctypes.c_void_p()
         handle = (ctypes.c_ubyte * 64)()
@@ -90,42 +138,56 @@ class SymmetricComm(_CommBase):
                 self._opened.append(p.value)
                 ptrs.append(p.value)
         self._allocs.append(ptr.value)
-        return tensor_from_ptr(ptr.value, n, dtype, self.device), ptrs
+        return tensor_from_ptr(ptr.value, n, dtype, self.device), ptrs, 0
 
     def alloc_tensor(self, n: int, dtype: torch.dtype, device=None) -> torch.Tensor:
-        t, ptrs = self._alloc(n * _DT[dtype][1], dtype, n)
+        t, ptrs, mc = self._alloc(n * _DT[dtype][1], dtype, n)
         t._rt1_peer_ptrs = ptrs
+        t._rt1_mc_ptr = mc
         return t
 
     def register_grad_buffer(self, t: torch.Tensor):
-        self._grad_ptrs = t._rt1_peer_ptrs
+        self._grad_ptrs, self._grad_mc = t._rt1_peer_ptrs, t._rt1_mc_ptr
 
     def register_param_buffer(self, t: torch.Tensor):
-        self._param_ptrs = t._rt1_peer_ptrs
+        self._param_ptrs, self._param_mc = t._rt1_peer_ptrs, t._rt1_mc_ptr
 
-    def allreduce_adamw(self, lo: int, hi: int, flat, h: dict):
+    def allreduce_adamw(self, lo: int, hi: int, flat, h: dict, final: bool = True):
+        """Fused reduce + AdamW of bucket ``[lo, hi)``.  Buckets of one step are chained: pass ``final=False`` for all
+        but the last one — the closing barrier and the clearing of a bucket then ride on the next call's opening
+        barrier (k + 1 barriers per step instead of 2k)."""
+        prev_lo, prev_n = self._pending if self._pending is not None else (0, 0)
+        self._pending = None if final else (lo, hi - lo)
         one = lambda t: _ptr_array([t.data_ptr()] * self.world)     # noqa: E731  (only [rank] is read)
+        nvls = self.has_multicast and self.use_nvls(self._grad_mc)
         call("rt1_p2p_allreduce_adamw", i32(self.world), i32(self.rank), _ptr_array(self._grad_ptrs),
              _ptr_array(self._param_ptrs), _ptr_array(self._flag_ptrs), one(flat.master), one(flat.exp_avg),
-             one(flat.exp_avg_sq), i64(lo), i64(hi - lo), ctypes.c_uint(self._next_epoch()), f32(h["lr"]), f32(h["beta1"]),
+             one(flat.exp_avg_sq), ctypes.c_void_p(self._grad_mc if nvls else 0),
+             ctypes.c_void_p(self._param_mc if nvls else 0), i64(lo), i64(hi - lo), i64(prev_lo), i64(prev_n),
+             i32(1 if final else 0), ctypes.c_uint(self._next_epoch()), f32(h["lr"]), f32(h["beta1"]),
              f32(h["beta2"]), f32(h["eps"]), f32(h["weight_decay"]), f32(h["bc1"]), f32(h["bc2"]),
              i32(self._ctas_for((hi - lo) * 2 // self.world)), i32(0), stream())
 
     def _ctas_for(self, bytes_per_rank: int) -> int:
         """Enough CTAs to keep ~2 MB of peer loads in flight (NVLink latency x bandwidth), never more than asked."""
-        return max(1, min(self.ctas_per_rank, bytes_per_rank // 16384))
+        return max(1, min(self.ctas_per_rank, bytes_per_rank // 8192))
 
-    def allreduce_(self, t: torch.Tensor, scale: float = 1.0, two_shot: Optional[bool] = None, n: Optional[int] = None):
-        """In-place sum over ranks of a tensor allocated by :meth:`alloc_tensor` (bf16 or fp32)."""
+    def allreduce_(self, t: torch.Tensor, scale: float = 1.0, two_shot: Optional[bool] = None, n: Optional[int] = None,
+                   algo: Optional[str] = None):
+        """In-place sum over ranks of a tensor allocated by :meth:`alloc_tensor` (bf16 or fp32).
+        ``algo``: ``one_shot`` (result in ``t[n:2n]``), ``two_shot`` (P2P), ``nvls``; default by size and world."""
         n = t.numel() if n is None else n
         nbytes = n * t.element_size()
-        if two_shot is None:
-            two_shot = nbytes >= 256 * 1024
+        if algo is None:
+            if two_shot is None:
+                two_shot = nbytes >= 256 * 1024
+            algo = "one_shot" if not two_shot else ("nvls" if self.use_nvls(t._rt1_mc_ptr) else "two_shot")
+        code = {"one_shot": 0, "two_shot": 1, "nvls": 2}[algo]
         call("rt1_p2p_allreduce", i32(self.world), i32(self.rank), _ptr_array(t._rt1_peer_ptrs),
-             _ptr_array(self._flag_ptrs), i64(0), i64(n), i32(t.dtype == torch.bfloat16), f32(scale), i32(two_shot),
-             ctypes.c_uint(self._next_epoch()),
-             i32(self._ctas_for(nbytes // self.world if two_shot else nbytes)), i32(0), stream())
-        return t[:n] if two_shot else t[n:2 * n]
+             _ptr_array(self._flag_ptrs), ctypes.c_void_p(t._rt1_mc_ptr if code == 2 else 0), i64(0), i64(n),
+             i32(t.dtype == torch.bfloat16), f32(scale), i32(code), ctypes.c_uint(self._next_epoch()),
+             i32(self._ctas_for(nbytes // self.world if code else nbytes)), i32(0), stream())
+        return t[:n] if code else t[n:2 * n]
 
     def allreduce_small(self, x: torch.Tensor) -> torch.Tensor:
         """Sum of a small fp32 tensor (≤ 1024 elements) over ranks via the one-shot kernel (metrics, C4)."""
@@ -135,8 +197,8 @@ class SymmetricComm(_CommBase):
         if n > x.numel():
             self._small[x.numel():n].zero_()
         call("rt1_p2p_allreduce", i32(self.world), i32(self.rank), _ptr_array(self._small_ptrs),
-             _ptr_array(self._flag_ptrs), i64(0), i64(n), i32(0), f32(1.0), i32(0), ctypes.c_uint(self._next_epoch()),
-             i32(1), i32(0), stream())
+             _ptr_array(self._flag_ptrs), ctypes.c_void_p(0), i64(0), i64(n), i32(0), f32(1.0), i32(0),
+             ctypes.c_uint(self._next_epoch()), i32(1), i32(0), stream())
         return self._small[n:n + x.numel()].clone().view(x.shape)
 
     def close(self):
@@ -151,6 +213,7 @@ class SymmetricComm(_CommBase):
             except Exception:
                 pass
         self._opened = []
+        self._allocs = [a for a in self._allocs if not isinstance(a, tuple)]
 
 
 class EmulatedComm(_CommBase):
@@ -169,11 +232,13 @@ class EmulatedComm(_CommBase):
         call("rt1_p2p_allreduce_adamw", i32(self.world), i32(0), _ptr_array([g.data_ptr() for g in grads]),
              _ptr_array([p.data_ptr() for p in params]), _ptr_array(self._flag_ptrs),
              _ptr_array([t.data_ptr() for t in masters]), _ptr_array([t.data_ptr() for t in ms]),
-             _ptr_array([t.data_ptr() for t in vs]), i64(lo), i64(hi - lo), ctypes.c_uint(self._next_epoch()),
+             _ptr_array([t.data_ptr() for t in vs]), ctypes.c_void_p(0), ctypes.c_void_p(0), i64(lo), i64(hi - lo),
+             i64(0), i64(0), i32(1), ctypes.c_uint(self._next_epoch()),
              f32(h["lr"]), f32(h["beta1"]), f32(h["beta2"]), f32(h["eps"]), f32(h["weight_decay"]), f32(h["bc1"]),
              f32(h["bc2"]), i32(self.ctas_per_rank), i32(1), stream())
 
     def allreduce_(self, bufs, n: int, scale: float = 1.0, two_shot: bool = True):
         call("rt1_p2p_allreduce", i32(self.world), i32(0), _ptr_array([b.data_ptr() for b in bufs]),
-             _ptr_array(self._flag_ptrs), i64(0), i64(n), i32(bufs[0].dtype == torch.bfloat16), f32(scale), i32(two_shot),
-             ctypes.c_uint(self._next_epoch()), i32(self.ctas_per_rank), i32(1), stream())
+             _ptr_array(self._flag_ptrs), ctypes.c_void_p(0), i64(0), i64(n), i32(bufs[0].dtype == torch.bfloat16),
+             f32(scale), i32(1 if two_shot else 0), ctypes.c_uint(self._next_epoch()), i32(self.ctas_per_rank), i32(1),
+             stream())
