@@ -269,14 +269,15 @@ __global__ void __launch_bounds__(128, 8) gemm_tcgen05_kernel(const __grid_const
 //   * one CTA per SM walks the (m-tile, n-tile) list; operand stages form ONE ring across tiles, so the TMA loads of
 //     the next tiles are in flight while the current tile is multiplied and the previous ones are written out;
 //   * two TMEM accumulators (2 x BLOCK_N columns): the MMA of tile i+1 overlaps the epilogue of tile i;
-//   * two epilogue warpgroups (4 warps each = the 4 TMEM lane quadrants) alternate tiles: tcgen05.ld → bias / alpha /
-//     dropout / residual → bf16 → 128B-swizzled staging tile in shared memory → ONE TMA store per 64-column slab
-//     (full 128-byte lines to L2, partial tiles clipped by the tensor map);
+//   * two epilogue groups of 8 warps (4 TMEM lane quadrants x 2 column halves) alternate tiles: tcgen05.ld → bias /
+//     alpha / dropout / residual → bf16 → 128B-swizzled staging tile in shared memory → ONE TMA store per 64-column
+//     slab (full 128-byte lines to L2, partial tiles clipped by the tensor map).  16 epilogue warps = 4 per scheduler:
+//     with 4 (one per scheduler) every tcgen05.ld / LDS latency was exposed and a 128x128 tile took ~5 us;
 //   * BatchNorm column statistics are taken from the staged bf16 tile (the values the consumer will actually read),
 //     accumulated per CTA in shared memory and flushed with one atomic per column per CTA at the end.
-// Warp roles: 0 = TMA producer, 1 = MMA issuer (+ TMEM alloc), 2-5 = epilogue group 0, 6-9 = epilogue group 1.
-constexpr int V2_THREADS = 320;
-constexpr int V2_EPI_THREADS = 128;
+// Warp roles: 0 = TMA producer, 1 = MMA issuer (+ TMEM alloc), 2-9 = epilogue group 0, 10-17 = epilogue group 1.
+constexpr int V2_THREADS = 576;
+constexpr int V2_EPI_THREADS = 256;
 constexpr int V2_STAGE_TILE_BYTES = BLOCK_M * 128;   // one 64-column bf16 slab of the staging tile (128B rows)
 
 struct GemmV2Smem {   // byte offsets from the 1024-aligned base
@@ -293,6 +294,15 @@ __host__ __device__ inline GemmV2Smem v2_smem_layout(int stages, int stage_bytes
   return L;
 }
 
+// Tile order: n fastest (the n-tiles of one 128-row A slab run back to back on the same SM), serpentine — odd slabs
+// walk the n-tiles backwards — so that consecutive tiles, which alternate between the two epilogue groups, alternate
+// between wide and narrow n-tiles as well.
+__device__ __forceinline__ void v2_tile_coords(int t, int n_tiles, int block_n, int& m0, int& n0) {
+  const int mt = t / n_tiles, j = t - mt * n_tiles;
+  m0 = mt * BLOCK_M;
+  n0 = ((mt & 1) ? n_tiles - 1 - j : j) * block_n;
+}
+
 __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                                               const __grid_constant__ CUtensorMap tma_b,
                                                                               const __grid_constant__ CUtensorMap tma_o,
@@ -304,6 +314,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
   const int m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
   const int num_tiles = n_tiles * m_tiles;
   const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+  // each CTA walks a CONTIGUOUS run of tiles (a strided walk with an even grid would hand one CTA only the wide and
+  // its neighbour only the narrow n-tiles of N = 128 + 16)
+  const int per_cta = (num_tiles + gridDim.x - 1) / gridDim.x;
+  const int t_begin = min(num_tiles, (int)blockIdx.x * per_cta), t_end = min(num_tiles, t_begin + per_cta);
   const int b_bytes = b_tile_bytes(p.block_n, p.b_mn);
   const int stage_bytes = A_TILE_BYTES + b_bytes;
   const int n_stats = p.col_sum != nullptr ? ((p.N + 3) & ~3) : 0;
@@ -330,7 +344,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
     }
     for (int g = 0; g < 2; ++g) {
       mbar_init(tfull0 + 8 * g, 1);
-      mbar_init(tempty0 + 8 * g, 4);       // one arrival per epilogue warp of the group
+      mbar_init(tempty0 + 8 * g, 8);       // one arrival per epilogue warp of the group
     }
     fence_barrier_init();
   }
@@ -348,8 +362,9 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
     if (lane == 0) {
       // ------------------------------------------------------------------ TMA producer (one ring across tiles)
       uint32_t it = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * p.block_n;
+      for (int t = t_begin; t < t_end; ++t) {
+        int m0, n0;
+        v2_tile_coords(t, n_tiles, p.block_n, m0, n0);
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % p.stages;
           const uint32_t ph = (it / p.stages) & 1u;
@@ -377,7 +392,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
       // ------------------------------------------------------------------ MMA issuer
       const uint32_t idesc = umma_idesc_bf16(BLOCK_M, p.block_n, p.a_mn, p.b_mn);
       uint32_t it = 0, li = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++li) {
+      for (int t = t_begin; t < t_end; ++t, ++li) {
         const uint32_t g = li & 1u, use = li >> 1;
         mbar_wait(tempty0 + 8 * g, (use & 1u) ^ 1u);       // epilogue has drained this accumulator
         tc_fence_after();
@@ -402,10 +417,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
       }
     }
   } else {
-    // -------------------------------------------------------------------- epilogue warpgroups (warps 2-5, 6-9)
-    const int grp = (warp - 2) >> 2;                       // 0 / 1: which accumulator + staging tile this group owns
+    // -------------------------------------------------------------------- epilogue groups (warps 2-9, 10-17)
+    const int grp = (warp - 2) >> 3;                       // 0 / 1: which staging tile this group owns
     const int quad = warp & 3;                             // TMEM lane quadrant this warp may read (warp id % 4)
-    const int tid = (((warp - 2) & 3) << 5) | lane;        // 0..127 within the group
+    const int half = ((warp - 2) & 7) >> 2;                // column half (= staging slab) this warp converts
+    const int tid = (((warp - 2) & 7) << 5) | lane;        // 0..255 within the group
     const int row_l = quad * 32 + lane;                    // accumulator row handled by this thread
     uint8_t* stage_g = smem + L.staging + grp * 2 * V2_STAGE_TILE_BYTES;
     const uint32_t stage_u32 = smem_u32(stage_g);
@@ -414,10 +430,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
     const float keep_scale = p.dropout_p > 0.f ? 1.f / (1.f - p.dropout_p) : 1.f;
     const bool issuer = tid == 0;
     uint32_t li = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++li) {
-      if ((int)(li & 1u) != grp) continue;
-      const uint32_t use = li >> 1;
-      const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * p.block_n;
+    for (int t = t_begin; t < t_end; ++t, ++li) {
+      if ((int)(li & 1u) != grp) continue;                 // group g owns accumulator g: it sees every phase of its barriers
+      const uint32_t acc_i = li & 1u, use = li >> 1;
+      int m0, n0;
+      v2_tile_coords(t, n_tiles, p.block_n, m0, n0);
       const int nv = min(p.block_n, p.N - n0);              // valid columns of this tile
       const int row = m0 + row_l;
       const bool row_ok = row < p.M;
@@ -425,16 +442,21 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
       if (issuer) tma_store_wait_read();
       if (p.bias != nullptr && tid < p.block_n) s_bias[tid] = (n0 + tid < p.N) ? __bfloat162float(p.bias[n0 + tid]) : 0.f;
       named_bar_sync(1 + grp, V2_EPI_THREADS);
-      mbar_wait(tfull0 + 8 * grp, use & 1u);
+      mbar_wait(tfull0 + 8 * acc_i, use & 1u);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(grp * acc_stride);
-      for (int c0 = 0; c0 < nv; c0 += 32) {
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc_i * (uint32_t)acc_stride;
+      const bool full_tile = m0 + BLOCK_M <= p.M;
+      for (int c0 = half * 64; c0 < min(nv, half * 64 + 64); c0 += 32) {
         uint32_t acc[32];
         tmem_ld_32x32(t_addr + (uint32_t)c0, acc);
         tmem_ld_wait();
         float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]) * p.alpha;
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
+        if (p.alpha != 1.f) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+        }
         if (p.bias != nullptr) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += s_bias[c0 + j];
@@ -463,9 +485,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
           }
         }
         // rows past M and columns past N are staged as zeros: the TMA store clips them, the statistics ignore them
+        if (!full_tile || c0 + 32 > nv) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (!row_ok || c0 + j >= nv) v[j] = 0.f;
+          for (int j = 0; j < 32; ++j)
+            if (!row_ok || c0 + j >= nv) v[j] = 0.f;
+        }
         // 128B-swizzled staging: 16-byte chunk c of row r lives at chunk (c ^ (r & 7)) — conflict-free for the
         // row-per-thread writes here and exactly the layout a SWIZZLE_128B tensor map reads back
         uint8_t* slab = stage_g + (c0 >> 6) * V2_STAGE_TILE_BYTES + row_l * 128;
@@ -479,7 +503,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
       // accumulator drained: hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty0 + 8 * grp);
+      if (lane == 0) mbar_arrive(tempty0 + 8 * acc_i);
       fence_proxy_async();                                   // staged tile → visible to the TMA (async proxy)
       named_bar_sync(1 + grp, V2_EPI_THREADS);
       if (issuer) {
@@ -487,14 +511,14 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
         tma_store_commit();
       }
       if (n_stats > 0) {
-        // column statistics from the staged bf16 values: thread ↔ (column pair, half of the rows)
+        // column statistics from the staged bf16 values: thread ↔ (column pair, quarter of the rows)
         const int cp = tid & 63, rh = tid >> 6;
         if (2 * cp < nv) {
           const uint8_t* slab = stage_g + (cp >> 5) * V2_STAGE_TILE_BYTES;
           const int chunk = (cp & 31) >> 2, inner = (cp & 3) * 4;
           float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll 8
-          for (int r = rh * 64; r < rh * 64 + 64; ++r) {
+          for (int r = rh * 32; r < rh * 32 + 32; ++r) {
             const bf162 x2 = *reinterpret_cast<const bf162*>(slab + r * 128 + ((chunk ^ (r & 7)) << 4) + inner);
             const float2 f = __bfloat1622float2(x2);
             s0 += f.x; q0 = fmaf(f.x, f.x, q0);
