@@ -41,6 +41,8 @@ struct GemmParams {
   // optional per-column statistics of the (post-bias) fp32 output: sum and sum of squares, atomically added
   float* col_sum;
   float* col_sumsq;
+  int b_resident;        // persistent kernel: all B tiles stay in shared memory (small weights, huge M)
+  int dbg;               // bench-only switches (RT1B200_GEMM_DBG): 1 no copy-out, 2 no statistics, 4 no TMEM drain/staging, 8 no A loads, 16 no B loads
 };
 
 constexpr int BLOCK_M = 128;
@@ -280,17 +282,21 @@ constexpr int V2_THREADS = 576;
 constexpr int V2_EPI_THREADS = 256;
 constexpr int V2_STAGE_TILE_BYTES = BLOCK_M * 128;   // one 64-column bf16 slab of the staging tile (128B rows)
 
+constexpr int V2_MAX_ACC = 4;                         // TMEM accumulator ring (512 columns / 128)
+constexpr int V2_BRES_MAX = 64 * 1024;                // B operands up to this size stay resident in shared memory
+
 struct GemmV2Smem {   // byte offsets from the 1024-aligned base
-  int stage0, staging, stats, bias, bars, total;
+  int stage0, bres, staging, stats, bias, bars, total;
 };
-__host__ __device__ inline GemmV2Smem v2_smem_layout(int stages, int stage_bytes, int n_stats) {
+__host__ __device__ inline GemmV2Smem v2_smem_layout(int stages, int stage_bytes, int bres_bytes, int n_stats) {
   GemmV2Smem L;
   L.stage0 = 0;
-  L.staging = stages * stage_bytes;                          // 2 groups x 2 slabs x 16 KiB
+  L.bres = stages * stage_bytes;                             // resident B tiles [n_tile][k_block] (0 bytes in ring mode)
+  L.staging = L.bres + bres_bytes;                           // 2 groups x 2 slabs x 16 KiB
   L.stats = L.staging + 2 * 2 * V2_STAGE_TILE_BYTES;         // 2 x n_stats floats
   L.bias = L.stats + 2 * n_stats * 4;                        // 2 groups x 128 floats
-  L.bars = (L.bias + 2 * 128 * 4 + 7) & ~7;                  // full[stages], empty[stages], tmem_full[2], tmem_empty[2], slot
-  L.total = L.bars + (2 * stages + 4) * 8 + 16;
+  L.bars = (L.bias + 2 * 128 * 4 + 7) & ~7;                  // full[stages], empty[stages], tmem_full[4], tmem_empty[4], bres, slot
+  L.total = L.bars + (2 * stages + 2 * V2_MAX_ACC + 1) * 8 + 16;
   return L;
 }
 
@@ -319,33 +325,41 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
   const int per_cta = (num_tiles + gridDim.x - 1) / gridDim.x;
   const int t_begin = min(num_tiles, (int)blockIdx.x * per_cta), t_end = min(num_tiles, t_begin + per_cta);
   const int b_bytes = b_tile_bytes(p.block_n, p.b_mn);
-  const int stage_bytes = A_TILE_BYTES + b_bytes;
+  // Weights of the early, huge-M 1x1 convolutions are a few KB: in resident mode every (n-tile, k-block) B tile is
+  // loaded ONCE per CTA and the stage ring carries A only.  (Re-loading them per tile cost more than the A stream:
+  // boxes that are mostly out of bounds — K = 24 of 64, N = 24 of 64 — are slow in the TMA unit.)
+  const int bres_bytes = p.b_resident ? n_tiles * num_kb * b_bytes : 0;
+  const int stage_bytes = A_TILE_BYTES + (p.b_resident ? 0 : b_bytes);
   const int n_stats = p.col_sum != nullptr ? ((p.N + 3) & ~3) : 0;
-  const GemmV2Smem L = v2_smem_layout(p.stages, stage_bytes, n_stats);
+  const GemmV2Smem L = v2_smem_layout(p.stages, stage_bytes, bres_bytes, n_stats);
 
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bars);
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + p.stages);
-  const uint32_t tfull0 = smem_u32(bars + 2 * p.stages), tempty0 = smem_u32(bars + 2 * p.stages + 2);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 4);
+  const uint32_t tfull0 = smem_u32(bars + 2 * p.stages), tempty0 = smem_u32(bars + 2 * p.stages + V2_MAX_ACC);
+  const uint32_t bres_bar = smem_u32(bars + 2 * p.stages + 2 * V2_MAX_ACC);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * p.stages + 2 * V2_MAX_ACC + 1);
   const uint32_t smem_base = smem_u32(smem);
   float* s_stats = reinterpret_cast<float*>(smem + L.stats);
 
+  // Accumulator ring: the MMA warp runs up to n_acc tiles ahead of the epilogue, which hides the
+  // tempty → MMA issue → commit → tfull handshake chain (~1.4 us end to end, measured with everything else off).
   const int acc_stride = (p.block_n + 31) & ~31;      // the epilogue reads 32 columns at a time
+  const uint32_t n_acc = 4 * acc_stride <= 512 ? 4u : 2u;
   uint32_t tmem_cols = 32;
-  while ((int)tmem_cols < 2 * acc_stride) tmem_cols <<= 1;
+  while (tmem_cols < n_acc * acc_stride) tmem_cols <<= 1;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
-    tma_prefetch_desc(&tma_o);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, 1);
     }
-    for (int g = 0; g < 2; ++g) {
+    for (int g = 0; g < V2_MAX_ACC; ++g) {
       mbar_init(tfull0 + 8 * g, 1);
       mbar_init(tempty0 + 8 * g, 8);       // one arrival per epilogue warp of the group
     }
+    mbar_init(bres_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -362,58 +376,83 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
     if (lane == 0) {
       // ------------------------------------------------------------------ TMA producer (one ring across tiles)
       uint32_t it = 0;
+      if (p.b_resident && t_begin < t_end) {
+        mbar_expect_tx(bres_bar, (uint32_t)bres_bytes);
+        for (int nt = 0; nt < n_tiles; ++nt)
+          for (int kb = 0; kb < num_kb; ++kb) {
+            const uint32_t b_dst = smem_base + L.bres + (nt * num_kb + kb) * b_bytes;
+            if (!p.b_mn) {
+              tma_load_2d(b_dst, &tma_b, bres_bar, kb * BLOCK_K, nt * p.block_n);
+            } else {
+              for (int j = 0; j * 64 < p.block_n; ++j)
+                tma_load_2d(b_dst + j * (BLOCK_K * 128), &tma_b, bres_bar, nt * p.block_n + 64 * j, kb * BLOCK_K);
+            }
+          }
+      }
+      uint32_t s = 0, ph = 0;
+      int mt = t_begin / n_tiles, j = t_begin - mt * n_tiles;
       for (int t = t_begin; t < t_end; ++t) {
-        int m0, n0;
-        v2_tile_coords(t, n_tiles, p.block_n, m0, n0);
+        const int m0 = mt * BLOCK_M, n0 = ((mt & 1) ? n_tiles - 1 - j : j) * p.block_n;
+        if (++j == n_tiles) { j = 0; ++mt; }
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (it / p.stages) & 1u;
           mbar_wait(empty0 + 8 * s, ph ^ 1u);
           const uint32_t a_dst = smem_base + s * stage_bytes, b_dst = a_dst + A_TILE_BYTES;
           const uint32_t bar = full0 + 8 * s;
-          mbar_expect_tx(bar, (uint32_t)stage_bytes);
+          const bool skip_a = (p.dbg & 8) && it >= (uint32_t)p.stages;
+          const bool skip_b = p.b_resident || ((p.dbg & 16) && it >= (uint32_t)p.stages);
+          mbar_expect_tx(bar, (uint32_t)((skip_a ? 0 : A_TILE_BYTES) + (skip_b ? 0 : b_bytes)));
           const int kg = kb * BLOCK_K;
-          if (!p.a_mn) {
+          if (skip_a) {
+          } else if (!p.a_mn) {
             tma_load_2d(a_dst, &tma_a, bar, kg, m0);
           } else {
             tma_load_2d(a_dst, &tma_a, bar, m0, kg);
             tma_load_2d(a_dst + BLOCK_K * 128, &tma_a, bar, m0 + 64, kg);
           }
-          if (!p.b_mn) {
+          if (skip_b) {
+          } else if (!p.b_mn) {
             tma_load_2d(b_dst, &tma_b, bar, kg, n0);
           } else {
-            for (int j = 0; j * 64 < p.block_n; ++j) tma_load_2d(b_dst + j * (BLOCK_K * 128), &tma_b, bar, n0 + 64 * j, kg);
+            for (int jj = 0; jj * 64 < p.block_n; ++jj) tma_load_2d(b_dst + jj * (BLOCK_K * 128), &tma_b, bar, n0 + 64 * jj, kg);
           }
+          if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       // ------------------------------------------------------------------ MMA issuer
+      // This loop runs on ONE thread and its instruction latency is the pipeline's clock (~0.8 us per tile with
+      // divisions and descriptor encoding inside; measured with all memory traffic switched off), so everything is
+      // incremental: ring indices and phases are counters, descriptors are a constant plus an address term.
       const uint32_t idesc = umma_idesc_bf16(BLOCK_M, p.block_n, p.a_mn, p.b_mn);
-      uint32_t it = 0, li = 0;
-      for (int t = t_begin; t < t_end; ++t, ++li) {
-        const uint32_t g = li & 1u, use = li >> 1;
-        mbar_wait(tempty0 + 8 * g, (use & 1u) ^ 1u);       // epilogue has drained this accumulator
+      const uint64_t a_desc0 = p.a_mn ? umma_smem_desc(0, BLOCK_K * 128, 1024) : umma_smem_desc(0, 16, 1024);
+      const uint64_t b_desc0 = p.b_mn ? umma_smem_desc(0, BLOCK_K * 128, 1024) : umma_smem_desc(0, 16, 1024);
+      const uint32_t a_kstep = p.a_mn ? 2048u >> 4 : 32u >> 4, b_kstep = p.b_mn ? 2048u >> 4 : 32u >> 4;
+      uint32_t s = 0, ph = 0, g = 0, gph = 1;                // stage ring index/phase, accumulator ring index/(phase ^ 1)
+      int mt = t_begin / n_tiles, j = t_begin - mt * n_tiles; // serpentine walk, see v2_tile_coords
+      if (p.b_resident && t_begin < t_end) mbar_wait(bres_bar, 0);
+      for (int t = t_begin; t < t_end; ++t) {
+        const int nt = (mt & 1) ? n_tiles - 1 - j : j;
+        mbar_wait(tempty0 + 8 * g, gph);                     // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + g * (uint32_t)acc_stride;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (it / p.stages) & 1u;
+        uint32_t b_res = smem_base + L.bres + nt * num_kb * b_bytes;
+        for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(full0 + 8 * s, ph);
           tc_fence_after();
-          const uint32_t a_src = smem_base + s * stage_bytes, b_src = a_src + A_TILE_BYTES;
+          const uint32_t a_src = smem_base + s * stage_bytes;
+          const uint32_t b_src = p.b_resident ? b_res : a_src + A_TILE_BYTES;
+          const uint64_t da = a_desc0 + (uint64_t)((a_src & 0x3FFFF) >> 4), db = b_desc0 + (uint64_t)((b_src & 0x3FFFF) >> 4);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k) {
-            const uint64_t da = p.a_mn ? umma_smem_desc(a_src + k * 2048, BLOCK_K * 128, 1024)
-                                       : umma_smem_desc(a_src + k * 32, 16, 1024);
-            const uint64_t db = p.b_mn ? umma_smem_desc(b_src + k * 2048, BLOCK_K * 128, 1024)
-                                       : umma_smem_desc(b_src + k * 32, 16, 1024);
-            umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0);
-          }
+          for (int k = 0; k < BLOCK_K / 16; ++k) umma_bf16(d_tmem, da + k * a_kstep, db + k * b_kstep, idesc, (kb | k) != 0);
           umma_commit(empty0 + 8 * s);
           if (kb == num_kb - 1) umma_commit(tfull0 + 8 * g);
+          b_res += b_bytes;
+          if (++s == (uint32_t)p.stages) { s = 0; ph ^= 1u; }
         }
+        if (++g == n_acc) { g = 0; gph ^= 1u; }
+        if (++j == n_tiles) { j = 0; ++mt; }
       }
     }
   } else {
@@ -424,93 +463,100 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
     const int tid = (((warp - 2) & 7) << 5) | lane;        // 0..255 within the group
     const int row_l = quad * 32 + lane;                    // accumulator row handled by this thread
     uint8_t* stage_g = smem + L.staging + grp * 2 * V2_STAGE_TILE_BYTES;
-    const uint32_t stage_u32 = smem_u32(stage_g);
     float* s_bias = reinterpret_cast<float*>(smem + L.bias) + grp * 128;
     const uint32_t thresh = rt1_drop_threshold(p.dropout_p);
     const float keep_scale = p.dropout_p > 0.f ? 1.f / (1.f - p.dropout_p) : 1.f;
-    const bool issuer = tid == 0;
     uint32_t li = 0;
     for (int t = t_begin; t < t_end; ++t, ++li) {
-      if ((int)(li & 1u) != grp) continue;                 // group g owns accumulator g: it sees every phase of its barriers
-      const uint32_t acc_i = li & 1u, use = li >> 1;
+      if ((int)(li & 1u) != grp) continue;                 // group g owns accumulators g, g + 2: it sees every phase of their barriers
+      const uint32_t acc_i = li % n_acc, use = li / n_acc;
       int m0, n0;
       v2_tile_coords(t, n_tiles, p.block_n, m0, n0);
       const int nv = min(p.block_n, p.N - n0);              // valid columns of this tile
       const int row = m0 + row_l;
       const bool row_ok = row < p.M;
-      // staging tile free again? (its previous TMA store must have finished reading shared memory)
-      if (issuer) tma_store_wait_read();
+      if (tid == 0) tma_store_wait_read();                   // staging tile free again (previous store has read it)
       if (p.bias != nullptr && tid < p.block_n) s_bias[tid] = (n0 + tid < p.N) ? __bfloat162float(p.bias[n0 + tid]) : 0.f;
       named_bar_sync(1 + grp, V2_EPI_THREADS);
       mbar_wait(tfull0 + 8 * acc_i, use & 1u);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc_i * (uint32_t)acc_stride;
       const bool full_tile = m0 + BLOCK_M <= p.M;
-      for (int c0 = half * 64; c0 < min(nv, half * 64 + 64); c0 += 32) {
+      // the accumulator goes back to the MMA warp as soon as its last chunk sits in registers
+      const int cbeg = half * 64, cend = (p.dbg & 4) ? 0 : min(nv, half * 64 + 64);
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        const int c0 = cbeg + 32 * h2;
         uint32_t acc[32];
-        tmem_ld_32x32(t_addr + (uint32_t)c0, acc);
-        tmem_ld_wait();
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
-        if (p.alpha != 1.f) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+        if (c0 < cend) {
+          tmem_ld_32x32(t_addr + (uint32_t)c0, acc);
+          tmem_ld_wait();
         }
-        if (p.bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] += s_bias[c0 + j];
+        if (h2 == 1) {                                     // last read of this accumulator: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty0 + 8 * acc_i);
         }
-        if (p.dropout_p > 0.f) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c0 + j));
-            v[j] = rt1_hash_u32(idx, p.seed) >= thresh ? v[j] * keep_scale : 0.f;
-          }
-        }
-        if (p.residual != nullptr && row_ok) {
-          const bf16* rr = p.residual + (long)row * p.ldr + n0 + c0;
-#pragma unroll
-          for (int j8 = 0; j8 < 32; j8 += 8) {
-            if (c0 + j8 + 8 <= nv && ((reinterpret_cast<uintptr_t>(rr + j8) & 15) == 0)) {
-              float r8[8];
-              unpack8(*reinterpret_cast<const bf16x8*>(rr + j8), r8);
-#pragma unroll
-              for (int k = 0; k < 8; ++k) v[j8 + k] += r8[k];
-            } else {
-#pragma unroll
-              for (int k = 0; k < 8; ++k)
-                if (c0 + j8 + k < nv) v[j8 + k] += __bfloat162float(rr[j8 + k]);
-            }
-          }
-        }
-        // rows past M and columns past N are staged as zeros: the TMA store clips them, the statistics ignore them
-        if (!full_tile || c0 + 32 > nv) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (!row_ok || c0 + j >= nv) v[j] = 0.f;
-        }
-        // 128B-swizzled staging: 16-byte chunk c of row r lives at chunk (c ^ (r & 7)) — conflict-free for the
-        // row-per-thread writes here and exactly the layout a SWIZZLE_128B tensor map reads back
+        if (c0 >= cend) continue;
+        const bool edge = !full_tile || c0 + 32 > nv;
+        // rows past M and columns past N are staged as zeros (the copy-out skips them, the statistics ignore them).
+        // XOR-swizzled staging: 16-byte chunk c of row r lives at chunk (c ^ (r & 7)) — conflict-free for the
+        // row-per-thread writes here and for the 8-lanes-per-row reads of the copy-out below
         uint8_t* slab = stage_g + (c0 >> 6) * V2_STAGE_TILE_BYTES + row_l * 128;
         const int cbase = (c0 & 63) >> 3;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const bf16x8 pk = pack8(v + 8 * q);
-          *reinterpret_cast<bf16x8*>(slab + (((cbase + q) ^ (row_l & 7)) << 4)) = pk;
+        for (int q = 0; q < 4; ++q) {                      // 8 columns at a time keeps the live register set small
+          const int c8 = c0 + 8 * q;
+          float v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(acc[8 * q + k]);
+          if (p.alpha != 1.f) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] *= p.alpha;
+          }
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] += s_bias[c8 + k];
+          }
+          if (p.dropout_p > 0.f) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c8 + k));
+              v[k] = rt1_hash_u32(idx, p.seed) >= thresh ? v[k] * keep_scale : 0.f;
+            }
+          }
+          if (p.residual != nullptr && row_ok) {
+            const bf16* rr = p.residual + (long)row * p.ldr + n0 + c8;
+            if (c8 + 8 <= nv && ((reinterpret_cast<uintptr_t>(rr) & 15) == 0)) {
+              float r8[8];
+              unpack8(*reinterpret_cast<const bf16x8*>(rr), r8);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) v[k] += r8[k];
+            } else {
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (c8 + k < nv) v[k] += __bfloat162float(rr[k]);
+            }
+          }
+          if (edge) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              if (!row_ok || c8 + k >= nv) v[k] = 0.f;
+          }
+          *reinterpret_cast<bf16x8*>(slab + (((cbase + q) ^ (row_l & 7)) << 4)) = pack8(v);
         }
       }
-      // accumulator drained: hand it back to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty0 + 8 * acc_i);
       fence_proxy_async();                                   // staged tile → visible to the TMA (async proxy)
       named_bar_sync(1 + grp, V2_EPI_THREADS);
-      if (issuer) {
-        for (int j = 0; j * 64 < nv; ++j) tma_store_2d(&tma_o, stage_u32 + j * V2_STAGE_TILE_BYTES, n0 + 64 * j, m0);
+      // ONE TMA store per 64-column slab: full 128-byte lines to L2, rows past M / columns past N clipped by the
+      // tensor map.  (Writing the tile out with ordinary 16-byte stores from the epilogue warps was tried and lost:
+      // the epilogue is instruction-issue bound and the copy-out added ~150 instructions per thread and tile.)
+      if (tid == 0 && !(p.dbg & 1)) {
+        for (int jj = 0; jj * 64 < nv; ++jj)
+          tma_store_2d(&tma_o, smem_u32(stage_g) + jj * V2_STAGE_TILE_BYTES, n0 + 64 * jj, m0);
         tma_store_commit();
       }
-      if (n_stats > 0) {
+      if (n_stats > 0 && !(p.dbg & 2)) {
         // column statistics from the staged bf16 values: thread ↔ (column pair, quarter of the rows)
         const int cp = tid & 63, rh = tid >> 6;
         if (2 * cp < nv) {
@@ -534,7 +580,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
         }
       }
     }
-    if (issuer) tma_store_wait_read();                       // shared memory must outlive the last bulk store's reads
+    if (tid == 0) tma_store_wait_read();                     // shared memory must outlive the last bulk store's reads
   }
 
   tc_fence_before();
@@ -595,6 +641,15 @@ static bool gemm_v2_enabled() {
   return on == 1;
 }
 
+static long v2_min_tiles() {
+  static long v = -1;
+  if (v < 0) {
+    const char* e = getenv("RT1B200_GEMM_PERSISTENT_MIN_TILES");
+    v = e ? atol(e) : 1;
+  }
+  return v;
+}
+
 // bf16-output GEMMs: persistent kernel, one CTA per SM, TMA-store epilogue
 static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, const void* B, long long ldb, void* out,
                                   long long ldo, const void* bias, const void* residual, long long ldr, float alpha,
@@ -607,12 +662,20 @@ static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, c
   p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
   p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed;
   p.col_sum = col_sum; p.col_sumsq = col_sumsq;
-  const int stage_bytes = A_TILE_BYTES + b_tile_bytes(bn, p.b_mn);
+  {
+    const char* e = getenv("RT1B200_GEMM_DBG");
+    p.dbg = e ? atoi(e) : 0;
+  }
+  const int n_tiles_h = (N + bn - 1) / bn, b_bytes_h = b_tile_bytes(bn, p.b_mn);
+  const long bres = (long)n_tiles_h * p.kb_per_split * b_bytes_h;
+  p.b_resident = (bres <= V2_BRES_MAX && !(p.dbg & 32)) ? 1 : 0;
+  const int bres_bytes = p.b_resident ? (int)bres : 0;
+  const int stage_bytes = A_TILE_BYTES + (p.b_resident ? 0 : b_bytes_h);
   const int n_stats = col_sum != nullptr ? ((N + 3) & ~3) : 0;
-  int stages = 4;
-  while (stages > 2 && v2_smem_layout(stages, stage_bytes, n_stats).total + 1024 > 227 * 1024) --stages;
+  int stages = p.b_resident ? 6 : 4;
+  while (stages > 2 && v2_smem_layout(stages, stage_bytes, bres_bytes, n_stats).total + 1024 > 227 * 1024) --stages;
   p.stages = stages;
-  const size_t smem = (size_t)v2_smem_layout(stages, stage_bytes, n_stats).total + 1024;
+  const size_t smem = (size_t)v2_smem_layout(stages, stage_bytes, bres_bytes, n_stats).total + 1024;
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_gemm_bf16: persistent kernel needs %zu bytes of shared memory", smem);
 
   CUtensorMap ta, tb, to;
@@ -657,7 +720,12 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   RT1_REQUIRE(!(accumulate && !out_fp32), "rt1_gemm_bf16: accumulate needs an fp32 output");
   GemmParams p;
   p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn;
-  if (!out_fp32 && split_k == 1 && !accumulate && ((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0 && gemm_v2_enabled())
+  // The persistent kernel pays ~10 us of set-up (TMEM allocation, barrier init, pipeline fill) and runs ONE CTA per SM:
+  // it wins when every SM gets a run of tiles (the huge-M 1x1 convolutions), the tile-per-CTA kernel below — 8 CTAs
+  // per SM, 64-column tiles — wins for the decoder and the late, small-M layers.
+  const long tiles128 = (long)((M + 127) / 128) * ((N + 127) / 128);
+  if (!out_fp32 && split_k == 1 && !accumulate && ((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0 && tiles128 >= v2_min_tiles() &&
+      gemm_v2_enabled())
     return launch_gemm_persistent(p, A, lda, B, ldb, out, ldo, bias, residual, ldr, alpha, dropout_p, seed, col_sum, col_sumsq, stream);
   // tile width: whole N when it fits in one UMMA (<= 256), else 128 — rounded up to the UMMA N granule of 16
   // Tile width: at most 64 accumulator columns per CTA.  These GEMMs are short-K and memory-bound; what hides
@@ -683,7 +751,7 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   p.out = out; p.ldo = ldo; p.out_fp32 = out_fp32; p.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
   p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
   p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed;
-  p.col_sum = col_sum; p.col_sumsq = col_sumsq;
+  p.col_sum = col_sum; p.col_sumsq = col_sumsq; p.dbg = 0; p.b_resident = 0;
 
   CUtensorMap ta, tb;
   int rc;
