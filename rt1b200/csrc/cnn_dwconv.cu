@@ -27,20 +27,34 @@ __device__ __forceinline__ ChanMap make_dw_map(int C8, int chunk_idx) {
 }
 static inline int dw_chunks(int C) { return (C / 8 + DW_MAXV - 1) / DW_MAXV; }
 
-// weights [C, K, K] (torch [C,1,K,K]) → smem [K*K][c8*8] fp32 for this chunk
+// weights [C, K, K] (torch [C,1,K,K]) → smem [K*K][2][c8] float4 for this chunk: plane 0 holds channels 0-3 of every
+// channel vector, plane 1 channels 4-7, so that consecutive threads (consecutive channel vectors) read consecutive
+// float4 — conflict-free.  (With 8 consecutive floats per thread every LDS.128 was a 2-way bank conflict and, read
+// per tap and per pixel, the weights were 90 % of the kernel's L1/shared traffic: ncu showed L1/TEX at 89 % busy.)
 template <int K>
 __device__ __forceinline__ void load_dw_weights(float* wsm, const bf16* w, const ChanMap& m) {
   const int chunk0 = m.cv - (threadIdx.x % m.c8);
   const int nch = m.c8 * 8;
   for (int i = threadIdx.x; i < nch * K * K; i += blockDim.x) {
     const int c = i / (K * K), t = i % (K * K);
-    wsm[t * nch + c] = __bfloat162float(w[(size_t)(chunk0 * 8 + c) * K * K + t]);
+    wsm[((t * 2 + ((c & 7) >> 2)) * m.c8 + (c >> 3)) * 4 + (c & 3)] = __bfloat162float(w[(size_t)(chunk0 * 8 + c) * K * K + t]);
   }
   __syncthreads();
 }
+// the K taps of kernel row ky for this thread's 8 channels → registers (reused by all PX pixels of the item)
+template <int K>
+__device__ __forceinline__ void load_dw_row(const float* wsm, int c8, int cvl, int ky, float (&wk)[K][8]) {
+  const float4* w4 = reinterpret_cast<const float4*>(wsm);
+#pragma unroll
+  for (int kx = 0; kx < K; ++kx) {
+    const float4 lo = w4[((ky * K + kx) * 2 + 0) * c8 + cvl], hi = w4[((ky * K + kx) * 2 + 1) * c8 + cvl];
+    wk[kx][0] = lo.x; wk[kx][1] = lo.y; wk[kx][2] = lo.z; wk[kx][3] = lo.w;
+    wk[kx][4] = hi.x; wk[kx][5] = hi.y; wk[kx][6] = hi.z; wk[kx][7] = hi.w;
+  }
+}
 
 template <int K, int S>
-__global__ void __launch_bounds__(CNN_THREADS) dwconv_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ a_in,
+__global__ void __launch_bounds__(CNN_THREADS, 2) dwconv_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ a_in,
                                                                  const float* __restrict__ b_in, const bf16* __restrict__ w,
                                                                  bf16* __restrict__ y, float* __restrict__ sum, float* __restrict__ sumsq,
                                                                  int H, int W, int Ho, int Wo, int C) {
@@ -55,7 +69,7 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_fwd_kernel(const bf16* __r
   cta_rows(items, ib, ie);
   float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (m.active) {
-    const int nch = m.c8 * 8, cl = (threadIdx.x % m.c8) * 8;
+    const int cvl = threadIdx.x % m.c8;
     float fa[8], fb[8];
     const bool has_bn = a_in != nullptr;
     if (has_bn) {
@@ -71,11 +85,13 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_fwd_kernel(const bf16* __r
       for (int p = 0; p < DW_PX; ++p)
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[p][k] = 0.f;
-#pragma unroll
+#pragma unroll 1
       for (int ky = 0; ky < K; ++ky) {
         const int iy = oy * S - PAD + ky;
         if (iy < 0 || iy >= H) continue;
         const int ix_base = ox0 * S - PAD;
+        float wk[K][8];
+        load_dw_row<K>(wsm, m.c8, cvl, ky, wk);
 #pragma unroll
         for (int j = 0; j < NIN; ++j) {
           const int ix = ix_base + j;
@@ -90,9 +106,8 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_fwd_kernel(const bf16* __r
           for (int p = 0; p < DW_PX; ++p) {
             const int kx = j - p * S;
             if (kx >= 0 && kx < K) {
-              const float* wp = wsm + (ky * K + kx) * nch + cl;
 #pragma unroll
-              for (int k = 0; k < 8; ++k) acc[p][k] = fmaf(wp[k], v[k], acc[p][k]);
+              for (int k = 0; k < 8; ++k) acc[p][k] = fmaf(wk[kx][k], v[k], acc[p][k]);
             }
           }
         }
@@ -120,7 +135,7 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_fwd_kernel(const bf16* __r
 // dIn[n,iy,ix,c] = sum_{ky,kx} w[c,ky,kx] * dOut[n,(iy+pad-ky)/S,(ix+pad-kx)/S,c]; then (if the conv input was
 // SiLU(BN(x_raw))) multiply by SiLU'(a*x_raw+b) and accumulate the BN-backward sums over dh and dh*xhat.
 template <int K, int S>
-__global__ void __launch_bounds__(CNN_THREADS) dwconv_bwd_data_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ w,
+__global__ void __launch_bounds__(CNN_THREADS, 2) dwconv_bwd_data_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ w,
                                                                       const bf16* __restrict__ x_raw, const float* __restrict__ a_in,
                                                                       const float* __restrict__ b_in, const float* __restrict__ mean,
                                                                       const float* __restrict__ rstd, bf16* __restrict__ din,
@@ -137,7 +152,7 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_bwd_data_kernel(const bf16
   cta_rows(items, ib, ie);
   float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (m.active) {
-    const int nch = m.c8 * 8, cl = (threadIdx.x % m.c8) * 8;
+    const int cvl = threadIdx.x % m.c8;
     const bool has_bn = a_in != nullptr;
     float fa[8], fb[8], mu[8], rs[8];
     if (has_bn) {
@@ -155,7 +170,7 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_bwd_data_kernel(const bf16
       for (int p = 0; p < DW_PX; ++p)
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[p][k] = 0.f;
-#pragma unroll
+#pragma unroll 1
       for (int ky = 0; ky < K; ++ky) {
         const int t = iy + PAD - ky;
         if (t < 0 || (t % S) != 0) continue;
@@ -164,6 +179,8 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_bwd_data_kernel(const bf16
         // candidate output columns: S == 1: ox = ix0 + PAD - (K-1) + j, kx = p + K-1 - j
         //                           S == 2: ox = ix0/2 - 1 + j,         kx = p + PAD + 2 - 2j   (ix0 is a multiple of 4)
         const int ox_base = (S == 1) ? (ix0 + PAD - (K - 1)) : (ix0 / 2 - 1);
+        float wk[K][8];
+        load_dw_row<K>(wsm, m.c8, cvl, ky, wk);
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
           const int ox = ox_base + j;
@@ -174,9 +191,8 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_bwd_data_kernel(const bf16
           for (int p = 0; p < DW_PX; ++p) {
             const int kx = (S == 1) ? (p + K - 1 - j) : (p + PAD + 2 - 2 * j);
             if (kx >= 0 && kx < K) {
-              const float* wp = wsm + (ky * K + kx) * nch + cl;
 #pragma unroll
-              for (int k = 0; k < 8; ++k) acc[p][k] = fmaf(wp[k], v[k], acc[p][k]);
+              for (int k = 0; k < 8; ++k) acc[p][k] = fmaf(wk[kx][k], v[k], acc[p][k]);
             }
           }
         }

@@ -166,49 +166,64 @@ __global__ void __launch_bounds__(P2P_THREADS, 1) p2p_allreduce_adamw_kernel(P2P
     dst[p] = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(NVLS ? c.mc_param : c.param[peer]) + base_el);
   }
   const long nvec = (hi - lo) >> 3;
-  const long tile = (long)P2P_THREADS * V;
+  // Outer batch: U output vectors per thread whose U x SRC gradient loads (NVLink or in-switch reduce: the long
+  // latency) are ALL issued first — 12 to 16 loads per thread; inner batches of V vectors then fetch their fp32
+  // state from local HBM and update.
+  constexpr int INFL = SRC >= 8 ? P2P_INFLIGHT : 12;   // register budget: U x SRC x 4 + V x 24 + addressing <= 128
+  constexpr int U = (INFL / SRC) < V ? V : (INFL / SRC) / V * V;
+  const long tile = (long)P2P_THREADS * U;
   for (long t0 = (long)blockIdx.x * tile; t0 < nvec; t0 += (long)gridDim.x * tile) {
-    uint4 raw[V][SRC];
-    float4 st[V][6];
+    uint4 raw[U][SRC];
 #pragma unroll
-    for (int u = 0; u < V; ++u) {
+    for (int u = 0; u < U; ++u) {
       const long i = t0 + u * P2P_THREADS + threadIdx.x;
       if (i < nvec) {
 #pragma unroll
         for (int p = 0; p < SRC; ++p) raw[u][p] = NVLS ? mc_ld_reduce_bf16x8(src[p] + i) : ld_peer_v4(src[p] + i);
-        st[u][0] = __ldcs(master + 2 * i); st[u][1] = __ldcs(master + 2 * i + 1);
-        st[u][2] = __ldcs(m + 2 * i);      st[u][3] = __ldcs(m + 2 * i + 1);
-        st[u][4] = __ldcs(v + 2 * i);      st[u][5] = __ldcs(v + 2 * i + 1);
       }
     }
 #pragma unroll
-    for (int u = 0; u < V; ++u) {
-      const long i = t0 + u * P2P_THREADS + threadIdx.x;
-      if (i >= nvec) continue;
-      float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int u0 = 0; u0 < U; u0 += V) {
+      float4 st[V][6];
 #pragma unroll
-      for (int p = 0; p < SRC; ++p) add_bf16x8(g, raw[u][p]);
-      float pp[8] = {st[u][0].x, st[u][0].y, st[u][0].z, st[u][0].w, st[u][1].x, st[u][1].y, st[u][1].z, st[u][1].w};
-      float mm[8] = {st[u][2].x, st[u][2].y, st[u][2].z, st[u][2].w, st[u][3].x, st[u][3].y, st[u][3].z, st[u][3].w};
-      float vv[8] = {st[u][4].x, st[u][4].y, st[u][4].z, st[u][4].w, st[u][5].x, st[u][5].y, st[u][5].z, st[u][5].w};
+      for (int v_ = 0; v_ < V; ++v_) {
+        const long i = t0 + (u0 + v_) * P2P_THREADS + threadIdx.x;
+        if (i < nvec) {
+          st[v_][0] = __ldcs(master + 2 * i); st[v_][1] = __ldcs(master + 2 * i + 1);
+          st[v_][2] = __ldcs(m + 2 * i);      st[v_][3] = __ldcs(m + 2 * i + 1);
+          st[v_][4] = __ldcs(v + 2 * i);      st[v_][5] = __ldcs(v + 2 * i + 1);
+        }
+      }
 #pragma unroll
-      for (int k = 0; k < 8; ++k) adam_update(pp[k], g[k], mm[k], vv[k], h);
-      float4* mo = const_cast<float4*>(master) + 2 * i;
-      float4* m1o = const_cast<float4*>(m) + 2 * i;
-      float4* vo = const_cast<float4*>(v) + 2 * i;
-      __stcs(mo, make_float4(pp[0], pp[1], pp[2], pp[3]));
-      __stcs(mo + 1, make_float4(pp[4], pp[5], pp[6], pp[7]));
-      __stcs(m1o, make_float4(mm[0], mm[1], mm[2], mm[3]));
-      __stcs(m1o + 1, make_float4(mm[4], mm[5], mm[6], mm[7]));
-      __stcs(vo, make_float4(vv[0], vv[1], vv[2], vv[3]));
-      __stcs(vo + 1, make_float4(vv[4], vv[5], vv[6], vv[7]));
-      const bf16x8 packed = pack8(pp);
-      const uint4 pk = *reinterpret_cast<const uint4*>(&packed);
-      if (NVLS) {
-        mc_st_v4(dst[0] + i, pk);
-      } else {
+      for (int v_ = 0; v_ < V; ++v_) {
+        const int u = u0 + v_;
+        const long i = t0 + u * P2P_THREADS + threadIdx.x;
+        if (i >= nvec) continue;
+        float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
-        for (int p = 0; p < SRC; ++p) st_peer_v4(dst[p] + i, pk);
+        for (int p = 0; p < SRC; ++p) add_bf16x8(g, raw[u][p]);
+        float pp[8] = {st[v_][0].x, st[v_][0].y, st[v_][0].z, st[v_][0].w, st[v_][1].x, st[v_][1].y, st[v_][1].z, st[v_][1].w};
+        float mm[8] = {st[v_][2].x, st[v_][2].y, st[v_][2].z, st[v_][2].w, st[v_][3].x, st[v_][3].y, st[v_][3].z, st[v_][3].w};
+        float vv[8] = {st[v_][4].x, st[v_][4].y, st[v_][4].z, st[v_][4].w, st[v_][5].x, st[v_][5].y, st[v_][5].z, st[v_][5].w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) adam_update(pp[k], g[k], mm[k], vv[k], h);
+        float4* mo = const_cast<float4*>(master) + 2 * i;
+        float4* m1o = const_cast<float4*>(m) + 2 * i;
+        float4* vo = const_cast<float4*>(v) + 2 * i;
+        __stcs(mo, make_float4(pp[0], pp[1], pp[2], pp[3]));
+        __stcs(mo + 1, make_float4(pp[4], pp[5], pp[6], pp[7]));
+        __stcs(m1o, make_float4(mm[0], mm[1], mm[2], mm[3]));
+        __stcs(m1o + 1, make_float4(mm[4], mm[5], mm[6], mm[7]));
+        __stcs(vo, make_float4(vv[0], vv[1], vv[2], vv[3]));
+        __stcs(vo + 1, make_float4(vv[4], vv[5], vv[6], vv[7]));
+        const bf16x8 packed = pack8(pp);
+        const uint4 pk = *reinterpret_cast<const uint4*>(&packed);
+        if (NVLS) {
+          mc_st_v4(dst[0] + i, pk);
+        } else {
+#pragma unroll
+          for (int p = 0; p < SRC; ++p) st_peer_v4(dst[p] + i, pk);
+        }
       }
     }
   }
