@@ -398,22 +398,36 @@ __global__ void __launch_bounds__(CNN_THREADS) bn_act_bwd_kernel(const bf16* __r
       load8f(c2 + m.cv * 8, k2);
     }
     const size_t off = ((size_t)n * HW) * C + (size_t)m.cv * 8;
-    for (int r = rb + m.r0; r < re; r += m.rows_per_pass) {
-      float gg[8], f[8], o[8];
-      load8bf(g + off + (size_t)r * C, gg);
-      load8bf(x + off + (size_t)r * C, f);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float dT = fmaf(gg[k], fs[k], dp[k]);
-        const float dh = silu ? dT * silu_grad_f(fmaf(fa[k], f[k], fb[k])) : dT;
-        const float xh = (f[k] - mu[k]) * rs[k];
-        if (APPLY) o[k] = fa[k] * (dh - k1[k] - xh * k2[k]);
-        else {
-          acc1[k] += dh;
-          acc2[k] += dh * xh;
-        }
+    // two rows per trip: four 16-byte loads are in flight before the first one is consumed
+    for (int r = rb + m.r0; r < re; r += 2 * m.rows_per_pass) {
+      const int r2 = r + m.rows_per_pass;
+      const bool has2 = r2 < re;
+      bf16x8 raw[4];
+      raw[0] = *reinterpret_cast<const bf16x8*>(g + off + (size_t)r * C);
+      raw[1] = *reinterpret_cast<const bf16x8*>(x + off + (size_t)r * C);
+      if (has2) {
+        raw[2] = *reinterpret_cast<const bf16x8*>(g + off + (size_t)r2 * C);
+        raw[3] = *reinterpret_cast<const bf16x8*>(x + off + (size_t)r2 * C);
       }
-      if (APPLY) store8bf(dx + off + (size_t)r * C, o);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        if (h == 1 && !has2) break;
+        float gg[8], f[8], o[8];
+        unpack8(raw[2 * h], gg);
+        unpack8(raw[2 * h + 1], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float dT = fmaf(gg[k], fs[k], dp[k]);
+          const float dh = silu ? dT * silu_grad_f(fmaf(fa[k], f[k], fb[k])) : dT;
+          const float xh = (f[k] - mu[k]) * rs[k];
+          if (APPLY) o[k] = fa[k] * (dh - k1[k] - xh * k2[k]);
+          else {
+            acc1[k] += dh;
+            acc2[k] += dh * xh;
+          }
+        }
+        if (APPLY) store8bf(dx + off + (size_t)(h ? r2 : r) * C, o);
+      }
     }
   }
   if (!APPLY) {
