@@ -53,8 +53,14 @@ def rt1_attention(qkv, mask, p_drop: float = 0.0, seed: Optional[int] = None):
 
 
 class _TokenLearner(Function):
+    """TokenLearner as LayerNorm kernel → tcgen05 GEMM (C → 64, all frames at once) → per-frame pooling kernel; the
+    backward mirrors it (pooling backward → two GEMMs for dLN(x) and dW1 → LayerNorm backward → direct pooling term).
+    ``RT1B200_TL_FUSED=1`` selects the older one-CTA-per-frame kernels instead."""
+
     @staticmethod
     def forward(ctx, feats, ln_w, ln_b, w1, b1, w2, b2, eps, params):
+        import os
+        from .kernels import gemm
         n, P, C = feats.shape
         T = w2.shape[0]
         feats = feats if feats.is_contiguous() else feats.contiguous()
@@ -62,27 +68,68 @@ class _TokenLearner(Function):
         w2m = w2.reshape(T, -1)
         assert w1m.shape == (64, C) and w2m.shape == (T, 64), "TokenLearner kernel expects a 64-wide bottleneck"
         tokens = torch.empty(n, T, C, dtype=BF16, device=feats.device)
-        call("rt1_token_learner_fwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(tokens),
-             i64(T * C), i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
-        ctx.save_for_backward(feats, ln_w, ln_b, w1m, b1, w2m, b2)
+        fused = os.environ.get("RT1B200_TL_FUSED", "0") == "1" or C % 64 != 0 or P > 128 or T > 8
+        ctx.fused = fused
         ctx.meta = (eps, params)
+        if fused:
+            call("rt1_token_learner_fwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(tokens),
+                 i64(T * C), i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
+            ctx.save_for_backward(feats, ln_w, ln_b, w1m, b1, w2m, b2)
+            return tokens
+        rows = n * P
+        x2 = feats.view(rows, C)
+        xn = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=feats.device)
+        rstd = torch.empty_like(mean)
+        call("rt1_layernorm_fwd", ptr(x2), ptr(ln_w), ptr(ln_b), ptr(xn), ptr(mean), ptr(rstd), i32(rows), i32(C), f32(eps), stream())
+        hpre = torch.empty(rows, 64, dtype=BF16, device=feats.device)
+        gemm(xn, w1m, hpre, rows, 64, C, bias=b1)
+        wmap = torch.empty(n, P, T, dtype=torch.float32, device=feats.device)
+        call("rt1_tl_pool_fwd", ptr(feats), ptr(hpre), ptr(w2m), ptr(b2), ptr(tokens), i64(T * C), ptr(wmap), i32(n), i32(P), i32(C),
+             i32(T), stream())
+        ctx.save_for_backward(feats, ln_w, w1m, w2m, xn, mean, rstd, hpre, wmap)
         return tokens
 
     @staticmethod
     def backward(ctx, dtok):
-        from .kernels import _grad_slot, _ready
-        feats, ln_w, ln_b, w1m, b1, w2m, b2 = ctx.saved_tensors
+        from .kernels import _grad_slot, _ready, gemm
         eps, params = ctx.meta
+        dtok = dtok if dtok.is_contiguous() else dtok.contiguous()
+        g = [_grad_slot(p) for p in params]     # order: ln_w, ln_b, w1, b1, w2, b2
+        if ctx.fused:
+            feats, ln_w, ln_b, w1m, b1, w2m, b2 = ctx.saved_tensors
+            n, P, C = feats.shape
+            T = w2m.shape[0]
+            dfeats = torch.empty_like(feats)
+            ns = 64 * C + 64 + T * 64 + T + 2 * C
+            scratch = torch.empty(ns, dtype=torch.float32, device=feats.device)
+            call("rt1_token_learner_bwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(dtok),
+                 i64(T * C), ptr(dfeats), ptr(scratch), ptr(g[0]), ptr(g[1]), ptr(g[2]), ptr(g[3]), ptr(g[4]), ptr(g[5]),
+                 i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
+            _ready(params)
+            return (dfeats,) + (None,) * 8
+        from .kernels_cnn import _wgrad_gemm
+        feats, ln_w, w1m, w2m, xn, mean, rstd, hpre, wmap = ctx.saved_tensors
         n, P, C = feats.shape
         T = w2m.shape[0]
-        dtok = dtok if dtok.is_contiguous() else dtok.contiguous()
+        rows = n * P
+        dev = feats.device
+        dhpre = torch.empty(rows, 64, dtype=BF16, device=dev)
+        scratch = torch.empty(T * 64 + T, dtype=torch.float32, device=dev)
+        call("rt1_tl_pool_bwd", ptr(feats), ptr(hpre), ptr(wmap), ptr(w2m), ptr(dtok), i64(T * C), ptr(dhpre), ptr(scratch), i32(n),
+             i32(P), i32(C), i32(T), stream())
+        call("rt1_cast_f32_bf16", ptr(scratch), ptr(g[4]), i64(T * 64), stream())                      # dW2
+        call("rt1_cast_f32_bf16", ptr(scratch[T * 64:]), ptr(g[5]), i64(T), stream())                  # db2
+        call("rt1_colsum_bf16", ptr(dhpre), i64(64), i32(rows), i32(64), ptr(g[3]), stream())          # db1
+        _wgrad_gemm(dhpre, xn, params[2], 64, C, rows)                                                 # dW1 = dhpre^T · LN(x)
+        dxn = torch.empty(rows, C, dtype=BF16, device=dev)
+        gemm(dhpre, w1m, dxn, rows, C, 64, b_mn=True)                                                  # dLN(x) = dhpre · W1
         dfeats = torch.empty_like(feats)
-        ns = 64 * C + 64 + T * 64 + T + 2 * C
-        scratch = torch.empty(ns, dtype=torch.float32, device=feats.device)
-        g = [_grad_slot(p) for p in params]     # order: ln_w, ln_b, w1, b1, w2, b2
-        call("rt1_token_learner_bwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(dtok),
-             i64(T * C), ptr(dfeats), ptr(scratch), ptr(g[0]), ptr(g[1]), ptr(g[2]), ptr(g[3]), ptr(g[4]), ptr(g[5]),
-             i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
+        n_scratch = min(148, (rows + 7) // 8) * 2 * C
+        ln_scratch = torch.empty(n_scratch, dtype=torch.float32, device=dev)
+        call("rt1_layernorm_bwd", ptr(feats.view(rows, C)), ptr(ln_w), ptr(dxn), ptr(mean), ptr(rstd), ptr(dfeats), ptr(g[0]), ptr(g[1]),
+             ptr(ln_scratch), i32(rows), i32(C), stream())
+        call("rt1_tl_direct_bwd", ptr(wmap), ptr(dtok), i64(T * C), ptr(dfeats), i32(n), i32(P), i32(C), i32(T), stream())
         _ready(params)
         return (dfeats,) + (None,) * 8
 
