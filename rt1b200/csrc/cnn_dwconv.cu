@@ -223,21 +223,25 @@ __global__ void __launch_bounds__(CNN_THREADS, 2) dwconv_bwd_data_kernel(const b
   }
 }
 
-// dw[ky][kx][c] += sum over (n, oy, ox) dOut * act(x); blockIdx.z = chunk * K + ky; scratch layout [K*K][C] fp32.
+// dw[ky][kx][c] += sum over (n, oy, ox) dOut * act(x); scratch layout [K*K][C] fp32.
+// K x K taps x 8 channels do not fit in registers at a useful occupancy, so blockIdx.z = chunk * K + ky splits the kernel
+// rows over CTAs (ALLKY keeps the single-CTA variant for reference).
 template <int K, int S>
-__global__ void __launch_bounds__(CNN_THREADS) dwconv_wgrad_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ x,
-                                                                   const float* __restrict__ a_in, const float* __restrict__ b_in,
-                                                                   float* __restrict__ dw, int H, int W, int Ho, int Wo, int C) {
+__global__ void __launch_bounds__(CNN_THREADS, 2) dwconv_wgrad_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ x,
+                                                                      const float* __restrict__ a_in, const float* __restrict__ b_in,
+                                                                      float* __restrict__ dw, int H, int W, int Ho, int Wo, int C) {
   __shared__ float red[CNN_THREADS * 8];
-  const int ky = blockIdx.z % K;
-  const ChanMap m = make_dw_map(C / 8, blockIdx.z / K);
+  constexpr bool ALLKY = false;   // all 9 taps of a 3x3 in one CTA was measured: 72 accumulators force 1 CTA/SM and it ran 17 % slower
+  constexpr int NKY = ALLKY ? K : 1;
+  const int ky0 = ALLKY ? 0 : blockIdx.z % K;
+  const ChanMap m = make_dw_map(C / 8, ALLKY ? blockIdx.z : blockIdx.z / K);
   constexpr int PAD = (K - 1) / 2, NIN = (DW_PX - 1) * S + K;
   const int n = blockIdx.y, XG = (Wo + DW_PX - 1) / DW_PX, items = Ho * XG;
   int ib, ie;
   cta_rows(items, ib, ie);
-  float acc[K][8];
+  float acc[NKY * K][8];
 #pragma unroll
-  for (int q = 0; q < K; ++q)
+  for (int q = 0; q < NKY * K; ++q)
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[q][k] = 0.f;
   if (m.active) {
@@ -251,8 +255,6 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_wgrad_kernel(const bf16* _
     const bf16* g = dout + (size_t)n * Ho * Wo * C + (size_t)m.cv * 8;
     for (int it = ib + m.r0; it < ie; it += m.rows_per_pass) {
       const int oy = it / XG, ox0 = (it % XG) * DW_PX;
-      const int iy = oy * S - PAD + ky;
-      if (iy < 0 || iy >= H) continue;
       float gd[DW_PX][8];
 #pragma unroll
       for (int p = 0; p < DW_PX; ++p) {
@@ -263,28 +265,36 @@ __global__ void __launch_bounds__(CNN_THREADS) dwconv_wgrad_kernel(const bf16* _
       }
       const int ix_base = ox0 * S - PAD;
 #pragma unroll
-      for (int j = 0; j < NIN; ++j) {
-        const int ix = ix_base + j;
-        if (ix < 0 || ix >= W) continue;
-        float v[8];
-        load8bf(xin + ((size_t)iy * W + ix) * C, v);
-        if (has_bn) {
+      for (int kyi = 0; kyi < NKY; ++kyi) {
+        const int iy = oy * S - PAD + ky0 + kyi;
+        if (iy < 0 || iy >= H) continue;
 #pragma unroll
-          for (int k = 0; k < 8; ++k) v[k] = silu_f(fmaf(fa[k], v[k], fb[k]));
-        }
+        for (int j = 0; j < NIN; ++j) {
+          const int ix = ix_base + j;
+          if (ix < 0 || ix >= W) continue;
+          float v[8];
+          load8bf(xin + ((size_t)iy * W + ix) * C, v);
+          if (has_bn) {
 #pragma unroll
-        for (int p = 0; p < DW_PX; ++p) {
-          const int kx = j - p * S;
-          if (kx >= 0 && kx < K) {
+            for (int k = 0; k < 8; ++k) v[k] = silu_f(fmaf(fa[k], v[k], fb[k]));
+          }
 #pragma unroll
-            for (int k = 0; k < 8; ++k) acc[kx][k] = fmaf(gd[p][k], v[k], acc[kx][k]);
+          for (int p = 0; p < DW_PX; ++p) {
+            const int kx = j - p * S;
+            if (kx >= 0 && kx < K) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k) acc[kyi * K + kx][k] = fmaf(gd[p][k], v[k], acc[kyi * K + kx][k]);
+            }
           }
         }
       }
     }
   }
 #pragma unroll
-  for (int kx = 0; kx < K; ++kx) cta_channel_reduce_atomic(m, acc[kx], red, dw + (size_t)(ky * K + kx) * C);
+  for (int kyi = 0; kyi < NKY; ++kyi)
+#pragma unroll
+    for (int kx = 0; kx < K; ++kx)
+      cta_channel_reduce_atomic(m, acc[kyi * K + kx], red, dw + (size_t)((ky0 + kyi) * K + kx) * C);
 }
 
 // scratch [K*K][C] fp32 → weight gradient [C][K*K] bf16
@@ -365,8 +375,9 @@ RT1_API int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in,
   const int items = Ho * ((Wo + DW_PX - 1) / DW_PX);
   RT1_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)k * k * C, stream));
   int ctas = dw_items_ctas(N, items);
-  ctas = (ctas + k - 1) / k;  // K-fold more CTAs already come from the ky split
-  dim3 grid(ctas < 1 ? 1 : ctas, N, dw_chunks(C) * k);
+  const int zsplit = k;   // kernel rows split over blockIdx.z
+  ctas = (ctas + zsplit - 1) / zsplit;
+  dim3 grid(ctas < 1 ? 1 : ctas, N, dw_chunks(C) * zsplit);
   DW_DISPATCH(dwconv_wgrad_kernel, <<<grid, CNN_THREADS, 0, stream>>>((const bf16*)dout, (const bf16*)x, a_in, b_in, scratch, H, W, Ho, Wo, C));
   int rc = rt1_check_launch("rt1_dwconv_wgrad");
   if (rc) return rc;
