@@ -97,6 +97,68 @@ int rt1_fused_adamw(void* param_bf16, float* master, void* grad, int grad_is_bf1
                     long long n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
                     float bias_corr2, float grad_scale, int zero_grad, cudaStream_t stream);
 
+/* ---- TokenLearner, GEMM-composed path (reference tokenizers/token_learner.py:64-95) -------------------------------
+ * hpre [n*P,64] = LayerNorm(feats) . W1^T + b1 comes from rt1_layernorm_fwd + rt1_gemm_bf16; these finish the module:
+ * softmax over the P positions of gelu(hpre).W2^T + b2 and the weighted pooling (fwd); dwmap → softmax backward → dhpre
+ * plus dW2/db2 sums (bwd; scratch fp32 [T*64+T], zeroed by the call); dfeats += wmap.dtok (direct pooling gradient). */
+int rt1_tl_pool_fwd(const void* feats, const void* hpre, const void* w2, const void* b2, void* tokens, long long out_stride,
+                    float* wmap, int n, int P, int C, int T, cudaStream_t stream);
+int rt1_tl_pool_bwd(const void* feats, const void* hpre, const float* wmap, const void* w2, const void* dtokens,
+                    long long dtok_stride, void* dhpre, float* scratch, int n, int P, int C, int T, cudaStream_t stream);
+int rt1_tl_direct_bwd(const float* wmap, const void* dtokens, long long dtok_stride, void* dfeats, int n, int P, int C, int T,
+                      cudaStream_t stream);
+
+/* ---- image tokenizer, NHWC bf16 (reference film_efficientnet_encoder.py:142-244,272-336; film_conditioning_layer.py) ----
+ * Activations are [N, H*W, C] bf16 with C % 8 == 0; BatchNorm runs on batch statistics (training) that the PRODUCING kernel
+ * emits (sum / sumsq, fp32 [C], caller-zeroed): a = gamma*rstd, b = beta - mean*a are what consumers apply on load. */
+int rt1_bn_finalize(const float* sum, const float* sumsq, float count, const void* gamma, const void* beta, float* running_mean,
+                    float* running_var, float momentum, float eps, int training, float* a, float* b, float* mean, float* rstd,
+                    int C, cudaStream_t stream);
+/* pooled[n,c] += sum_hw SiLU(a x + b)   (squeeze of squeeze-excite; caller-zeroed) */
+int rt1_bn_act_pool(const void* x, const float* a, const float* b, float* pooled, int N, int HW, int C, cudaStream_t stream);
+/* y = act(a x + b) * s[n,c]   (s = SE scale or NULL; silu = 0 leaves the affine only) */
+int rt1_bn_act_scale(const void* x, const float* a, const float* b, const float* s, void* y, int N, int HW, int C, int silu,
+                     cudaStream_t stream);
+/* out = FiLM((a y + b) [+ skip * sd[n]])  with gamma/beta rows taken from gb[n, gb_off .. gb_off+2C) (or no FiLM when gb = NULL) */
+int rt1_block_finalize(const void* y, const float* a, const float* b, const void* skip, const float* sd, const void* gb,
+                       long long gb_stride, long long gb_off, void* out, int N, int HW, int C, cudaStream_t stream);
+int rt1_block_finalize_bwd(const void* dout, const void* y, const void* skip, const void* gb, long long gb_stride, long long gb_off,
+                           const float* sd, const float* a, const float* mean, const float* rstd, const void* gamma3,
+                           const void* beta3, float* S, float* c1, float* c2, void* dgb, void* dgamma3, void* dbeta3, void* dy,
+                           void* dskip, int N, int HW, int C, cudaStream_t stream);
+/* ds[n,c] = sum_hw g * SiLU(a x + b)   (gradient of the SE scale) */
+int rt1_se_scale_bwd_reduce(const void* g, const void* x, const float* a, const float* b, float* ds, int N, int HW, int C,
+                            cudaStream_t stream);
+/* backward of t = act(BN(x)) [* s + pooled gradient]: reduce pass (skipped when sums_ready), dgamma/dbeta, dx */
+int rt1_bn_act_bwd(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
+                   const float* s, const float* dpool, float* sums, int sums_ready, float* c1, float* c2, void* dgamma, void* dbeta,
+                   void* dx, int N, int HW, int C, int silu, cudaStream_t stream);
+/* squeeze-excite FC pair on per-frame vectors (z1, s fp32 outputs; Cs even, <= 128) and its backward + weight gradients */
+int rt1_se_fc_fwd(const float* pooled_sum, float inv_hw, const void* w1, const void* b1, const void* w2, const void* b2, float* z1,
+                  float* s, int N, int C, int Cs, cudaStream_t stream);
+int rt1_se_fc_bwd(const float* ds, const float* s, const float* z1, const float* pooled_sum, float inv_hw, const void* w1,
+                  const void* w2, float* dz2, float* dz1, float* dpooled, void* dw1, void* db1, void* dw2, void* db2, int N, int C,
+                  int Cs, cudaStream_t stream);
+/* depthwise k x k (k in {3,5}, stride in {1,2}, pad (k-1)/2): forward (+ BN statistics of the output), data gradient
+ * (x SiLU'(BN(x_raw)) + BN-backward sums when x_raw/a_in/... are given), weight gradient (scratch fp32 [k*k*C]) */
+int rt1_dwconv_fwd(const void* x, const float* a_in, const float* b_in, const void* w, void* y, float* sum, float* sumsq, int N,
+                   int H, int W, int C, int k, int stride, cudaStream_t stream);
+int rt1_dwconv_bwd_data(const void* dout, const void* w, const void* x_raw, const float* a_in, const float* b_in, const float* mean,
+                        const float* rstd, void* din, float* sums, int N, int H, int W, int C, int k, int stride,
+                        cudaStream_t stream);
+int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in, const float* b_in, float* scratch, void* dw, int N, int H,
+                     int W, int C, int k, int stride, cudaStream_t stream);
+/* stem 3x3 stride 2 on the [N,H,W,8] frames produced by rt1_preprocess_nhwc (channels 0..2 used) */
+int rt1_stem_fwd(const void* x, const void* w, void* y, float* sum, float* sumsq, int N, int H, int W, int CO, cudaStream_t stream);
+int rt1_stem_wgrad(const void* dy, const void* x, float* scratch, void* dw, int N, int H, int W, int CO, cudaStream_t stream);
+
+/* ---- synthetic Language-Table frames (replaces the TinyRenderer call of reference language_table.py:579-597 and the
+ *      crop + resize of eval/wrappers.py:88-96; oracle = the numpy restatement in rt1b200/envs/raster.py) ----------------
+ * tris fp32 [E, max_tris, 13] screen-space triangles (3 x (x,y,z) + rgb + pad), ntris int32 [E] → uint8 [E,H,W,3] */
+int rt1_raster(const float* tris, const int* ntris, int max_tris, unsigned char* out, int E, int H, int W, float bg_r, float bg_g,
+               float bg_b, cudaStream_t stream);
+int rt1_crop_resize(const unsigned char* in, float* out, int E, int H, int W, int OH, int OW, float crop, cudaStream_t stream);
+
 /* ---- NVLink / NVSwitch collectives fused with the optimizer (replaces DDP + NCCL all-reduce + Adam,
  *      reference distribute_train.py:99-110,231-238) ------------------------------------------------------------
  * Symmetric buffers: every rank allocates the same sizes in the same order and maps every peer's allocation
