@@ -9,6 +9,14 @@
 // and activates every loaded input exactly once (sliding window in registers).
 #include "cnn_common.cuh"
 
+// channel-pair kernels (cnn_dwconv2.cu): opt-in alternative (RT1B200_DW_PAIR=1), measured slower
+bool rt1_dw2_enabled();
+int rt1_dw2_fwd(const void* x, const void* w, void* y, float* sum, float* sumsq, int N, int H, int W, int C, int k, int stride,
+                cudaStream_t stream);
+int rt1_dw2_bwd_data_s1(const void* dout, const void* w, const void* x_raw, const float* a_in, const float* b_in, const float* mean,
+                        const float* rstd, void* din, float* sums, int N, int H, int W, int C, int k, cudaStream_t stream);
+int rt1_dw2_wgrad(const void* dout, const void* x, float* scratch, int N, int H, int W, int C, int k, int stride, cudaStream_t stream);
+
 #define DW_PX 4
 #define DW_MAXV 64  // channel vectors per CTA chunk
 
@@ -326,6 +334,7 @@ static int dw_items_ctas(int N, int items) {
 RT1_API int rt1_dwconv_fwd(const void* x, const float* a_in, const float* b_in, const void* w, void* y, float* sum, float* sumsq,
                            int N, int H, int W, int C, int k, int stride, cudaStream_t stream) {
   RT1_REQUIRE(C % 8 == 0, "rt1_dwconv_fwd: C=%d must be a multiple of 8", C);
+  if (a_in == nullptr && rt1_dw2_enabled()) return rt1_dw2_fwd(x, w, y, sum, sumsq, N, H, W, C, k, stride, stream);
   const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const int items = Ho * ((Wo + DW_PX - 1) / DW_PX);
   dim3 grid(dw_items_ctas(N, items), N, dw_chunks(C));
@@ -350,6 +359,8 @@ RT1_API int rt1_dwconv_bwd_data(const void* dout, const void* w, const void* x_r
                                 const float* mean, const float* rstd, void* din, float* sums, int N, int H, int W, int C, int k,
                                 int stride, cudaStream_t stream) {
   RT1_REQUIRE(C % 8 == 0, "rt1_dwconv_bwd_data: C=%d must be a multiple of 8", C);
+  if (stride == 1 && rt1_dw2_enabled())
+    return rt1_dw2_bwd_data_s1(dout, w, x_raw, a_in, b_in, mean, rstd, din, sums, N, H, W, C, k, stream);
   const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const int items = H * ((W + DW_PX - 1) / DW_PX);
   dim3 grid(dw_items_ctas(N, items), N, dw_chunks(C));
@@ -374,6 +385,12 @@ RT1_API int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in,
   const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const int items = Ho * ((Wo + DW_PX - 1) / DW_PX);
   RT1_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)k * k * C, stream));
+  if (a_in == nullptr && rt1_dw2_enabled()) {
+    int rc2 = rt1_dw2_wgrad(dout, x, scratch, N, H, W, C, k, stride, stream);
+    if (rc2) return rc2;
+    dw_wgrad_cast_kernel<<<rt1_cdiv((long)C * k * k, 256), 256, 0, stream>>>(scratch, (bf16*)dw, C, k * k);
+    return rt1_check_launch("rt1_dwconv_wgrad(cast)");
+  }
   int ctas = dw_items_ctas(N, items);
   const int zsplit = k;   // kernel rows split over blockIdx.z
   ctas = (ctas + zsplit - 1) / zsplit;
