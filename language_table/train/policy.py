@@ -34,3 +34,34 @@ class BCJaxPyPolicyRT1:
             out, self.network_state = self.model.policy_step(obs, self.network_state)
         act = out["action"][0].float().cpu().numpy() * self.action_std + self.action_mean
         return np.clip(act, -self.action_clip, self.action_clip).astype(np.float32)
+
+
+class BCJaxPyPolicy:
+    """Policy adapter for the LAVA BC baseline (the class the reference's ``eval/main.py:95`` expects; upstream it wraps a
+    Flax checkpoint, here a ``language_table.train.bc.BCAgent`` state): stacked frames + sentence embedding → model →
+    de-normalise with the stored action statistics → clip to the dataset's action range."""
+
+    def __init__(self, model, norm_info: Dict, device=None, action_clip: Optional[float] = None):
+        self.model = model.eval()
+        self.device = torch.device(device) if device is not None else next(model.parameters()).device
+        st = norm_info["action_statistics"]
+        self.mean, self.std = np.asarray(st["mean"], np.float32), np.maximum(np.asarray(st["std"], np.float32), EPS)
+        self.amin, self.amax = np.asarray(norm_info["action_min"], np.float32), np.asarray(norm_info["action_max"], np.float32)
+        self.action_clip = action_clip
+
+    @classmethod
+    def from_checkpoint(cls, model, checkpoint_path: str, device=None, **kw):
+        sd = torch.load(checkpoint_path, map_location=device or "cpu", weights_only=False)
+        model.load_state_dict(sd["params"])
+        return cls(model.to(device) if device is not None else model, sd["norm_info"], device=device, **kw)
+
+    def action(self, observation) -> np.ndarray:
+        """``observation``: history-stacked dict with ``rgb_sequence [T,H,W,3]`` in [0,1] and ``instruction_tokenized_use [T,512]``."""
+        obs = {"rgb": torch.from_numpy(np.ascontiguousarray(observation["rgb_sequence"]))[None].to(self.device, torch.float32),
+               "clip_embedding": torch.from_numpy(np.asarray(observation["instruction_tokenized_use"], np.float32))[None].to(self.device)}
+        with torch.no_grad():
+            a = self.model(obs)[0].float().cpu().numpy()
+        a = np.clip(a * self.std + self.mean, self.amin, self.amax)
+        if self.action_clip is not None:
+            a = np.clip(a, -self.action_clip, self.action_clip)
+        return a.astype(np.float32)

@@ -1,0 +1,138 @@
+"""PyTorch restatement of the vendored LAVA baseline (reference ``language_table/train``, ``common/clip_tokenizer.py``,
+``eval/main.py``).  Mirrors the reference's ``resnet_v1_test.py`` (exact parameter counts) and
+``clip_tokenizer_test.py`` (BPE behaviour, on a tiny merge table since the real one is not shipped), and adds what the
+reference never tested: network shapes, a BC training run that learns, normalisation statistics, the CLI."""
+import numpy as np
+import pytest
+import torch
+
+from language_table.common import clip_tokenizer
+from language_table.train import main as train_main
+from language_table.train import normalization
+from language_table.train import train as train_lib
+from language_table.train.configs import language_table_resnet_sim_local, language_table_sim_local
+from language_table.train.networks import lava, pixel, resnet_v1
+
+
+@pytest.mark.parametrize("name,count", [("ResNet18", 11_689_512), ("ResNet34", 21_797_672), ("ResNet50", 25_557_032),
+                                        ("ResNet101", 44_549_160), ("ResNet152", 60_192_808), ("ResNet200", 64_673_832)])
+def test_resnet_parameter_counts(name, count):
+    model = getattr(resnet_v1, name)(num_classes=1000)
+    assert sum(p.numel() for p in model.parameters()) == count
+
+
+def test_multiscale_resnet_pyramid():
+    feats = resnet_v1.MultiscaleResNet(stage_sizes=(3, 4))(torch.rand(1, 3, 224, 224))
+    assert [tuple(f.shape[1:]) for f in feats] == [(64, 112, 112), (64, 56, 56), (256, 56, 56), (512, 28, 28)]
+
+
+def _small(cfg):
+    cfg.model.dense_resnet_width, cfg.model.lava_d_model, cfg.model.lava_num_layers = 64, 32, 2
+    cfg.data_target_height, cfg.data_target_width = 64, 96
+    cfg.synthetic_data, cfg.per_device_batch_size = True, 4
+    cfg.log_loss_every_steps, cfg.checkpoint_every_steps = 10 ** 6, 5
+    return cfg
+
+
+@pytest.mark.parametrize("encoder", ["conv_maxpool", "resnet"])
+def test_sequence_lava_shapes_and_frozen_resnet(encoder):
+    cfg = _small(language_table_sim_local.get_config() if encoder == "conv_maxpool" else language_table_resnet_sim_local.get_config())
+    model = train_lib.create_model(cfg)
+    obs = {"rgb": torch.rand(2, 4, 64, 96, 3), "clip_embedding": torch.randn(2, 4, 512)}
+    out = model(obs)
+    assert out.shape == (2, 2)
+    out.sum().backward()
+    if encoder == "resnet":
+        assert all(p.grad is None for p in model.encoder.image_encoder.resnet.parameters())
+        model.train()
+        assert not model.encoder.image_encoder.resnet.training          # frozen tower keeps inference-mode BatchNorm
+
+
+def test_pixel_lang_mse_shapes():
+    model = pixel.PixelLangMSE(2, 64, 2, sequence_length=4)
+    assert model({"rgb": torch.rand(3, 4, 64, 96, 3), "clip_embedding": torch.randn(3, 4, 512)}).shape == (3, 2)
+
+
+def test_positional_codes():
+    pe = lava.positional_encoding2d(32, 5, 7)
+    assert pe.shape == (1, 35, 32) and float(pe.abs().max()) <= 1.0
+    s = lava.sinusoid_1d(6, 16)
+    assert s.shape == (1, 6, 16) and torch.allclose(s[0, 0, 0::2], torch.zeros(8)) and torch.allclose(s[0, 0, 1::2], torch.ones(8))
+
+
+def test_chan_statistics_match_numpy():
+    rng = np.random.default_rng(0)
+    data = rng.normal(2.0, 3.0, size=(1000, 4))
+    st = normalization.ChanRunningStatistics()
+    for chunk in np.array_split(data, 7):
+        st.update_running_statistics(chunk)
+    assert st.n == 1000
+    np.testing.assert_allclose(st.mean, data.mean(0), rtol=1e-10)
+    np.testing.assert_allclose(st.std, data.std(0), rtol=1e-10)
+    norm, denorm = normalization.StdNormalizer(st.mean, st.std), normalization.StdDenormalizer(st.mean, st.std)
+    np.testing.assert_allclose(denorm(norm(data[:5].astype(np.float32))), data[:5], rtol=1e-4)
+    mm = normalization.MinMaxNormalizer(data.min(0), data.max(0))
+    assert float(np.abs(mm(data)).max()) <= 1.0 + 1e-5
+    np.testing.assert_allclose(normalization.MinMaxDenormalizer(data.min(0), data.max(0))(mm(data[:5])), data[:5], rtol=1e-4, atol=1e-4)
+
+
+def test_bc_training_learns_checkpoints_and_resumes(tmp_path):
+    cfg = _small(language_table_sim_local.get_config())
+    cfg.image_photometric_distortions = False
+    cfg.num_train_steps = 12
+    out = train_lib.train(cfg, str(tmp_path), device="cpu", verbose=False)
+    assert out["steps"] == 12 and np.isfinite(out["losses"]).all()
+    assert np.mean(out["losses"][-4:]) < np.mean(out["losses"][:4])          # the BC loss goes down
+    assert train_lib.latest_checkpoint(str(tmp_path)).endswith("ckpt_12.pt")
+    cfg.num_train_steps = 14
+    again = train_lib.train(cfg, str(tmp_path), device="cpu", verbose=False)   # restores step 12, runs 2 more
+    assert again["steps"] == 14 and len(again["losses"]) == 2
+    # the evaluation-side policy adapter loads the checkpoint and acts inside the dataset's action range
+    from language_table.train.policy import BCJaxPyPolicy
+    pol = BCJaxPyPolicy.from_checkpoint(train_lib.create_model(cfg), train_lib.latest_checkpoint(str(tmp_path)), device="cpu")
+    act = pol.action({"rgb_sequence": np.random.rand(4, 64, 96, 3).astype(np.float32),
+                      "instruction_tokenized_use": np.random.randn(4, 512).astype(np.float32)})
+    assert act.shape == (2,) and np.all(act >= pol.amin - 1e-6) and np.all(act <= pol.amax + 1e-6)
+
+
+def test_train_cli(tmp_path):
+    import os
+    cfg_path = os.path.join(os.path.dirname(train_main.__file__), "configs", "language_table_sim_local.py")
+    cfg = train_main.load_config(cfg_path)
+    assert cfg.model_name == "sequence_lav_mse" and cfg.sequence_length == 4 and cfg.per_device_batch_size == 4
+
+
+def test_clip_bpe_tokenizer():
+    # tiny merge table: "pu"+"sh</w>" etc. — the real table is CLIP's 48 894 merges
+    merges = [("p", "u"), ("s", "h</w>"), ("pu", "sh</w>"), ("t", "h"), ("th", "e</w>")]
+    enc, ranks = clip_tokenizer.create_vocab(merges=merges)
+    assert len(enc) == 512 + len(merges) + 2
+    tok = clip_tokenizer.ClipTokenizer(enc, ranks)
+    ids = tok.tokenize("  Push   the RED block! ")
+    assert ids[0] == enc["push</w>"] and ids[1] == enc["the</w>"]
+    assert ids[-1] == enc["!</w>"]
+    out = clip_tokenizer.tokenize_text(["push the block", "push"], tok, vocab_size=len(enc))
+    assert out.shape == (2, 77) and out[0, 0] == len(enc) - 2 and out[1, 2] == len(enc) - 1 and out[1, 3] == 0
+
+
+def test_dataset_example_and_plan_plot(tmp_path):
+    from language_table.environments.oracles import plot
+    from language_table.examples import dataset_example
+    eps = dataset_example.main(["--episodes", "1"])
+    assert len(eps) == 1 and "rgb" in eps[0][0]
+    img = plot.plot_plan([(0.2, -0.2), (0.4, 0.0), (0.5, 0.2)], [(0.35, -0.05, 0.03)], (0.2, -0.2), (0.5, 0.2),
+                         filename=str(tmp_path / "plan.ppm"))
+    assert img.shape == (400, 400, 3) and (img == (220, 30, 30)).all(-1).any()
+    assert (tmp_path / "plan.ppm").stat().st_size > 400 * 400 * 3
+
+
+def test_lava_closed_loop_eval_entry(tmp_path):
+    """``language_table/eval/main.py``: five task families, oracle-validated resets, results.json."""
+    from language_table.eval import main as eval_main
+    cfg = _small(language_table_sim_local.get_config())
+    cfg.num_train_steps, cfg.checkpoint_every_steps = 2, 2
+    train_lib.train(cfg, str(tmp_path / "run"), device="cpu", verbose=False)
+    res = eval_main.evaluate_checkpoint(train_lib.latest_checkpoint(str(tmp_path / "run")), str(tmp_path / "eval"), cfg,
+                                        num_evals_per_reward=1, max_episode_steps=2, device="cpu")
+    assert list(res) == ["blocktoblock", "blocktoabsolutelocation", "blocktoblockrelativelocation", "blocktorelativelocation", "separate"]
+    assert all(v["episodes"] == 1 for v in res.values()) and (tmp_path / "eval" / "results.json").exists()
