@@ -26,7 +26,33 @@ from .kernels import BF16, _grad_slot, _ready, gemm
 F32 = torch.float32
 
 
+class _ZeroArena:
+    """One pre-zeroed fp32 buffer per encoder pass from which the ~200 small statistics / accumulator tensors are carved:
+    a single fill launch instead of one per tensor (they were 184 launches and 0.4 ms of a 35 ms step).  Each pass gets
+    its own arena and the views keep it alive, so buffers saved for the backward never alias a later pass."""
+
+    def __init__(self, device, numel: int = 4 << 20):
+        self.buf = torch.zeros(numel, dtype=F32, device=device)
+        self.off = 0
+
+    def take(self, shape):
+        n = 1
+        for d in shape:
+            n *= int(d)
+        n_al = (n + 63) // 64 * 64
+        if self.off + n_al > self.buf.numel():
+            return torch.zeros(*shape, dtype=F32, device=self.buf.device)
+        out = self.buf[self.off:self.off + n].view(*shape)
+        self.off += n_al
+        return out
+
+
+_ARENA = None       # set for the duration of _EncoderFn.forward / backward
+
+
 def _zeros(*shape, device):
+    if _ARENA is not None and _ARENA.buf.device == torch.device(device):
+        return _ARENA.take(shape)
     return torch.zeros(*shape, dtype=F32, device=device)
 
 
@@ -41,7 +67,7 @@ class _BN:
     def __init__(self, mod, device):
         C = mod.num_features
         self.mod = mod
-        buf = torch.zeros(6, C, dtype=F32, device=device)
+        buf = _zeros(6, C, device=device)
         self.sum, self.sumsq, self.a, self.b, self.mean, self.rstd = buf.unbind(0)
 
     def finalize(self, count: int, training: bool):
@@ -68,7 +94,7 @@ def _wgrad_gemm(g: torch.Tensor, x: torch.Tensor, param: torch.nn.Parameter, n_o
     if split == 1:
         gemm(g, x, slot.view(n_out, k_out), n_out, k_out, m_red, a_mn=True, b_mn=True)
     else:
-        acc = torch.zeros(n_out, k_out, dtype=F32, device=g.device)
+        acc = _zeros(n_out, k_out, device=g.device)
         gemm(g, x, acc, n_out, k_out, m_red, a_mn=True, b_mn=True, split_k=split)
         call("rt1_cast_f32_bf16", ptr(acc), ptr(slot), i64(acc.numel()), stream())
 
@@ -90,8 +116,10 @@ def _film_operands(enc):
 class _EncoderFn(Function):
     @staticmethod
     def forward(ctx, enc, x8, context, sd_scales, *anchors):
+        global _ARENA
         net = enc.net
         dev = x8.device
+        _ARENA = _ZeroArena(dev)
         training = enc.training
         N, H, W, _ = x8.shape
         S = []                                    # saved per-layer state for backward
@@ -204,13 +232,16 @@ class _EncoderFn(Function):
         ctx.S, ctx.gb, ctx.film_off, ctx.GB, ctx.use_early, ctx.context = S, gb, film_off, GB, use_early, context
         if training:
             enc._nbt_pending = getattr(enc, "_nbt_pending", 0) + 1
+        _ARENA = None
         return feats
 
     @staticmethod
     def backward(ctx, dfeats):
+        global _ARENA
         enc, S, gb, film_off, GB = ctx.enc, ctx.S, ctx.gb, ctx.film_off, ctx.GB
         net = enc.net
         dev = dfeats.device
+        _ARENA = _ZeroArena(dev)
         dfeats = dfeats.contiguous()
         N = dfeats.shape[0]
         dgb = torch.zeros_like(gb)
@@ -370,6 +401,7 @@ class _EncoderFn(Function):
             fl += [f._projection_add.weight, f._projection_add.bias, f._projection_mult.weight, f._projection_mult.bias]
         _ready(fl)
         ctx.S = ctx.head = ctx.stem = None
+        _ARENA = None
         return (None, None, None, None) + (None,) * (len(ctx.needs_input_grad) - 4)
 
 
