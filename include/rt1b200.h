@@ -151,6 +151,8 @@ int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in, const f
 /* stem 3x3 stride 2 on the [N,H,W,8] frames produced by rt1_preprocess_nhwc (channels 0..2 used) */
 int rt1_stem_fwd(const void* x, const void* w, void* y, float* sum, float* sumsq, int N, int H, int W, int CO, cudaStream_t stream);
 int rt1_stem_wgrad(const void* dy, const void* x, float* scratch, void* dw, int N, int H, int W, int CO, cudaStream_t stream);
+/* im2col of the stem window: cols bf16 [N*Ho*Wo, 32], column ci*9+ky*3+kx (27 used) — the stem then runs as rt1_gemm_bf16 */
+int rt1_stem_im2col(const void* x, void* cols, int N, int H, int W, cudaStream_t stream);
 
 /* ---- synthetic Language-Table frames (replaces the TinyRenderer call of reference language_table.py:579-597 and the
  *      crop + resize of eval/wrappers.py:88-96; oracle = the numpy restatement in rt1b200/envs/raster.py) ----------------

@@ -499,6 +499,47 @@ __global__ void __launch_bounds__(CNN_THREADS) stem_wgrad_kernel(const bf16* __r
       cta_channel_reduce_atomic(m, acc[ci * 3 + kx], red, scratch + (size_t)(ci * 9 + ky * 3 + kx) * CO);
 }
 
+// ---- stem as a tensor-core GEMM: im2col of the 3x3 stride-2 window -------------------------------------------------
+// x [N,H,W,8] bf16 (channels 0..2 used) → cols [N*Ho*Wo, 32] bf16, column ci*9 + ky*3 + kx (the flattening of the torch
+// weight [CO,3,3,3]); columns 27..31 are zero.  The direct kernels above run at ~7 % of DRAM bandwidth (L1-bound window
+// loads, like the depthwise kernels); 64 bytes per output pixel of extra traffic buy a K = 32 tcgen05 GEMM for the forward
+// (with the BatchNorm statistics in its epilogue) and a split-K GEMM for the weight gradient.
+__global__ void __launch_bounds__(256) stem_im2col_kernel(const bf16* __restrict__ x, bf16* __restrict__ cols, int H, int W, int Ho,
+                                                          int Wo, long total) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int ox = (int)(i % Wo), oy = (int)((i / Wo) % Ho);
+  const long n = i / ((long)Wo * Ho);
+  const bf16* xin = x + n * (long)H * W * 8;
+  __align__(16) bf16 v[32];
+#pragma unroll
+  for (int t = 0; t < 32; ++t) v[t] = __float2bfloat16_rn(0.f);
+#pragma unroll
+  for (int ky = 0; ky < 3; ++ky) {
+    const int iy = oy * 2 - 1 + ky;
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const int ix = ox * 2 - 1 + kx;
+      if (iy < 0 || iy >= H || ix < 0 || ix >= W) continue;
+      const uint2 px = *reinterpret_cast<const uint2*>(xin + ((long)iy * W + ix) * 8);   // channels 0..3
+      const bf16* c = reinterpret_cast<const bf16*>(&px);
+      v[0 * 9 + ky * 3 + kx] = c[0];
+      v[1 * 9 + ky * 3 + kx] = c[1];
+      v[2 * 9 + ky * 3 + kx] = c[2];
+    }
+  }
+  uint4* dst = reinterpret_cast<uint4*>(cols + i * 32);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) dst[q] = reinterpret_cast<const uint4*>(v)[q];
+}
+
+RT1_API int rt1_stem_im2col(const void* x, void* cols, int N, int H, int W, cudaStream_t stream) {
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const long total = (long)N * Ho * Wo;
+  stem_im2col_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>((const bf16*)x, (bf16*)cols, H, W, Ho, Wo, total);
+  return rt1_check_launch("rt1_stem_im2col");
+}
+
 RT1_API int rt1_stem_fwd(const void* x, const void* w, void* y, float* sum, float* sumsq, int N, int H, int W, int CO,
                          cudaStream_t stream) {
   RT1_REQUIRE(CO % 8 == 0 && CO <= 64, "rt1_stem_fwd: CO=%d must be a multiple of 8 and <= 64", CO);

@@ -16,6 +16,8 @@ from __future__ import annotations
 import ctypes
 from typing import List, Optional
 
+import os
+
 import torch
 from torch.autograd import Function
 
@@ -144,13 +146,24 @@ class _EncoderFn(Function):
         Ho, Wo = (H + 2 - 3) // 2 + 1, (W + 2 - 3) // 2 + 1
         stem_raw = _empty(N, Ho, Wo, C0, device=dev)
         bn0 = _BN(bn0m, dev)
-        call("rt1_stem_fwd", ptr(x8), ptr(conv0.weight), ptr(stem_raw), ptr(bn0.sum if training else None),
-             ptr(bn0.sumsq if training else None), i32(N), i32(H), i32(W), i32(C0), stream())
+        stem_cols = None
+        if os.environ.get("RT1B200_STEM_GEMM", "1") != "0":
+            # 3x3 s2 stem as im2col (K = 27 padded to 32) + tcgen05 GEMM with the BatchNorm statistics in its epilogue
+            stem_cols = _empty(N * Ho * Wo, 32, device=dev)
+            call("rt1_stem_im2col", ptr(x8), ptr(stem_cols), i32(N), i32(H), i32(W), stream())
+            w32 = torch.nn.functional.pad(conv0.weight.detach().view(C0, 27), (0, 5))
+            gemm(stem_cols, w32, stem_raw.view(N * Ho * Wo, C0), N * Ho * Wo, C0, 32,
+                 col_sum=bn0.sum if training else None, col_sumsq=bn0.sumsq if training else None)
+            if not training:
+                stem_cols = None
+        else:
+            call("rt1_stem_fwd", ptr(x8), ptr(conv0.weight), ptr(stem_raw), ptr(bn0.sum if training else None),
+                 ptr(bn0.sumsq if training else None), i32(N), i32(H), i32(W), i32(C0), stream())
         bn0.finalize(N * Ho * Wo, training)
         x = _empty(N, Ho, Wo, C0, device=dev)
         call("rt1_bn_act_scale", ptr(stem_raw), ptr(bn0.a), ptr(bn0.b), ptr(None), ptr(x), i32(N), i32(Ho * Wo), i32(C0), i32(1),
              stream())
-        ctx.stem = (x8, stem_raw, bn0)
+        ctx.stem = (x8, stem_raw, bn0, stem_cols)
         Hc, Wc = Ho, Wo
 
         # ---- MBConv blocks -------------------------------------------------------------------------------
@@ -362,7 +375,7 @@ class _EncoderFn(Function):
             dout = dxi.view(N, Hin, Win, Cin)
 
         # ---- stem ------------------------------------------------------------------------------------------
-        x8, stem_raw, bn0 = ctx.stem
+        x8, stem_raw, bn0, stem_cols = ctx.stem
         C0 = stem_raw.shape[-1]
         Hs, Ws = stem_raw.shape[1], stem_raw.shape[2]
         b0 = bn0.mod
@@ -372,9 +385,15 @@ class _EncoderFn(Function):
              ptr(sums), i32(0), ptr(c1), ptr(c2), ptr(_grad_slot(b0.weight)), ptr(_grad_slot(b0.bias)), ptr(dstem), i32(N), i32(Hs * Ws),
              i32(C0), i32(1), stream())
         conv0 = net.convNormAct0[0]
-        scratch = _empty(27 * C0, device=dev, dtype=F32)
-        call("rt1_stem_wgrad", ptr(dstem), ptr(x8), ptr(scratch), ptr(_grad_slot(conv0.weight)), i32(N), i32(x8.shape[1]),
-             i32(x8.shape[2]), i32(C0), stream())
+        if stem_cols is not None:
+            Ms = N * Hs * Ws
+            acc = _zeros(C0, 32, device=dev)
+            gemm(dstem.view(Ms, C0), stem_cols, acc, C0, 32, Ms, a_mn=True, b_mn=True, split_k=min(296, (Ms + 63) // 64))
+            _grad_slot(conv0.weight).view(C0, 27).copy_(acc[:, :27])
+        else:
+            scratch = _empty(27 * C0, device=dev, dtype=F32)
+            call("rt1_stem_wgrad", ptr(dstem), ptr(x8), ptr(scratch), ptr(_grad_slot(conv0.weight)), i32(N), i32(x8.shape[1]),
+                 i32(x8.shape[2]), i32(C0), stream())
         _ready([b0.weight, b0.bias, conv0.weight])
 
         # ---- FiLM projections: dW = dgb^T @ context, db = colsum(dgb) ---------------------------------------
