@@ -23,7 +23,7 @@ from torch.autograd import Function
 
 from . import _lib
 from ._lib import call, f32, i32, i64, ptr, stream
-from .kernels import BF16, _grad_slot, _ready, gemm
+from .kernels import BF16, _grad_slot, _ready, gemm, wgrad_lane
 
 F32 = torch.float32
 
@@ -255,6 +255,7 @@ class _EncoderFn(Function):
         net = enc.net
         dev = dfeats.device
         _ARENA = _ZeroArena(dev)
+        lane = wgrad_lane(dev)
         dfeats = dfeats.contiguous()
         N = dfeats.shape[0]
         dgb = torch.zeros_like(gb)
@@ -312,7 +313,8 @@ class _EncoderFn(Function):
             wp = blk.project[0]
             da2 = _empty(Mo, Ce, device=dev)
             gemm(dy_raw, _conv_w2d(wp), da2, Mo, Ce, Co, b_mn=True)
-            _wgrad_gemm(dy_raw, st["a2"].view(Mo, Ce), wp.weight, Co, Ce, Mo)
+            a2_ = st["a2"]
+            lane.run(lambda: _wgrad_gemm(dy_raw, a2_.view(Mo, Ce), wp.weight, Co, Ce, Mo), dy_raw, a2_)
             ready.append(wp.weight)
             # squeeze-excite
             se = blk.se
@@ -342,9 +344,13 @@ class _EncoderFn(Function):
             dwc = blk.depthwise[0]
             has_exp = blk.expand is not None
             dw_in = st["e_act"] if has_exp else x_in
-            scratch = _empty(k * k * Ce, device=dev, dtype=F32)
-            call("rt1_dwconv_wgrad", ptr(dd_raw), ptr(dw_in), ptr(None), ptr(None),
-                 ptr(scratch), ptr(_grad_slot(dwc.weight)), i32(N), i32(Hin), i32(Win), i32(Ce), i32(k), i32(s), stream())
+            dw_slot = _grad_slot(dwc.weight)
+
+            def _dw_wgrad(dd_raw=dd_raw, dw_in=dw_in, dw_slot=dw_slot, k=k, s=s, Ce=Ce, Hin=Hin, Win=Win):
+                scratch = _empty(k * k * Ce, device=dev, dtype=F32)
+                call("rt1_dwconv_wgrad", ptr(dd_raw), ptr(dw_in), ptr(None), ptr(None),
+                     ptr(scratch), ptr(dw_slot), i32(N), i32(Hin), i32(Win), i32(Ce), i32(k), i32(s), stream())
+            lane.run(_dw_wgrad, dd_raw, dw_in)
             ready.append(dwc.weight)
             dhe = _empty(Mi, Ce, device=dev)
             if has_exp:
@@ -359,7 +365,8 @@ class _EncoderFn(Function):
                 we = blk.expand[0]
                 dxi = _empty(Mi, Cin, device=dev)
                 gemm(de_raw, _conv_w2d(we), dxi, Mi, Cin, Ce, b_mn=True, residual=dskip)
-                _wgrad_gemm(de_raw, x_in.view(Mi, Cin), we.weight, Ce, Cin, Mi)
+                lane.run(lambda de_raw=de_raw, x_in=x_in, we=we: _wgrad_gemm(de_raw, x_in.view(Mi, Cin), we.weight, Ce, Cin, Mi),
+                         de_raw, x_in)
                 ready += [b1.weight, b1.bias, we.weight]
                 del de_raw
             else:
@@ -369,10 +376,12 @@ class _EncoderFn(Function):
                 if dskip is not None:
                     dxi.add_(dskip.view_as(dxi))
             del dhe, dd_raw, dy_raw, dskip
-            _ready(ready)
+            lane.block_done(ready)
             # release this block's saved activations as early as possible
             st.clear()
             dout = dxi.view(N, Hin, Win, Cin)
+
+        lane.flush()
 
         # ---- stem ------------------------------------------------------------------------------------------
         x8, stem_raw, bn0, stem_cols = ctx.stem
