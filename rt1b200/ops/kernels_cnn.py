@@ -275,7 +275,7 @@ class _EncoderFn(Function):
         wc = _conv_w2d(enc.conv1x1)
         dt = _empty(M, Ch, device=dev)
         gemm(df_raw, wc, dt, M, Ch, E, b_mn=True)
-        _wgrad_gemm(df_raw, t_act, enc.conv1x1.weight, E, Ch, M)
+        lane.run(lambda: _wgrad_gemm(df_raw, t_act, enc.conv1x1.weight, E, Ch, M), df_raw, t_act)
         sums = _empty(2, Ch, device=dev, dtype=F32)
         dh_raw = _empty(M, Ch, device=dev)
         bnm = bnh.mod
@@ -285,8 +285,8 @@ class _EncoderFn(Function):
         convh = net.convNormAct1[0]
         dx = _empty(M, Cl, device=dev)
         gemm(dh_raw, _conv_w2d(convh), dx, M, Cl, Ch, b_mn=True)
-        _wgrad_gemm(dh_raw, x_head.view(M, Cl), convh.weight, Ch, Cl, M)
-        _ready([enc.conv1x1.weight, bnm.weight, bnm.bias, convh.weight])
+        lane.run(lambda: _wgrad_gemm(dh_raw, x_head.view(M, Cl), convh.weight, Ch, Cl, M), dh_raw, x_head)
+        lane.block_done([enc.conv1x1.weight, bnm.weight, bnm.bias, convh.weight])
         del dt, dh_raw, df_raw
 
         # ---- blocks, last to first -------------------------------------------------------------------------
