@@ -139,6 +139,9 @@ int rt1_se_fc_fwd(const float* pooled_sum, float inv_hw, const void* w1, const v
 int rt1_se_fc_bwd(const float* ds, const float* s, const float* z1, const float* pooled_sum, float inv_hw, const void* w1,
                   const void* w2, float* dz2, float* dz1, float* dpooled, void* dw1, void* db1, void* dw2, void* db2, int N, int C,
                   int Cs, cudaStream_t stream);
+/* the parameter-gradient half of rt1_se_fc_bwd alone (call that one with dw1 = NULL): a leaf that can run on another stream */
+int rt1_se_wgrad(const float* dz2, const float* dz1, const float* z1, const float* pooled_sum, float inv_hw, void* dw1, void* db1,
+                 void* dw2, void* db2, int N, int C, int Cs, cudaStream_t stream);
 /* depthwise k x k (k in {3,5}, stride in {1,2}, pad (k-1)/2): forward (+ BN statistics of the output), data gradient
  * (x SiLU'(BN(x_raw)) + BN-backward sums when x_raw/a_in/... are given), weight gradient (scratch fp32 [k*k*C]) */
 int rt1_dwconv_fwd(const void* x, const float* a_in, const float* b_in, const void* w, void* y, float* sum, float* sumsq, int N,

@@ -152,6 +152,16 @@ RT1_API int rt1_se_fc_bwd(const float* ds, const float* s, const float* z1, cons
                                                                        dpooled, C, Cs);
   int rc = rt1_check_launch("rt1_se_fc_bwd");
   if (rc) return rc;
+  if (dw1 == nullptr) return 0;   // parameter gradients requested separately (rt1_se_wgrad), e.g. on another stream
+  const long total = (long)C * Cs + C + Cs;
+  se_wgrad_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>(dz2, dz1, z1, pooled_sum, inv_hw, (bf16*)dw1, (bf16*)db1, (bf16*)dw2,
+                                                           (bf16*)db2, N, C, Cs);
+  return rt1_check_launch("rt1_se_wgrad");
+}
+
+// The parameter-gradient half of rt1_se_fc_bwd on its own (pass dw1 = NULL there): a leaf of the backward graph.
+RT1_API int rt1_se_wgrad(const float* dz2, const float* dz1, const float* z1, const float* pooled_sum, float inv_hw, void* dw1,
+                         void* db1, void* dw2, void* db2, int N, int C, int Cs, cudaStream_t stream) {
   const long total = (long)C * Cs + C + Cs;
   se_wgrad_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>(dz2, dz1, z1, pooled_sum, inv_hw, (bf16*)dw1, (bf16*)db1, (bf16*)dw2,
                                                            (bf16*)db2, N, C, Cs);

@@ -328,8 +328,13 @@ class _EncoderFn(Function):
                 dpool = _empty(N, Ce, device=dev, dtype=F32)
                 sc = st["s"]
                 call("rt1_se_fc_bwd", ptr(ds), ptr(sc), ptr(st["z1"]), ptr(st["pooled"]), f32(1.0 / HWo), ptr(se.fc1.weight),
-                     ptr(se.fc2.weight), ptr(dz2), ptr(dz1), ptr(dpool), ptr(_grad_slot(se.fc1.weight)), ptr(_grad_slot(se.fc1.bias)),
-                     ptr(_grad_slot(se.fc2.weight)), ptr(_grad_slot(se.fc2.bias)), i32(N), i32(Ce), i32(Cs), stream())
+                     ptr(se.fc2.weight), ptr(dz2), ptr(dz1), ptr(dpool), ptr(None), ptr(None), ptr(None), ptr(None),
+                     i32(N), i32(Ce), i32(Cs), stream())
+                z1_, pooled_ = st["z1"], st["pooled"]
+                se_slots = [_grad_slot(q) for q in (se.fc1.weight, se.fc1.bias, se.fc2.weight, se.fc2.bias)]
+                lane.run(lambda: call("rt1_se_wgrad", ptr(dz2), ptr(dz1), ptr(z1_), ptr(pooled_), f32(1.0 / HWo), ptr(se_slots[0]),
+                                      ptr(se_slots[1]), ptr(se_slots[2]), ptr(se_slots[3]), i32(N), i32(Ce), i32(Cs), stream()),
+                         dz2, dz1, z1_, pooled_)
                 ready += [se.fc1.weight, se.fc1.bias, se.fc2.weight, se.fc2.bias]
             # BN2 + SiLU (+ SE scale, + pooled gradient)
             b2 = bn2.mod
