@@ -309,6 +309,9 @@ __device__ __forceinline__ void v2_tile_coords(int t, int n_tiles, int block_n, 
   n0 = ((mt & 1) ? n_tiles - 1 - j : j) * block_n;
 }
 
+// PLAIN = no alpha / bias / dropout / residual (every 1x1 convolution of the image tokenizer): the epilogue is
+// instruction-issue bound, so the four per-8-column feature tests are compiled out for it.
+template <bool PLAIN>
 __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a,
                                                                               const __grid_constant__ CUtensorMap tma_b,
                                                                               const __grid_constant__ CUtensorMap tma_o,
@@ -510,22 +513,22 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
           float v[8];
 #pragma unroll
           for (int k = 0; k < 8; ++k) v[k] = __uint_as_float(acc[8 * q + k]);
-          if (p.alpha != 1.f) {
+          if (!PLAIN && p.alpha != 1.f) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] *= p.alpha;
           }
-          if (p.bias != nullptr) {
+          if (!PLAIN && p.bias != nullptr) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] += s_bias[c8 + k];
           }
-          if (p.dropout_p > 0.f) {
+          if (!PLAIN && p.dropout_p > 0.f) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
               const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c8 + k));
               v[k] = rt1_hash_u32(idx, p.seed) >= thresh ? v[k] * keep_scale : 0.f;
             }
           }
-          if (p.residual != nullptr && row_ok) {
+          if (!PLAIN && p.residual != nullptr && row_ok) {
             const bf16* rr = p.residual + (long)row * p.ldr + n0 + c8;
             if (c8 + 8 <= nv && ((reinterpret_cast<uintptr_t>(rr) & 15) == 0)) {
               float r8[8];
@@ -691,7 +694,8 @@ static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, c
 
   static size_t configured = 0;
   if (smem > configured) {
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
   static int sm_count = 0;
@@ -702,7 +706,9 @@ static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, c
   }
   const long tiles = (long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn);
   const int grid = (int)(tiles < sm_count ? tiles : sm_count);
-  gemm_tcgen05_persistent_kernel<<<grid, V2_THREADS, smem, stream>>>(ta, tb, to, p);
+  const bool plain = alpha == 1.f && bias == nullptr && residual == nullptr && dropout_p <= 0.f;
+  if (plain) gemm_tcgen05_persistent_kernel<true><<<grid, V2_THREADS, smem, stream>>>(ta, tb, to, p);
+  else gemm_tcgen05_persistent_kernel<false><<<grid, V2_THREADS, smem, stream>>>(ta, tb, to, p);
   return rt1_check_launch("rt1_gemm_bf16(persistent)");
 }
 
