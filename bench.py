@@ -13,8 +13,9 @@ all-reduce + optimizer update, nothing skipped.
 Timing: W >= 3 warm-up steps; exactly K steps between CUDA events, barrier + synchronize on both sides, MAX
 over ranks; `nvidia-smi` clocks sampled during the timed region.  Two numbers:
   value      — device-resident inputs (a rotating pool of distinct batches), no host traffic in the loop;
-  e2e.value  — through the public API (`Trainer.train_step(host_batch)`): every step copies that step's batch
-               from pinned host memory and reads the step's loss back to the host.
+  e2e.value  — through the public API (`Trainer.train_step(host_batch)` + `Trainer.prefetch(next_host_batch)`, the
+               loop `Trainer.fit` runs): every step copies that step's batch from pinned host memory (on a copy
+               stream, overlapping the previous step's compute) and reads the step's loss back to the host.
 Rank 0 prints ONE JSON line.
 """
 from __future__ import annotations
@@ -190,8 +191,12 @@ def run_ours(args):
         host_loss = []
 
         def e2e_step(i):
-            loss = trainer.train_step(src.pool[i % len(src.pool)])      # pinned host → device inside the API
-            host_loss.append(float(loss))                              # device → host read of the step's loss
+            # every step: this step's batch goes pinned host → device inside the API (staged on the trainer's copy
+            # stream by the previous iteration's prefetch, like a data loader with a one-batch look-ahead — the copy
+            # itself still happens inside the timed region, once per step), and the step's loss is read back to the host
+            trainer.train_step(src.pool[i % len(src.pool)])
+            trainer.prefetch(src.pool[(i + 1) % len(src.pool)])
+            host_loss.append(trainer.read_loss())       # D2H of THIS step's loss (pinned, side stream; waits for its forward)
 
         for i in range(2):
             e2e_step(i)

@@ -178,7 +178,30 @@ class Trainer:
 
     def _to_device(self, batch):
         from ..data.dataset import to_device
+        pf = getattr(self, "_prefetched", None)
+        if pf is not None and pf[0] is batch:           # this host batch was staged by prefetch(): just order the streams
+            _, dev_batch, ev = pf
+            self._prefetched = None
+            torch.cuda.current_stream(self.device).wait_event(ev)
+            return dev_batch
         return to_device(batch, self.device)
+
+    def prefetch(self, batch):
+        """Start the host→device copy of a (pinned) host batch on a copy stream while the current step computes; the next
+        ``train_step(batch)`` with the SAME object picks the staged copy up instead of copying in line.  This is what a
+        prefetching data loader does; ``fit()`` uses it with a one-batch look-ahead."""
+        from ..data.dataset import to_device, tree_leaves
+        if self.device.type != "cuda":
+            return
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        with torch.cuda.stream(self._copy_stream):
+            dev_batch = to_device(batch, self.device)
+            ev = torch.cuda.Event()
+            ev.record(self._copy_stream)
+        for t in tree_leaves(dev_batch):
+            t.record_stream(torch.cuda.current_stream(self.device))
+        self._prefetched = (batch, dev_batch, ev)
 
     # ------------------------------------------------------------------------------------------ steps
     def train_step(self, batch) -> torch.Tensor:
@@ -187,11 +210,38 @@ class Trainer:
         self.module.train()
         lr = self.sched.get_lr()
         loss = self.module.training_step(batch, self.global_step)
+        self._stage_loss(loss)
         self.engine.begin_step(lr)
         loss.backward()
         self.engine.step(lr)
         self.global_step += 1
         return loss.detach()
+
+    def _stage_loss(self, loss: torch.Tensor):
+        """Copy the step's loss to pinned host memory on a side stream as soon as the FORWARD has produced it, so that
+        :meth:`read_loss` does not have to wait for the backward pass and the optimizer (a ``float(loss)`` on the main
+        stream does, and leaves the GPU idle while the host queues the next step)."""
+        if self.device.type != "cuda":
+            self._loss_host = loss.detach().float().reshape(1)
+            return
+        if getattr(self, "_d2h_stream", None) is None:
+            self._d2h_stream = torch.cuda.Stream(device=self.device)
+            self._loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+            self._loss_ev = torch.cuda.Event()
+        l32 = loss.detach().float().reshape(1)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._d2h_stream.wait_event(ev)
+        l32.record_stream(self._d2h_stream)
+        with torch.cuda.stream(self._d2h_stream):
+            self._loss_host.copy_(l32, non_blocking=True)
+            self._loss_ev.record(self._d2h_stream)
+
+    def read_loss(self) -> float:
+        """The last step's (rank-local) loss as a Python float: device→host read that waits for that step's forward only."""
+        if self.device.type == "cuda":
+            self._loss_ev.synchronize()
+        return float(self._loss_host[0])
 
     def _run_eval(self, loader, step_fn) -> float:
         self.module.eval()
@@ -218,8 +268,14 @@ class Trainer:
             acc = torch.zeros((), device=self.device)
             window = torch.zeros((), device=self.device)
             n = 0
-            for batch in train_loader:
+            it = iter(train_loader)
+            nxt = next(it, None)
+            while nxt is not None:
+                batch, nxt = nxt, None
                 loss = self.train_step(batch).float()
+                nxt = next(it, None)                      # the loader works while the GPU runs the step just queued
+                if nxt is not None:
+                    self.prefetch(nxt)
                 acc += loss
                 window += loss
                 n += 1
