@@ -129,6 +129,12 @@ int rt1_block_finalize_bwd(const void* dout, const void* y, const void* skip, co
 /* ds[n,c] = sum_hw g * SiLU(a x + b)   (gradient of the SE scale) */
 int rt1_se_scale_bwd_reduce(const void* g, const void* x, const float* a, const float* b, float* ds, int N, int HW, int C,
                             cudaStream_t stream);
+/* ONE pass over (g, x) for both the SE-scale gradient and the separable parts of the BatchNorm-backward sums of the same
+ * tensor: out5 fp32 [5][N][C] = ds, A1..A4 (zeroed by the call); rt1_bn_sums_from_parts combines A1..A4 with s and dpool
+ * (known only after the SE backward) into the [2,C] sums that rt1_bn_act_bwd accepts with sums_ready = 1. */
+int rt1_se_bn_bwd_reduce(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
+                         float* out5, int N, int HW, int C, cudaStream_t stream);
+int rt1_bn_sums_from_parts(const float* parts, const float* s, const float* dpool, float* sums, int N, int C, cudaStream_t stream);
 /* backward of t = act(BN(x)) [* s + pooled gradient]: reduce pass (skipped when sums_ready), dgamma/dbeta, dx */
 int rt1_bn_act_bwd(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
                    const float* s, const float* dpool, float* sums, int sums_ready, float* c1, float* c2, void* dgamma, void* dbeta,

@@ -379,6 +379,105 @@ RT1_API int rt1_se_scale_bwd_reduce(const void* g, const void* x, const float* a
   return rt1_check_launch("rt1_se_scale_bwd_reduce");
 }
 
+// ---- one pass for the SE-scale gradient AND the BatchNorm-backward sums of the same tensor ---------------------------------
+// With t = SiLU(u) * s[n,c], u = a x + b, and the pooled-gradient term dpool[n,c]:  dT = G s + dpool,  dh = dT SiLU'(u).
+// s and dpool are constant over the frame, so the sums BatchNorm's backward needs separate into per-(frame, channel) parts
+//   sum_hw dh       = s * A1 + dpool * A2        A1 = sum G SiLU'(u)        A2 = sum SiLU'(u)
+//   sum_hw dh xhat  = s * A3 + dpool * A4        A3 = sum G SiLU'(u) xhat   A4 = sum SiLU'(u) xhat
+// which can be taken in the SAME pass over (G, x) that produces ds = sum G SiLU(u) for the squeeze-excite backward —
+// before s's gradient path (SE backward → dpool) has run.  This replaces the separate reduce pass of rt1_bn_act_bwd
+// (one full read of G and x per block).  out: fp32 [5][N][C] = ds, A1, A2, A3, A4 (zeroed here).
+__global__ void __launch_bounds__(CNN_THREADS) se_bn_bwd_reduce_kernel(const bf16* __restrict__ g, const bf16* __restrict__ x,
+                                                                       const float* __restrict__ a, const float* __restrict__ b,
+                                                                       const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                       float* __restrict__ out, int N, int HW, int C) {
+  __shared__ float sm[CNN_THREADS * 8];
+  const ChanMap m = make_chan_map(C / 8);
+  const int n = blockIdx.y;
+  int rb, re;
+  cta_rows(HW, rb, re);
+  float ds[8], a1[8], a2[8], a3[8], a4[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) ds[k] = a1[k] = a2[k] = a3[k] = a4[k] = 0.f;
+  if (m.active) {
+    float fa[8], fb[8], mu[8], rs[8];
+    load8f(a + m.cv * 8, fa);
+    load8f(b + m.cv * 8, fb);
+    load8f(mean + m.cv * 8, mu);
+    load8f(rstd + m.cv * 8, rs);
+    const size_t off = ((size_t)n * HW) * C + (size_t)m.cv * 8;
+    for (int r = rb + m.r0; r < re; r += m.rows_per_pass) {
+      float gg[8], f[8];
+      load8bf(g + off + (size_t)r * C, gg);
+      load8bf(x + off + (size_t)r * C, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float u = fmaf(fa[k], f[k], fb[k]);
+        const float sg = sigmoid_f(u);
+        const float d1 = sg * (1.f + u * (1.f - sg));      // SiLU'(u)
+        const float xh = (f[k] - mu[k]) * rs[k];
+        const float gd = gg[k] * d1;
+        ds[k] = fmaf(gg[k] * u, sg, ds[k]);
+        a1[k] += gd;
+        a2[k] += d1;
+        a3[k] = fmaf(gd, xh, a3[k]);
+        a4[k] = fmaf(d1, xh, a4[k]);
+      }
+    }
+  }
+  const size_t plane = (size_t)N * C, row = (size_t)n * C;
+  cta_channel_reduce_atomic(m, ds, sm, out + row);
+  cta_channel_reduce_atomic(m, a1, sm, out + plane + row);
+  cta_channel_reduce_atomic(m, a2, sm, out + 2 * plane + row);
+  cta_channel_reduce_atomic(m, a3, sm, out + 3 * plane + row);
+  cta_channel_reduce_atomic(m, a4, sm, out + 4 * plane + row);
+}
+
+// sums[0,c] = sum_n s A1 + dpool A2 ; sums[1,c] = sum_n s A3 + dpool A4   (block (32 channels, 8 frame lanes))
+__global__ void __launch_bounds__(256) bn_sums_from_parts_kernel(const float* __restrict__ parts, const float* __restrict__ s,
+                                                                 const float* __restrict__ dpool, float* __restrict__ sums, int N, int C) {
+  __shared__ float p1[8][33], p2[8][33];
+  const int tx = threadIdx.x, ny = threadIdx.y, c = blockIdx.x * 32 + tx;
+  const size_t plane = (size_t)N * C;
+  float s1 = 0.f, s2 = 0.f;
+  if (c < C)
+    for (int n = ny; n < N; n += 8) {
+      const size_t i = (size_t)n * C + c;
+      const float sv = s[i], dp = dpool[i];
+      s1 += sv * parts[plane + i] + dp * parts[2 * plane + i];
+      s2 += sv * parts[3 * plane + i] + dp * parts[4 * plane + i];
+    }
+  p1[ny][tx] = s1;
+  p2[ny][tx] = s2;
+  __syncthreads();
+  if (ny == 0 && c < C) {
+    s1 = s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s1 += p1[k][tx];
+      s2 += p2[k][tx];
+    }
+    sums[c] = s1;
+    sums[C + c] = s2;
+  }
+}
+
+RT1_API int rt1_se_bn_bwd_reduce(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
+                                 float* out5, int N, int HW, int C, cudaStream_t stream) {
+  RT1_REQUIRE(C % 8 == 0, "rt1_se_bn_bwd_reduce: C=%d must be a multiple of 8", C);
+  RT1_CHECK_CUDA(cudaMemsetAsync(out5, 0, sizeof(float) * 5 * (size_t)N * C, stream));
+  dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
+  se_bn_bwd_reduce_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)g, (const bf16*)x, a, b, mean, rstd, out5, N, HW, C);
+  return rt1_check_launch("rt1_se_bn_bwd_reduce");
+}
+
+// parts = out5 of rt1_se_bn_bwd_reduce; s, dpool fp32 [N,C]; sums fp32 [2,C] (overwritten) → pass to rt1_bn_act_bwd with sums_ready = 1
+RT1_API int rt1_bn_sums_from_parts(const float* parts, const float* s, const float* dpool, float* sums, int N, int C,
+                                   cudaStream_t stream) {
+  bn_sums_from_parts_kernel<<<rt1_cdiv(C, 32), dim3(32, 8), 0, stream>>>(parts, s, dpool, sums, N, C);
+  return rt1_check_launch("rt1_bn_sums_from_parts");
+}
+
 // ---------------------------------------------------------------- backward of  t = act(BN(x)) [* s + pooled grad]
 // dT = G * s[n,c] + dpool[n,c];  dh = silu ? dT * SiLU'(a*x+b) : dT;  xhat = (x - mean) * rstd
 // reduce: sums[0, c] += dh, sums[1, c] += dh * xhat          apply: dX = a * (dh - c1 - xhat * c2)

@@ -321,9 +321,11 @@ class _EncoderFn(Function):
             sc = dpool = None
             if se is not None:
                 Cs = se.fc1.out_channels
-                ds = _empty(N, Ce, device=dev, dtype=F32)
-                call("rt1_se_scale_bwd_reduce", ptr(da2), ptr(st["d_raw"]), ptr(bn2.a), ptr(bn2.b), ptr(ds), i32(N), i32(HWo), i32(Ce),
-                     stream())
+                # one pass over (da2, d_raw): the SE-scale gradient ds AND the separable parts of BN2's backward sums
+                parts = _empty(5, N, Ce, device=dev, dtype=F32)
+                call("rt1_se_bn_bwd_reduce", ptr(da2), ptr(st["d_raw"]), ptr(bn2.a), ptr(bn2.b), ptr(bn2.mean), ptr(bn2.rstd),
+                     ptr(parts), i32(N), i32(HWo), i32(Ce), stream())
+                ds = parts[0]
                 dz2, dz1 = _empty(N, Ce, device=dev, dtype=F32), _empty(N, Cs, device=dev, dtype=F32)
                 dpool = _empty(N, Ce, device=dev, dtype=F32)
                 sc = st["s"]
@@ -340,9 +342,13 @@ class _EncoderFn(Function):
             b2 = bn2.mod
             sums = _empty(2, Ce, device=dev, dtype=F32)
             dd_raw = _empty(Mo, Ce, device=dev)
+            sums_ready = 0
+            if se is not None:
+                call("rt1_bn_sums_from_parts", ptr(parts), ptr(sc), ptr(dpool), ptr(sums), i32(N), i32(Ce), stream())
+                sums_ready = 1
             call("rt1_bn_act_bwd", ptr(da2), ptr(st["d_raw"]), ptr(bn2.a), ptr(bn2.b), ptr(bn2.mean), ptr(bn2.rstd), ptr(sc), ptr(dpool),
-                 ptr(sums), i32(0), ptr(c1), ptr(c2), ptr(_grad_slot(b2.weight)), ptr(_grad_slot(b2.bias)), ptr(dd_raw), i32(N), i32(HWo),
-                 i32(Ce), i32(1), stream())
+                 ptr(sums), i32(sums_ready), ptr(c1), ptr(c2), ptr(_grad_slot(b2.weight)), ptr(_grad_slot(b2.bias)), ptr(dd_raw), i32(N),
+                 i32(HWo), i32(Ce), i32(1), stream())
             ready += [b2.weight, b2.bias]
             del da2
             # depthwise conv
