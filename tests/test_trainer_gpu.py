@@ -8,11 +8,11 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _trainer(seed=0):
+def _trainer(seed=0, hw=(64, 96)):
     from rt1b200.models.factory import RT1Config
     from rt1b200.train.trainer import RT1Module, Trainer
     torch.manual_seed(seed)
-    H, W, T = 64, 96, 3
+    (H, W), T = hw, 3
     args = Namespace(height=H, width=W, seq_len=T, lr=1e-3, milestones=[], exp_name="t", log_dir="/tmp/rt1_t/logs",
                      ckpt_dir="/tmp/rt1_t/ckpt", log_every_n_steps=10 ** 9, ckpt_every_n_epochs=1, max_epochs=1)
     cfg = RT1Config.language_table(height=H, width=W, seq_len=T, num_layers=2, dropout_rate=0.0)
@@ -36,24 +36,32 @@ def test_prefetch_and_read_loss_match_inline_path():
 
 
 def test_wgrad_lane_matches_inline_gradients():
-    """Same model, same batch: weight gradients computed on the side stream equal the in-line ones."""
+    """Same model, same batch: weight gradients computed on the side stream equal the in-line ones — up to the run-to-run
+    noise of the in-line schedule itself (BatchNorm statistics are accumulated with fp32 atomics and, at this tiny test
+    size, a 26-block BatchNorm backward amplifies the last-bit differences), which is measured alongside."""
     from rt1b200.data.dataset import SyntheticBatchSource, to_device
-    src = SyntheticBatchSource(2, 3, 64, 96, pool=1, seed=2, image_dtype=torch.uint8, pin=False)
-    grads = []
-    for lane in ("1", "0"):
+    from rt1b200.ops import kernels
+    src = SyntheticBatchSource(4, 3, 96, 160, pool=1, seed=2, image_dtype=torch.uint8, pin=False)
+
+    def grads_with(lane: str):
         os.environ["RT1B200_WGRAD_STREAM"] = lane
         try:
-            from rt1b200.ops import kernels
             kernels._LANES.clear()
-            tr = _trainer(seed=3)
+            tr = _trainer(seed=3, hw=(96, 160))
             batch = to_device(src.pool[0], tr.device)
             tr.module.train()
-            loss = tr.module.training_step(batch, 0)
             tr.engine.zero_grad()
+            loss = tr.module.training_step(batch, 0)
             loss.backward()
             torch.cuda.synchronize()
-            grads.append(tr.engine.flat.grad.float().clone())
+            return tr.engine.flat.grad.float().clone()
         finally:
             os.environ.pop("RT1B200_WGRAD_STREAM", None)
-    denom = grads[1].norm().clamp_min(1e-6)
-    assert float((grads[0] - grads[1]).norm() / denom) < 2e-2          # BN statistics use fp32 atomics: not bit-identical
+            kernels._LANES.clear()
+
+    inline_a, inline_b, lane = grads_with("0"), grads_with("0"), grads_with("1")
+    assert torch.isfinite(lane).all()
+    denom = inline_a.norm().clamp_min(1e-6)
+    noise = float((inline_a - inline_b).norm() / denom)
+    diff = float((lane - inline_a).norm() / denom)
+    assert diff < max(3.0 * noise, 2e-2), (diff, noise)
