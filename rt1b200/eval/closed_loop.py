@@ -19,7 +19,9 @@ from ..envs.board import BatchedLanguageTable
 @torch.no_grad()
 def run_closed_loop(model, num_envs: int = 64, episodes: int = 1, max_episode_steps: int = 80, device="cuda", seed: int = 0,
                     action_clip: float = 0.03, image_hw=(256, 456), record_frames: bool = False, use_oracle: bool = False,
-                    block_mode=None) -> Dict:
+                    block_mode=None, graphed: bool = False) -> Dict:
+    """``graphed=True`` replays ONE captured CUDA graph per control step for the policy (``rt1b200.eval.graphed``; fixed
+    centred crop instead of the reference's per-call random pad-shift)."""
     from language_table.environments import blocks as blocks_module
     dev = torch.device(device)
     env = BatchedLanguageTable(num_envs, block_mode or blocks_module.LanguageTableBlockVariants.BLOCK_8, device=dev, seed=seed,
@@ -28,9 +30,15 @@ def run_closed_loop(model, num_envs: int = 64, episodes: int = 1, max_episode_st
     model.eval()
     successes, lengths, latencies_ms, frames = 0, [], [], []
     timing = dev.type == "cuda"
+    gp = None
+    if graphed and not use_oracle and dev.type == "cuda":
+        from .graphed import GraphedPolicy
+        gp = GraphedPolicy(model, num_envs, image_hw[0], image_hw[1], device=dev)
     for ep in range(episodes):
         env.reset()
         state = model.initial_state(num_envs, device=dev, dtype=dtype)
+        if gp is not None:
+            gp.reset()
         alive = torch.ones(num_envs, dtype=torch.bool, device=dev)
         ep_len = torch.zeros(num_envs, dtype=torch.long, device=dev)
         for t in range(max_episode_steps):
@@ -40,6 +48,8 @@ def run_closed_loop(model, num_envs: int = 64, episodes: int = 1, max_episode_st
             obs = env.observe()
             if use_oracle:
                 action = env.scripted_action(action_clip)
+            elif gp is not None:
+                action = gp.step(obs["image"], obs["natural_language_embedding"])["action"].float().clamp(-action_clip, action_clip)
             else:
                 out, state = model.policy_step({"image": obs["image"], "natural_language_embedding": obs["natural_language_embedding"]}, state)
                 action = out["action"].float().clamp(-action_clip, action_clip)

@@ -31,3 +31,30 @@ def test_batched_closed_loop_policy_and_oracle():
     assert res["episodes"] == 8 and res["step_latency_ms_p50"] > 0
     res = run_closed_loop(model, num_envs=8, episodes=1, max_episode_steps=80, device="cuda", image_hw=(128, 224), use_oracle=True)
     assert res["success_rate"] >= 0.75
+
+
+def test_graphed_policy_matches_eager_steps():
+    """One CUDA-graph replay per control step == the eager policy_step (same fixed crop), over a window roll."""
+    from rt1b200.eval.graphed import GraphedPolicy
+    from rt1b200.models import RT1Config, build_rt1
+    from rt1b200.parallel.engine import keep_bn_stats_fp32
+    torch.manual_seed(0)
+    H, W, T, B = 128, 224, 3, 4
+    model = build_rt1(RT1Config.language_table(height=H, width=W, seq_len=T, num_layers=2), eval_center_crop=True).cuda().to(torch.bfloat16)
+    keep_bn_stats_fp32(model)
+    model.eval()
+    gp = GraphedPolicy(model, B, H, W)
+    state = model.initial_state(B, device="cuda", dtype=torch.bfloat16)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    emb = torch.randn(B, 512, device="cuda", generator=g)
+    for step in range(T + 2):                              # past the point where the window starts to roll
+        img = torch.rand(B, 3, H, W, device="cuda", generator=g)
+        with torch.no_grad():
+            want, state = model.policy_step({"image": img, "natural_language_embedding": emb}, state)
+        got = gp.step(img, emb)
+        torch.cuda.synchronize()
+        assert torch.equal(got["terminate_episode"].cpu(), want["terminate_episode"].cpu()), step
+        torch.testing.assert_close(got["action"].float().cpu(), want["action"].float().cpu(), rtol=0, atol=2 * 0.2 / 255)
+    assert int(gp.state["seq_idx"][0]) == T
+    gp.reset()
+    assert int(gp.state["seq_idx"].sum()) == 0

@@ -53,6 +53,45 @@ def ours(a):
             "what": "render + crop/resize + batched policy_step + board step for all envs, per control step"}
 
 
+def graphed(a):
+    """Policy call latency, eager vs one CUDA-graph replay, at batch 1 (one robot) and at --envs."""
+    import numpy as np
+    import torch
+    from rt1b200.eval.graphed import GraphedPolicy
+    from rt1b200.models.factory import RT1Config, build_rt1
+    from rt1b200.parallel.engine import keep_bn_stats_fp32
+    torch.manual_seed(0)
+    dev = torch.device("cuda", 0)
+    model = build_rt1(RT1Config.language_table(), eval_center_crop=True).to(dev).to(torch.bfloat16)
+    keep_bn_stats_fp32(model)
+    model.eval()
+    out = {"impl": "ours-graphed", "dtype": "bf16", "control_steps": a.steps}
+
+    def time_it(fn):
+        lat = []
+        for _ in range(a.steps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record(); e1.synchronize()
+            lat.append(e0.elapsed_time(e1))
+        lat = np.asarray(lat[3:])
+        return float(np.percentile(lat, 50)), float(np.percentile(lat, 99))
+
+    for b in (1, a.envs):
+        img, emb = torch.rand(b, 3, 256, 456, device=dev), torch.randn(b, 512, device=dev)
+        state = {"s": model.initial_state(b, device=dev, dtype=torch.bfloat16)}
+
+        def eager():
+            with torch.no_grad():
+                _, state["s"] = model.policy_step({"image": img, "natural_language_embedding": emb}, state["s"])
+        gp = GraphedPolicy(model, b, 256, 456)
+        e50, e99 = time_it(eager)
+        g50, g99 = time_it(lambda: gp.step(img, emb))
+        out[f"batch{b}"] = {"eager_ms_p50": e50, "eager_ms_p99": e99, "graph_ms_p50": g50, "graph_ms_p99": g99}
+    return out
+
+
 def reference(a):
     sys.path.insert(0, os.path.join(REPO, "baseline"))
     import refenv
@@ -120,12 +159,12 @@ def raster_bench(a):
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--impl", choices=["ours", "reference", "raster"], default="ours")
+    ap.add_argument("--impl", choices=["ours", "reference", "raster", "graphed"], default="ours")
     ap.add_argument("--envs", type=int, default=64)
     ap.add_argument("--steps", type=int, default=30)
     a = ap.parse_args()
     try:
-        out = ours(a) if a.impl == "ours" else (reference(a) if a.impl == "reference" else raster_bench(a))
+        out = {"ours": ours, "reference": reference, "raster": raster_bench, "graphed": graphed}[a.impl](a)
     except Exception as e:      # noqa: BLE001
         out = {"impl": a.impl, "error": f"{type(e).__name__}: {str(e)[:400]}"}
     print(json.dumps(out), flush=True)
