@@ -57,6 +57,28 @@ def test_gemm_mn_major_operands(a_mn, b_mn, M, N, K):
     _close(out, a_l.float() @ b_l.float().t(), msg=f"gemm a_mn={a_mn} b_mn={b_mn} {M}x{N}x{K}")
 
 
+@pytest.mark.parametrize("M,N,K,stats", [(1000, 144, 24, True), (70000, 144, 24, True), (70000, 24, 144, False),
+                                         (20000, 192, 32, True), (4100, 40, 32, True), (333, 200, 72, False)])
+def test_gemm_persistent_many_tiles_stats_and_strided_output(M, N, K, stats):
+    """The persistent kernel's regimes: long tile runs per CTA, wide + narrow n-tiles (N = 128 + 16), resident weights,
+    a ragged last m-tile, BatchNorm column statistics, and an output that is a column slice of a wider buffer."""
+    k = _k()
+    a, b = _bf(M, K, seed=11), _bf(N, K, scale=1 / math.sqrt(K), seed=12)
+    ld = ((N + 7) // 8) * 8 + 16
+    wide = torch.full((M, ld), 7.0, dtype=BF, device=DEV)
+    out = wide[:, 8:8 + N]                                   # 16-byte aligned column slice, row stride ld
+    s = torch.zeros(N, device=DEV) if stats else None
+    q = torch.zeros(N, device=DEV) if stats else None
+    k.gemm(a, b, out, M, N, K, col_sum=s, col_sumsq=q)
+    y = a.float() @ b.float().t()
+    _close(out, y, msg=f"persistent {M}x{N}x{K}")
+    assert float((wide[:, :8] - 7.0).abs().max()) == 0.0 and float((wide[:, 8 + N:] - 7.0).abs().max()) == 0.0   # nothing outside
+    if stats:
+        yb = y.to(BF).float()                                # the statistics describe the stored (bf16) values
+        _close(s, yb.sum(0), rtol=1e-2, atol=0.02 * math.sqrt(M), msg="col_sum")
+        _close(q, (yb * yb).sum(0), rtol=1e-2, atol=0.02 * math.sqrt(M), msg="col_sumsq")
+
+
 def test_gemm_epilogue_bias_residual_dropout_stats_splitk():
     k = _k()
     M, N, K = 528, 512, 512
