@@ -44,6 +44,14 @@ def parse():
     p.add_argument("--model", choices=["rt1", "scaled"], default="rt1")
     p.add_argument("--backend", default="auto")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--reps", type=int, default=3,
+                   help="back-to-back repetitions of the --steps window; the MEDIAN window is reported (all are listed)")
+    p.add_argument("--ref-precision", choices=["fp32", "bf16"], default="fp32",
+                   help="reference arm only: fp32 = the reference's stock precision (what the driver runs); bf16 = the same "
+                        "unmodified training_step under torch.autocast(bfloat16) with channels_last convolutions")
+    p.add_argument("--cnn", choices=["kernels", "cudnn"], default="kernels",
+                   help="our arm only: 'cudnn' runs OUR model with the image tokenizer on stock PyTorch bf16 channels-last ops "
+                        "(cuDNN/cuBLAS) — the library number every encoder kernel family has to beat")
     return p.parse_args()
 
 
@@ -144,6 +152,26 @@ def timed_loop(step_fn, steps: int, world: int, dev):
     return max_over_ranks(e0.elapsed_time(e1), world, dev)
 
 
+def timed_reps(step_fn, steps: int, reps: int, world: int, dev):
+    """`reps` windows of exactly `steps` steps each; returns (median window ms, all windows)."""
+    wins = [timed_loop(step_fn, steps, world, dev) for _ in range(max(1, reps))]
+    return statistics.median(wins), wins
+
+
+def params_equal_across_ranks(flat_param, world: int, dev) -> bool:
+    """After training: every rank must hold bit-identical bf16 parameters (the fused reduce+update writes them to all peers)."""
+    import torch
+    if world == 1:
+        return True
+    v = flat_param.view(torch.int16).to(torch.int64)
+    idx = torch.arange(1, v.numel() + 1, device=dev, dtype=torch.int64)
+    digest = torch.stack([v.sum(), (v * (idx % 65521)).sum(), (v ^ (idx & 0x7FFF)).sum()])
+    lo, hi = digest.clone(), digest.clone()
+    torch.distributed.all_reduce(lo, op=torch.distributed.ReduceOp.MIN)
+    torch.distributed.all_reduce(hi, op=torch.distributed.ReduceOp.MAX)
+    return bool((lo == hi).all().item())
+
+
 def make_batches(batch, pool, seed, uint8: bool, pin: bool):
     from rt1b200.data.dataset import SyntheticBatchSource
     import torch
@@ -160,6 +188,8 @@ def run_ours(args):
     from rt1b200.ops import _lib
     from rt1b200.train.trainer import RT1Module, Trainer
 
+    if args.cnn == "cudnn":
+        os.environ["RT1B200_CNN_BENCH_CUDNN"] = "1"      # read by rt1b200.ops.cnn (bench/tests only)
     rank, world, local, dev = dist_setup(args)
     torch.manual_seed(0)
     targs = Namespace(height=HEIGHT, width=WIDTH, seq_len=SEQ_LEN, lr=5e-4, milestones=[50, 75, 90], exp_name="bench",
@@ -182,8 +212,8 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     launches0 = _lib.launch_count()
-    ms = timed_loop(dev_step, args.steps, world, dev)
-    launches = _lib.launch_count() - launches0
+    ms, windows = timed_reps(dev_step, args.steps, args.reps, world, dev)
+    launches = (_lib.launch_count() - launches0) // max(1, args.reps)
     clocks = sampler.stop() if rank == 0 else {}
 
     e2e = None
@@ -200,10 +230,15 @@ def run_ours(args):
 
         for i in range(2):
             e2e_step(i)
-        ms_e2e = timed_loop(e2e_step, args.steps, world, dev)
+        sampler2 = ClockSampler(local)
+        if rank == 0:
+            sampler2.start()
+        ms_e2e, windows_e2e = timed_reps(e2e_step, args.steps, args.reps, world, dev)
+        clocks_e2e = sampler2.stop() if rank == 0 else {}
         e2e = {"value": args.batch * world * args.steps / (ms_e2e / 1e3), "unit": "samples/s",
                "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-               "last_loss": host_loss[-1]}
+               "last_loss": host_loss[-1], "windows_ms": [round(w, 3) for w in windows_e2e], "clocks": clocks_e2e}
+    equal = params_equal_across_ranks(trainer.engine.flat.param, world, dev)
     if world > 1:
         torch.distributed.barrier()
     result = None
@@ -221,6 +256,8 @@ def run_ours(args):
                        "l2": "working set >> L2: rotating pool of 4 distinct input batches + GBs of activations per step",
                        "optimizer": "Adam(lr 5e-4) as fused reduce+AdamW, fp32 master weights"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "windows_ms": [round(w, 3) for w in windows], "reps": len(windows), "timing": "median of `reps` windows of `steps` steps",
+            "params_equal_across_ranks": equal, "cnn": args.cnn,
             "kernels_loaded": _lib.available(), "native_lib": os.path.relpath(_lib.LIB_PATH, REPO),
         }
     if world > 1:
@@ -284,6 +321,17 @@ def run_reference(args):
     else:
         run = lambda b: module.training_step(b, 0)   # noqa: E731
 
+    bf16 = args.ref_precision == "bf16"
+    if bf16:
+        # same unmodified training_step; what `Trainer(precision="bf16-mixed")` + channels_last would do in Lightning:
+        # fp32 parameters and Adam state, autocast to bf16 around forward/loss, NHWC convolutions
+        module.to(memory_format=torch.channels_last)
+        run_plain = run
+
+        def run(b):                                  # noqa: F811
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                return run_plain(b)
+
     def train_step(batch):
         loss = run(batch)
         opt.zero_grad(set_to_none=True)
@@ -299,7 +347,7 @@ def run_reference(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms = timed_loop(dev_step, args.steps, world, dev)
+    ms, windows = timed_reps(dev_step, args.steps, args.reps, world, dev)
     clocks = sampler.stop() if rank == 0 else {}
     e2e = None
     if not args.no_e2e:
@@ -310,22 +358,26 @@ def run_reference(args):
 
         for i in range(2):
             e2e_step(i)
-        ms_e2e = timed_loop(e2e_step, args.steps, world, dev)
+        ms_e2e, windows_e2e = timed_reps(e2e_step, args.steps, args.reps, world, dev)
         e2e = {"value": B * world * args.steps / (ms_e2e / 1e3), "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": losses[-1]}
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "last_loss": losses[-1],
+               "windows_ms": [round(w, 3) for w in windows_e2e]}
     result = None
     if rank == 0:
         result = {
             "metric": METRIC, "value": B * world * args.steps / (ms / 1e3), "unit": "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "impl": "reference",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16-autocast" if bf16 else "fp32",
+            "data": "synthetic", "impl": "reference",
             "config": {"model": "reference RT1_Lightning (unmodified, baseline/_ref)", "global_batch": B * world,
                        "per_gpu_batch": B, "seq_len": SEQ_LEN, "frames": f"{HEIGHT}x{WIDTH}",
                        "parallelism": f"dp{world}" + (" torch DDP(find_unused_parameters=True) over NCCL" if world > 1 else ""),
-                       "optimizer": "torch.optim.Adam(lr 5e-4)", "precision": "fp32 (Lightning default 32-true)",
+                       "optimizer": "torch.optim.Adam(lr 5e-4)",
+                       "precision": "bf16 autocast + channels_last (NOT the reference's stock path; like-for-like precision arm)"
+                       if bf16 else "fp32 (Lightning default 32-true)",
                        "l2": "working set >> L2"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": 0,
+            "windows_ms": [round(w, 3) for w in windows], "reps": len(windows), "timing": "median of `reps` windows of `steps` steps",
         }
     if world > 1:
         torch.distributed.barrier()

@@ -3,7 +3,8 @@
  * Conventions: every function returns 0 on success, otherwise a CUDA error code or -1 (argument/shape error) and
  * rt1_last_error() holds a message (thread-local).  All pointers are device pointers unless stated otherwise;
  * bf16 tensors are passed as void*; every launch goes to the given stream and returns without synchronising.
- * No entry point allocates device memory: scratch buffers are caller-provided (their sizes are given per call).
+ * No compute entry point allocates device memory: scratch buffers are caller-provided (their sizes are given per call).
+ * The one allocating call is rt1_symm_alloc (cudaMalloc of a peer-mappable buffer at set-up time).
  *
  * "Reference" citations name the file:line of tanhuajie/Pytorch-RT1-for-Distributed-Training whose behaviour
  * the kernel reproduces (the reference itself has no native code; it reaches these ops through ATen/cuDNN/
@@ -22,6 +23,10 @@ extern "C" {
 const char* rt1_last_error(void);
 int rt1_abi_version(void);
 int rt1_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* smem_optin);
+/* Register a caller-owned uint32 in device memory whose value is added to every dropout seed on the current device (NULL
+ * clears it).  A captured CUDA graph bakes the seeds passed by value; advancing this word from a node of the graph gives
+ * every replay fresh dropout masks (forward and backward of one replay read the same value). */
+int rt1_set_seed_epoch(const void* dev_u32);
 /* Benchmark helper: stream `bytes` of writes through `buf` (use a buffer larger than the 126 MB L2). */
 int rt1_l2_flush(void* buf, long long bytes, unsigned tag, cudaStream_t stream);
 
@@ -32,6 +37,7 @@ int rt1_l2_flush(void* buf, long long bytes, unsigned tag, cudaStream_t stream);
  * out is bf16 (out_fp32 = 0) or fp32; split_k > 1 / accumulate need fp32 `out` (atomic accumulation; zero it first).
  * col_sum / col_sumsq (optional, fp32 [N], caller-zeroed): per-column sum and sum of squares of the fp32 result
  * (BatchNorm batch statistics fused into the producing GEMM).
+ * split_k > 1 or accumulate exclude bias, residual, dropout and column statistics (rejected with an error).
  * Replaces: nn.Linear of the decoder (reference transformer.py:45-49,126,171-173) and every 1x1 convolution of
  * the image tokenizer (film_efficientnet_encoder.py:185-224,329-336; pretrained_efficientnet_encoder.py:45-51). */
 int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
@@ -91,6 +97,9 @@ int rt1_token_learner_bwd(const void* feats, const void* ln_w, const void* ln_b,
  * in [N,3,H,W] uint8|f32 -> out [N,H,W,8] bf16 NHWC with the pad-and-shift crop (one offset per batch). */
 int rt1_preprocess_nhwc(const void* in, int in_is_uint8, void* out, int N, int H, int W, int shift_h, int shift_w,
                         int pad_h, int pad_w, cudaStream_t stream);
+/* same, the (dh, dw) offset read from device memory (int32[2]) at execution time — for CUDA-graph-captured steps */
+int rt1_preprocess_nhwc_dev(const void* in, int in_is_uint8, void* out, int N, int H, int W, const int* shift_dev, int pad_h,
+                            int pad_w, cudaStream_t stream);
 
 /* ---- optimizer: flat fused AdamW (reference distribute_train.py:100 torch.optim.Adam) ---------------------- */
 int rt1_fused_adamw(void* param_bf16, float* master, void* grad, int grad_is_bf16, float* exp_avg, float* exp_avg_sq,
@@ -119,7 +128,8 @@ int rt1_bn_act_pool(const void* x, const float* a, const float* b, float* pooled
 /* y = act(a x + b) * s[n,c]   (s = SE scale or NULL; silu = 0 leaves the affine only) */
 int rt1_bn_act_scale(const void* x, const float* a, const float* b, const float* s, void* y, int N, int HW, int C, int silu,
                      cudaStream_t stream);
-/* out = FiLM((a y + b) [+ skip * sd[n]])  with gamma/beta rows taken from gb[n, gb_off .. gb_off+2C) (or no FiLM when gb = NULL) */
+/* out = FiLM([skip +] sd[n] * (a y + b)): stochastic depth ("row" mode) scales the BRANCH, the skip is added unscaled;
+ * gamma/beta rows are taken from gb[n, gb_off .. gb_off+2C) (no FiLM when gb = NULL) */
 int rt1_block_finalize(const void* y, const float* a, const float* b, const void* skip, const float* sd, const void* gb,
                        long long gb_stride, long long gb_off, void* out, int N, int HW, int C, cudaStream_t stream);
 int rt1_block_finalize_bwd(const void* dout, const void* y, const void* skip, const void* gb, long long gb_stride, long long gb_off,
@@ -157,15 +167,13 @@ int rt1_dwconv_bwd_data(const void* dout, const void* w, const void* x_raw, cons
                         cudaStream_t stream);
 int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in, const float* b_in, float* scratch, void* dw, int N, int H,
                      int W, int C, int k, int stride, cudaStream_t stream);
-/* stem 3x3 stride 2 on the [N,H,W,8] frames produced by rt1_preprocess_nhwc (channels 0..2 used) */
-int rt1_stem_fwd(const void* x, const void* w, void* y, float* sum, float* sumsq, int N, int H, int W, int CO, cudaStream_t stream);
-int rt1_stem_wgrad(const void* dy, const void* x, float* scratch, void* dw, int N, int H, int W, int CO, cudaStream_t stream);
+/* stem 3x3 stride 2 on the [N,H,W,8] frames produced by rt1_preprocess_nhwc (channels 0..2 used): */
 /* im2col of the stem window: cols bf16 [N*Ho*Wo, 32], column ci*9+ky*3+kx (27 used) — the stem then runs as rt1_gemm_bf16 */
 int rt1_stem_im2col(const void* x, void* cols, int N, int H, int W, cudaStream_t stream);
 
 /* ---- synthetic Language-Table frames (replaces the TinyRenderer call of reference language_table.py:579-597 and the
  *      crop + resize of eval/wrappers.py:88-96; oracle = the numpy restatement in rt1b200/envs/raster.py) ----------------
- * tris fp32 [E, max_tris, 13] screen-space triangles (3 x (x,y,z) + rgb + pad), ntris int32 [E] → uint8 [E,H,W,3] */
+ * tris fp32 [E, max_tris, 12] screen-space triangles (3 x (x,y,z) + rgb, stride 12 floats), ntris int32 [E] → uint8 [E,H,W,3] */
 int rt1_raster(const float* tris, const int* ntris, int max_tris, unsigned char* out, int E, int H, int W, float bg_r, float bg_g,
                float bg_b, cudaStream_t stream);
 int rt1_crop_resize(const unsigned char* in, float* out, int E, int H, int W, int OH, int OW, float crop, cudaStream_t stream);

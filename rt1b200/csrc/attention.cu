@@ -17,7 +17,9 @@ struct AttnDims {
   float scale;      // 1/sqrt(dk)
   float p_drop;
   uint32_t seed;
+  const uint32_t* seed_epoch;   // device word added to `seed` (or null), see rt1_seed_epoch_ptr()
 };
+__device__ __forceinline__ uint32_t attn_seed(const AttnDims& d) { return d.seed + (d.seed_epoch != nullptr ? __ldg(d.seed_epoch) : 0u); }
 
 __device__ __forceinline__ void load_tile(bf16* dst, const bf16* src, int S, int DK, int ld_src, int ld_dst) {
   const int vec_per_row = DK / 8;
@@ -91,7 +93,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_kernel(const bf16* __res
     for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
       const int i = p / S, j = p % S;
       const float pv = prob[i * ldp + j];
-      prob[i * ldp + j] = rt1_hash_u32(head_base + (uint32_t)p, d.seed) >= thresh ? pv * ks : 0.f;
+      prob[i * ldp + j] = rt1_hash_u32(head_base + (uint32_t)p, attn_seed(d)) >= thresh ? pv * ks : 0.f;
     }
     __syncthreads();
   }
@@ -140,7 +142,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_kernel(const bf16* __res
   for (int p = threadIdx.x; p < S * S; p += blockDim.x) {
     const int i = p / S, j = p % S;
     float g = dot_rows(go + i * ld, v + j * ld, DK);
-    if (d.p_drop > 0.f) g = rt1_hash_u32(head_base + (uint32_t)p, d.seed) >= thresh ? g * ks : 0.f;
+    if (d.p_drop > 0.f) g = rt1_hash_u32(head_base + (uint32_t)p, attn_seed(d)) >= thresh ? g * ks : 0.f;
     ds[i * ldp + j] = g;
   }
   __syncthreads();
@@ -154,7 +156,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_kernel(const bf16* __res
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int i = 0; i < S; ++i) {
       float pv = prob[i * ldp + j];
-      if (d.p_drop > 0.f) pv = rt1_hash_u32(head_base + (uint32_t)(i * S + j), d.seed) >= thresh ? pv * ks : 0.f;
+      if (d.p_drop > 0.f) pv = rt1_hash_u32(head_base + (uint32_t)(i * S + j), attn_seed(d)) >= thresh ? pv * ks : 0.f;
       float fo[8];
       unpack8(*reinterpret_cast<const bf16x8*>(go + i * ld + c * 8), fo);
 #pragma unroll
@@ -198,12 +200,8 @@ RT1_API int rt1_attention_fwd(const void* qkv, const unsigned char* mask, void* 
   RT1_REQUIRE(DK % 8 == 0 && DK <= 256 && S <= 160, "rt1_attention_fwd: unsupported S=%d dk=%d", S, DK);
   const size_t smem = attn_smem(S, DK, false);
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_attention_fwd: S=%d dk=%d needs %zu B of shared memory", S, DK, smem);
-  static size_t configured = 0;
-  if (smem > configured) {
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
-  AttnDims d{B, S, H, DK, 1.f / sqrtf((float)DK), p_drop, seed};
+  if (int rc = rt1_ensure_dyn_smem((const void*)attn_fwd_kernel, smem)) return rc;
+  AttnDims d{B, S, H, DK, 1.f / sqrtf((float)DK), p_drop, seed, p_drop > 0.f ? rt1_seed_epoch_ptr() : nullptr};
   attn_fwd_kernel<<<dim3(H, B), ATT_THREADS, smem, stream>>>((const bf16*)qkv, mask, (bf16*)out, d);
   return rt1_check_launch("rt1_attention_fwd");
 }
@@ -213,23 +211,20 @@ RT1_API int rt1_attention_bwd(const void* qkv, const unsigned char* mask, const 
   RT1_REQUIRE(DK % 8 == 0 && DK <= 256 && S <= 160, "rt1_attention_bwd: unsupported S=%d dk=%d", S, DK);
   const size_t smem = attn_smem(S, DK, true);
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_attention_bwd: S=%d dk=%d needs %zu B of shared memory", S, DK, smem);
-  static size_t configured = 0;
-  if (smem > configured) {
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
-  AttnDims d{B, S, H, DK, 1.f / sqrtf((float)DK), p_drop, seed};
+  if (int rc = rt1_ensure_dyn_smem((const void*)attn_bwd_kernel, smem)) return rc;
+  AttnDims d{B, S, H, DK, 1.f / sqrtf((float)DK), p_drop, seed, p_drop > 0.f ? rt1_seed_epoch_ptr() : nullptr};
   attn_bwd_kernel<<<dim3(H, B), ATT_THREADS, smem, stream>>>((const bf16*)qkv, mask, (const bf16*)dout, (bf16*)dqkv, d);
   return rt1_check_launch("rt1_attention_bwd");
 }
 
 // dropout mask re-application for the backward of a GEMM-epilogue dropout: out = keep ? in/(1-p) : 0
 __global__ void dropout_apply_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, long n, uint32_t thresh, float ks,
-                                     uint32_t seed) {
+                                     uint32_t seed, const uint32_t* seed_epoch) {
+  if (seed_epoch != nullptr) seed += __ldg(seed_epoch);
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = rt1_hash_u32((uint32_t)i, seed) >= thresh ? __float2bfloat16_rn(__bfloat162float(in[i]) * ks) : __float2bfloat16_rn(0.f);
 }
 RT1_API int rt1_dropout_apply(const void* in, void* out, long long n, float p, unsigned seed, cudaStream_t stream) {
-  dropout_apply_kernel<<<rt1_cdiv(n, 256), 256, 0, stream>>>((const bf16*)in, (bf16*)out, n, rt1_drop_threshold(p), 1.f / (1.f - p), seed);
+  dropout_apply_kernel<<<rt1_cdiv(n, 256), 256, 0, stream>>>((const bf16*)in, (bf16*)out, n, rt1_drop_threshold(p), 1.f / (1.f - p), seed, rt1_seed_epoch_ptr());
   return rt1_check_launch("rt1_dropout_apply");
 }

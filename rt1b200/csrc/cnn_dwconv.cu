@@ -1,312 +1,342 @@
-// Depthwise k x k convolution (k in {3,5}, stride in {1,2}, padding (k-1)/2) and the 3x3 s2 stem convolution in NHWC
-// bf16 (replaces cuDNN depthwise fprop/dgrad/wgrad of K2, K4).
+// Depthwise k x k convolution (k in {3,5}, stride in {1,2}, padding (k-1)/2) in NHWC bf16: forward, data gradient and
+// weight gradient as ONE tile kernel family (replaces cuDNN's depthwise fprop/dgrad/wgrad behind
+// film_efficientnet_encoder.py:198-208 of the reference).
 //
-// Fusion: the BatchNorm + SiLU of the *producer* (expand conv) is applied while loading — the activated expand
-// tensor never exists in HBM — and the per-channel sum / sum-of-squares the *next* BatchNorm needs are emitted
-// from the epilogue.  The backward-data kernel likewise multiplies by SiLU'(BN(x)) and emits the BN-backward sums.
-// Thread mapping is channel-stationary (cnn_common.cuh) with channel chunks of <= 64 vectors so the chunk's
-// k*k*C weights sit in shared memory; each thread produces PX = 4 neighbouring pixels of a row for its 8 channels
-// and activates every loaded input exactly once (sliding window in registers).
+// Design (sm_100a):
+//   * A CTA walks a contiguous run of work items (channel chunk of <= 64 channels, frame, 16-wide spatial tile).  The
+//     item's source tile INCLUDING its halo is fetched by one 4-D TMA box load (cp.async.bulk.tensor.4d) into shared
+//     memory; coordinates outside the image arrive as zeros, which is the convolution's padding — no bounds tests in the
+//     inner loop.  Two stages: the load of item i+1 is in flight while item i is computed.
+//   * lane = channel pair, warp = position inside the tile.  A thread owns a PX x PY block of destination pixels for two
+//     channels; it reads every source row of its footprint ONCE (one conflict-free 4-byte LDS per pixel: the 32 lanes of a
+//     warp read 32 consecutive words) and uses it for all PY x K row/tap combinations, so a source element costs one
+//     shared-memory read per thread instead of K reads through L1 (the round-1 kernels were L1/TEX-bound at 4-7 % of
+//     DRAM bandwidth).  All tap indices are compile-time after unrolling.
+//   * the two channels of a thread are the two halves of a packed fp32 pair: every multiply-add is one FFMA2
+//     (fma.rn.f32x2), the only way to reach the full fp32 rate on sm_100 (a 3-register FFMA issues every other cycle).
+//   * fusions: BatchNorm+SiLU of the producer can be applied to the tile in shared memory (each source element once per
+//     CTA, zero padding re-imposed afterwards); the forward emits the per-channel sum / sum of squares the next
+//     BatchNorm needs; the data gradient multiplies by SiLU'(BN(x)) and emits the BatchNorm-backward sums; the weight
+//     gradient keeps its K*K accumulators in registers across all items of a chunk.
 #include "cnn_common.cuh"
+#include "sm100.cuh"
 
-// channel-pair kernels (cnn_dwconv2.cu): opt-in alternative (RT1B200_DW_PAIR=1), measured slower
-bool rt1_dw2_enabled();
-int rt1_dw2_fwd(const void* x, const void* w, void* y, float* sum, float* sumsq, int N, int H, int W, int C, int k, int stride,
-                cudaStream_t stream);
-int rt1_dw2_bwd_data_s1(const void* dout, const void* w, const void* x_raw, const float* a_in, const float* b_in, const float* mean,
-                        const float* rstd, void* din, float* sums, int N, int H, int W, int C, int k, cudaStream_t stream);
-int rt1_dw2_wgrad(const void* dout, const void* x, float* scratch, int N, int H, int W, int C, int k, int stride, cudaStream_t stream);
+using namespace sm100;
 
-#define DW_PX 4
-#define DW_MAXV 64  // channel vectors per CTA chunk
+namespace {
 
-__device__ __forceinline__ ChanMap make_dw_map(int C8, int chunk_idx) {
-  ChanMap m;
-  const int nchunks = (C8 + DW_MAXV - 1) / DW_MAXV;
-  int c8 = (C8 + nchunks - 1) / nchunks;
-  const int chunk0 = chunk_idx * c8;
-  c8 = min(c8, C8 - chunk0);
-  m.c8 = c8;
-  m.rows_per_pass = CNN_THREADS / c8;
-  m.active = (int)threadIdx.x < m.rows_per_pass * c8;
-  m.cv = chunk0 + threadIdx.x % c8;
-  m.r0 = threadIdx.x / c8;
-  return m;
+typedef unsigned long long f2;  // two fp32 values (channels c, c+1) in one 64-bit register pair
+
+__device__ __forceinline__ f2 f2_pack(float lo, float hi) {
+  f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
 }
-static inline int dw_chunks(int C) { return (C / 8 + DW_MAXV - 1) / DW_MAXV; }
+__device__ __forceinline__ void f2_unpack(f2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f2 f2_fma(f2 a, f2 b, f2 c) {
+  f2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f2 f2_add(f2 a, f2 b) {
+  f2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// bf16x2 word (low half = even channel) → packed fp32 pair: two ALU ops, no conversion instruction
+__device__ __forceinline__ f2 bf2_to_f2(uint32_t u) { return f2_pack(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u)); }
+__device__ __forceinline__ uint32_t f2_to_bf2(float lo, float hi) {
+  const bf162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
 
-// weights [C, K, K] (torch [C,1,K,K]) → smem [K*K][2][c8] float4 for this chunk: plane 0 holds channels 0-3 of every
-// channel vector, plane 1 channels 4-7, so that consecutive threads (consecutive channel vectors) read consecutive
-// float4 — conflict-free.  (With 8 consecutive floats per thread every LDS.128 was a 2-way bank conflict and, read
-// per tap and per pixel, the weights were 90 % of the kernel's L1/shared traffic: ncu showed L1/TEX at 89 % busy.)
-template <int K>
-__device__ __forceinline__ void load_dw_weights(float* wsm, const bf16* w, const ChanMap& m) {
-  const int chunk0 = m.cv - (threadIdx.x % m.c8);
-  const int nch = m.c8 * 8;
-  for (int i = threadIdx.x; i < nch * K * K; i += blockDim.x) {
-    const int c = i / (K * K), t = i % (K * K);
-    wsm[((t * 2 + ((c & 7) >> 2)) * m.c8 + (c >> 3)) * 4 + (c & 3)] = __bfloat162float(w[(size_t)(chunk0 * 8 + c) * K * K + t]);
+enum { DW_FWD = 0, DW_BWD = 1, DW_WGRAD = 2 };
+
+// Geometry of one instantiation.  "Destination" pixels are what a thread holds in registers (forward: outputs; data
+// gradient: input gradients; weight gradient: the output gradients it multiplies with), "source" is the haloed tile.
+template <int K, int S, int MODE>
+struct DwGeom {
+  static constexpr int PAD = (K - 1) / 2;
+  static constexpr int QLO = PAD / 2;  // data gradient, stride 2: source rows below destination row / 2
+  static constexpr int PX = 4;
+  static constexpr int PY = (S == 2 && MODE != DW_BWD) ? 2 : 4;
+  static constexpr int POSX = 4, POSY = 2;  // 8 warps
+  static constexpr int TX = PX * POSX, TY = PY * POSY;
+  static constexpr int QX = MODE == DW_BWD ? (S == 1 ? PX + K - 1 : PX / 2 + PAD) : (PX - 1) * S + K;
+  static constexpr int QY = MODE == DW_BWD ? (S == 1 ? PY + K - 1 : PY / 2 + PAD) : (PY - 1) * S + K;
+  static constexpr int STEPX = MODE == DW_BWD ? (S == 1 ? PX : PX / 2) : PX * S;
+  static constexpr int STEPY = MODE == DW_BWD ? (S == 1 ? PY : PY / 2) : PY * S;
+  static constexpr int SX = (POSX - 1) * STEPX + QX, SY = (POSY - 1) * STEPY + QY;
+  // kernel tap that links destination offset p and source offset q of a thread (valid iff in [0, K))
+  __host__ __device__ static constexpr int tap(int p, int q) {
+    return MODE == DW_BWD ? (S == 1 ? p + K - 1 - q : p + PAD + 2 * QLO - 2 * q) : q - S * p;
+  }
+  // source coordinate of the tile origin for destination tile origin d0 (d0 is a multiple of TX / TY, hence even)
+  __host__ __device__ static constexpr int src0(int d0) { return MODE == DW_BWD ? (S == 1 ? d0 - PAD : d0 / 2 - QLO) : d0 * S - PAD; }
+};
+
+struct DwParams {
+  const bf16* w;           // [C][K][K]
+  bf16* dst;               // forward: y [N,DH,DW,C]; data gradient: din [N,DH,DW,C]
+  const float* a_in;       // forward / weight gradient: BN scale of the producer, applied with SiLU to the source tile (or null)
+  const float* b_in;       // data gradient: BN scale/shift of the tensor whose SiLU' multiplies the result (or null)
+  const float* mean;       // data gradient with BN
+  const float* rstd;
+  float* s1;               // forward: sum; data gradient: sum dh            (fp32 [C], caller-zeroed, or null)
+  float* s2;               // forward: sum of squares; data gradient: sum dh*xhat
+  float* dw;               // weight gradient: fp32 [K*K][C], zeroed by the host wrapper
+  int N, C, SH, SW, DH, DW;  // source / destination spatial sizes
+  int tiles_x, tiles_y, cw, cww;
+  int items, per_cta;
+  int src_bytes, aux_bytes, src_region, aux_region;
+};
+
+constexpr int DW_THREADS = 256;
+
+template <int K, int S, int MODE, int CWW>
+__global__ void __launch_bounds__(DW_THREADS, (K == 3 && MODE != DW_BWD) ? 3 : 2)
+dw_tile_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constant__ CUtensorMap aux_map, const DwParams p) {
+  using G = DwGeom<K, S, MODE>;
+  constexpr int PX = G::PX, PY = G::PY, QX = G::QX, QY = G::QY, SX = G::SX, TX = G::TX, TY = G::TY;
+  extern __shared__ __align__(128) uint8_t dw_dyn[];
+  __shared__ __align__(8) uint64_t full_bar[2];
+  __shared__ float red[8 * 32 * 2 * (MODE == DW_WGRAD ? K : 2)];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int posx = warp % G::POSX, posy = warp / G::POSX;
+  const int cww = CWW ? CWW : p.cww;
+  uint8_t* const base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dw_dyn) + 127) & ~(uintptr_t)127);
+  const int stage_bytes = p.src_region + p.aux_region;
+
+  const int it0 = blockIdx.x * p.per_cta, it1 = min(p.items, it0 + p.per_cta);
+  if (it0 >= it1) return;
+  if (tid == 0) {
+    mbar_init(smem_u32(&full_bar[0]), 1);
+    mbar_init(smem_u32(&full_bar[1]), 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&src_map);
+    if (p.aux_bytes) tma_prefetch_desc(&aux_map);
   }
   __syncthreads();
-}
-// the K taps of kernel row ky for this thread's 8 channels → registers (reused by all PX pixels of the item)
-template <int K>
-__device__ __forceinline__ void load_dw_row(const float* wsm, int c8, int cvl, int ky, float (&wk)[K][8]) {
-  const float4* w4 = reinterpret_cast<const float4*>(wsm);
-#pragma unroll
-  for (int kx = 0; kx < K; ++kx) {
-    const float4 lo = w4[((ky * K + kx) * 2 + 0) * c8 + cvl], hi = w4[((ky * K + kx) * 2 + 1) * c8 + cvl];
-    wk[kx][0] = lo.x; wk[kx][1] = lo.y; wk[kx][2] = lo.z; wk[kx][3] = lo.w;
-    wk[kx][4] = hi.x; wk[kx][5] = hi.y; wk[kx][6] = hi.z; wk[kx][7] = hi.w;
-  }
-}
 
-template <int K, int S>
-__global__ void __launch_bounds__(CNN_THREADS, 2) dwconv_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ a_in,
-                                                                 const float* __restrict__ b_in, const bf16* __restrict__ w,
-                                                                 bf16* __restrict__ y, float* __restrict__ sum, float* __restrict__ sumsq,
-                                                                 int H, int W, int Ho, int Wo, int C) {
-  extern __shared__ float dyn_sm[];
-  float* wsm = dyn_sm;                       // [K*K][c8*8]
-  float* red = dyn_sm + K * K * DW_MAXV * 8;  // CNN_THREADS * 8
-  const ChanMap m = make_dw_map(C / 8, blockIdx.z);
-  load_dw_weights<K>(wsm, w, m);
-  constexpr int PAD = (K - 1) / 2, NIN = (DW_PX - 1) * S + K;
-  const int n = blockIdx.y, XG = (Wo + DW_PX - 1) / DW_PX, items = Ho * XG;
-  int ib, ie;
-  cta_rows(items, ib, ie);
-  float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (m.active) {
-    const int cvl = threadIdx.x % m.c8;
-    float fa[8], fb[8];
-    const bool has_bn = a_in != nullptr;
-    if (has_bn) {
-      load8f(a_in + m.cv * 8, fa);
-      load8f(b_in + m.cv * 8, fb);
-    }
-    const bf16* xin = x + (size_t)n * H * W * C + (size_t)m.cv * 8;
-    bf16* yout = y + (size_t)n * Ho * Wo * C + (size_t)m.cv * 8;
-    for (int it = ib + m.r0; it < ie; it += m.rows_per_pass) {
-      const int oy = it / XG, ox0 = (it % XG) * DW_PX;
-      float acc[DW_PX][8];
+  auto issue = [&](int it, int stage) {
+    const int tx = it % p.tiles_x;
+    int r = it / p.tiles_x;
+    const int ty = r % p.tiles_y;
+    r /= p.tiles_y;
+    const int n = r % p.N, chunk = r / p.N;
+    const uint32_t bar = smem_u32(&full_bar[stage]);
+    const uint32_t dst = smem_u32(base + (size_t)stage * stage_bytes);
+    fence_proxy_async();
+    mbar_expect_tx(bar, (uint32_t)(p.src_bytes + p.aux_bytes));
+    tma_load_4d(dst, &src_map, bar, chunk * p.cw, G::src0(tx * TX), G::src0(ty * TY), n);
+    if (p.aux_bytes) tma_load_4d(dst + p.src_region, &aux_map, bar, chunk * p.cw, tx * TX, ty * TY, n);
+  };
+  if (tid == 0) issue(it0, 0);
+
+  // per-chunk thread state
+  f2 w[K][K];                       // forward / data gradient: taps of this lane's channel pair; weight gradient: accumulators
+  f2 pa = 0, pb = 0, pmu = 0, prs = 0;   // BN constants of the lane's channel pair
+  f2 st1 = 0, st2 = 0;              // running statistics of the chunk
+  int cur_chunk = -1, c_lo = 0;     // c_lo = first channel of this lane
+  bool chan_ok = false;
+
+  auto flush = [&]() {
+    // combine the 8 warps (= positions) that share a channel pair, then one atomic per channel (and tap)
+    if (MODE == DW_WGRAD) {
 #pragma unroll
-      for (int p = 0; p < DW_PX; ++p)
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[p][k] = 0.f;
-#pragma unroll 1
       for (int ky = 0; ky < K; ++ky) {
-        const int iy = oy * S - PAD + ky;
-        if (iy < 0 || iy >= H) continue;
-        const int ix_base = ox0 * S - PAD;
-        float wk[K][8];
-        load_dw_row<K>(wsm, m.c8, cvl, ky, wk);
+        __syncthreads();
 #pragma unroll
-        for (int j = 0; j < NIN; ++j) {
-          const int ix = ix_base + j;
-          if (ix < 0 || ix >= W) continue;
-          float v[8];
-          load8bf(xin + ((size_t)iy * W + ix) * C, v);
-          if (has_bn) {
+        for (int kx = 0; kx < K; ++kx) {
+          float lo, hi;
+          f2_unpack(w[ky][kx], lo, hi);
+          red[((warp * K + kx) * 32 + lane) * 2 + 0] = lo;
+          red[((warp * K + kx) * 32 + lane) * 2 + 1] = hi;
+          w[ky][kx] = 0;
+        }
+        __syncthreads();
+        for (int i = tid; i < K * 64; i += DW_THREADS) {
+          const int kx = i >> 6, l2 = i & 63;
+          float s = 0.f;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = silu_f(fmaf(fa[k], v[k], fb[k]));
-          }
-#pragma unroll
-          for (int p = 0; p < DW_PX; ++p) {
-            const int kx = j - p * S;
-            if (kx >= 0 && kx < K) {
-#pragma unroll
-              for (int k = 0; k < 8; ++k) acc[p][k] = fmaf(wk[kx][k], v[k], acc[p][k]);
-            }
-          }
+          for (int wp = 0; wp < 8; ++wp) s += red[((wp * K + kx) * 32) * 2 + l2];
+          const int ch = cur_chunk * p.cw + l2;
+          if (l2 < p.cw && ch < p.C) atomicAdd(p.dw + (size_t)(ky * K + kx) * p.C + ch, s);
         }
       }
+      __syncthreads();
+    } else if (p.s1 != nullptr) {
+      __syncthreads();
+      float a0, a1, b0, b1;
+      f2_unpack(st1, a0, a1);
+      f2_unpack(st2, b0, b1);
+      float4* r4 = reinterpret_cast<float4*>(red);
+      r4[warp * 32 + lane] = make_float4(a0, a1, b0, b1);
+      __syncthreads();
+      if (tid < 128) {
+        const int l = tid >> 2, comp = tid & 3;
+        float s = 0.f;
 #pragma unroll
-      for (int p = 0; p < DW_PX; ++p) {
-        const int ox = ox0 + p;
-        if (ox < Wo) {
-          store8bf(yout + ((size_t)oy * Wo + ox) * C, acc[p]);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            s1[k] += acc[p][k];
-            s2[k] += acc[p][k] * acc[p][k];
-          }
-        }
+        for (int wp = 0; wp < 8; ++wp) s += red[(wp * 32 + l) * 4 + comp];
+        const int cl = 2 * l + (comp & 1), ch = cur_chunk * p.cw + cl;
+        if (cl < p.cw && ch < p.C) atomicAdd((comp < 2 ? p.s1 : p.s2) + ch, s);
       }
+      __syncthreads();
+      st1 = 0;
+      st2 = 0;
     }
-  }
-  if (sum != nullptr) {
-    cta_channel_reduce_atomic(m, s1, red, sum);
-    cta_channel_reduce_atomic(m, s2, red, sumsq);
-  }
-}
+  };
 
-// dIn[n,iy,ix,c] = sum_{ky,kx} w[c,ky,kx] * dOut[n,(iy+pad-ky)/S,(ix+pad-kx)/S,c]; then (if the conv input was
-// SiLU(BN(x_raw))) multiply by SiLU'(a*x_raw+b) and accumulate the BN-backward sums over dh and dh*xhat.
-template <int K, int S>
-__global__ void __launch_bounds__(CNN_THREADS, 2) dwconv_bwd_data_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ w,
-                                                                      const bf16* __restrict__ x_raw, const float* __restrict__ a_in,
-                                                                      const float* __restrict__ b_in, const float* __restrict__ mean,
-                                                                      const float* __restrict__ rstd, bf16* __restrict__ din,
-                                                                      float* __restrict__ sums, int H, int W, int Ho, int Wo, int C) {
-  extern __shared__ float dyn_sm[];
-  float* wsm = dyn_sm;
-  float* red = dyn_sm + K * K * DW_MAXV * 8;
-  const ChanMap m = make_dw_map(C / 8, blockIdx.z);
-  load_dw_weights<K>(wsm, w, m);
-  constexpr int PAD = (K - 1) / 2;
-  constexpr int NJ = (S == 1) ? (DW_PX + K - 1) : 4;
-  const int n = blockIdx.y, XG = (W + DW_PX - 1) / DW_PX, items = H * XG;
-  int ib, ie;
-  cta_rows(items, ib, ie);
-  float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (m.active) {
-    const int cvl = threadIdx.x % m.c8;
-    const bool has_bn = a_in != nullptr;
-    float fa[8], fb[8], mu[8], rs[8];
-    if (has_bn) {
-      load8f(a_in + m.cv * 8, fa);
-      load8f(b_in + m.cv * 8, fb);
-      load8f(mean + m.cv * 8, mu);
-      load8f(rstd + m.cv * 8, rs);
-    }
-    const bf16* g = dout + (size_t)n * Ho * Wo * C + (size_t)m.cv * 8;
-    const size_t in_off = (size_t)n * H * W * C + (size_t)m.cv * 8;
-    for (int it = ib + m.r0; it < ie; it += m.rows_per_pass) {
-      const int iy = it / XG, ix0 = (it % XG) * DW_PX;
-      float acc[DW_PX][8];
+  for (int it = it0, k = 0; it < it1; ++it, ++k) {
+    const int stage = k & 1;
+    __syncthreads();  // every thread is done with the other stage (item k-1): it may be refilled
+    if (tid == 0 && it + 1 < it1) issue(it + 1, stage ^ 1);
+    const int tx = it % p.tiles_x;
+    int r = it / p.tiles_x;
+    const int ty = r % p.tiles_y;
+    r /= p.tiles_y;
+    const int n = r % p.N, chunk = r / p.N;
+    if (chunk != cur_chunk) {
+      if (cur_chunk >= 0) flush();
+      cur_chunk = chunk;
+      c_lo = chunk * p.cw + 2 * lane;
+      chan_ok = 2 * lane < p.cw && c_lo < p.C;
+      if (MODE == DW_WGRAD) {
 #pragma unroll
-      for (int p = 0; p < DW_PX; ++p)
+        for (int ky = 0; ky < K; ++ky)
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[p][k] = 0.f;
-#pragma unroll 1
-      for (int ky = 0; ky < K; ++ky) {
-        const int t = iy + PAD - ky;
-        if (t < 0 || (t % S) != 0) continue;
-        const int oy = t / S;
-        if (oy >= Ho) continue;
-        // candidate output columns: S == 1: ox = ix0 + PAD - (K-1) + j, kx = p + K-1 - j
-        //                           S == 2: ox = ix0/2 - 1 + j,         kx = p + PAD + 2 - 2j   (ix0 is a multiple of 4)
-        const int ox_base = (S == 1) ? (ix0 + PAD - (K - 1)) : (ix0 / 2 - 1);
-        float wk[K][8];
-        load_dw_row<K>(wsm, m.c8, cvl, ky, wk);
+          for (int kx = 0; kx < K; ++kx) w[ky][kx] = 0;
+      } else {
+        const bf16* wp = p.w + (size_t)c_lo * K * K;
 #pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-          const int ox = ox_base + j;
-          if (ox < 0 || ox >= Wo) continue;
-          float v[8];
-          load8bf(g + ((size_t)oy * Wo + ox) * C, v);
+        for (int ky = 0; ky < K; ++ky)
 #pragma unroll
-          for (int p = 0; p < DW_PX; ++p) {
-            const int kx = (S == 1) ? (p + K - 1 - j) : (p + PAD + 2 - 2 * j);
-            if (kx >= 0 && kx < K) {
-#pragma unroll
-              for (int k = 0; k < 8; ++k) acc[p][k] = fmaf(wk[kx][k], v[k], acc[p][k]);
-            }
-          }
+          for (int kx = 0; kx < K; ++kx)
+            w[ky][kx] = chan_ok ? f2_pack(__bfloat162float(wp[ky * K + kx]), __bfloat162float(wp[K * K + ky * K + kx])) : (f2)0;
+      }
+      if (p.a_in != nullptr) {
+        pa = chan_ok ? f2_pack(p.a_in[c_lo], p.a_in[c_lo + 1]) : (f2)0;
+        pb = chan_ok ? f2_pack(p.b_in[c_lo], p.b_in[c_lo + 1]) : (f2)0;
+        if (MODE == DW_BWD) {
+          pmu = chan_ok ? f2_pack(p.mean[c_lo], p.mean[c_lo + 1]) : (f2)0;
+          prs = chan_ok ? f2_pack(p.rstd[c_lo], p.rstd[c_lo + 1]) : (f2)0;
         }
       }
-#pragma unroll
-      for (int p = 0; p < DW_PX; ++p) {
-        const int ix = ix0 + p;
-        if (ix >= W) continue;
-        const size_t o = in_off + ((size_t)iy * W + ix) * C;
-        if (has_bn) {
-          float xr[8];
-          load8bf(x_raw + o, xr);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const float dh = acc[p][k] * silu_grad_f(fmaf(fa[k], xr[k], fb[k]));
-            acc[p][k] = dh;
-            s1[k] += dh;
-            s2[k] += dh * (xr[k] - mu[k]) * rs[k];
-          }
-        }
-        store8bf(din + o, acc[p]);
-      }
     }
-  }
-  if (sums != nullptr) {
-    cta_channel_reduce_atomic(m, s1, red, sums);
-    cta_channel_reduce_atomic(m, s2, red, sums + C);
-  }
-}
+    uint32_t* const tile = reinterpret_cast<uint32_t*>(base + (size_t)stage * stage_bytes);
+    const uint32_t* const aux = reinterpret_cast<const uint32_t*>(base + (size_t)stage * stage_bytes + p.src_region);
+    mbar_wait(smem_u32(&full_bar[stage]), (uint32_t)((k >> 1) & 1));
 
-// dw[ky][kx][c] += sum over (n, oy, ox) dOut * act(x); scratch layout [K*K][C] fp32.
-// K x K taps x 8 channels do not fit in registers at a useful occupancy, so blockIdx.x % K splits the kernel
-// rows over CTAs (ALLKY keeps the single-CTA variant for reference).
-template <int K, int S>
-__global__ void __launch_bounds__(CNN_THREADS, 2) dwconv_wgrad_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ x,
-                                                                      const float* __restrict__ a_in, const float* __restrict__ b_in,
-                                                                      float* __restrict__ dw, int H, int W, int Ho, int Wo, int C) {
-  __shared__ float red[CNN_THREADS * 8];
-  constexpr bool ALLKY = false;   // all 9 taps of a 3x3 in one CTA was measured: 72 accumulators force 1 CTA/SM and it ran 17 % slower
-  constexpr int NKY = ALLKY ? K : 1;
-  // The K CTAs that share a tile (one per kernel row) are neighbours in blockIdx.x: they run at the same time and the
-  // second..K-th read of dOut and x hits L2 (with ky on blockIdx.z they were a whole grid apart and every operand
-  // streamed from HBM K times: ncu showed 796 MB of DRAM reads for 224 MB of data).
-  const int ky0 = ALLKY ? 0 : blockIdx.x % K;
-  const int xb = ALLKY ? blockIdx.x : blockIdx.x / K, xn = ALLKY ? gridDim.x : gridDim.x / K;
-  const ChanMap m = make_dw_map(C / 8, blockIdx.z);
-  constexpr int PAD = (K - 1) / 2, NIN = (DW_PX - 1) * S + K;
-  const int n = blockIdx.y, XG = (Wo + DW_PX - 1) / DW_PX, items = Ho * XG;
-  const int per = (items + xn - 1) / xn;
-  const int ib = xb * per, ie = min(items, ib + per);
-  float acc[NKY * K][8];
-#pragma unroll
-  for (int q = 0; q < NKY * K; ++q)
-#pragma unroll
-    for (int k = 0; k < 8; ++k) acc[q][k] = 0.f;
-  if (m.active) {
-    const bool has_bn = a_in != nullptr;
-    float fa[8], fb[8];
-    if (has_bn) {
-      load8f(a_in + m.cv * 8, fa);
-      load8f(b_in + m.cv * 8, fb);
-    }
-    const bf16* xin = x + (size_t)n * H * W * C + (size_t)m.cv * 8;
-    const bf16* g = dout + (size_t)n * Ho * Wo * C + (size_t)m.cv * 8;
-    for (int it = ib + m.r0; it < ie; it += m.rows_per_pass) {
-      const int oy = it / XG, ox0 = (it % XG) * DW_PX;
-      float gd[DW_PX][8];
-#pragma unroll
-      for (int p = 0; p < DW_PX; ++p) {
-        if (ox0 + p < Wo) load8bf(g + ((size_t)oy * Wo + ox0 + p) * C, gd[p]);
-        else
-#pragma unroll
-          for (int k = 0; k < 8; ++k) gd[p][k] = 0.f;
+    if (MODE != DW_BWD && p.a_in != nullptr) {
+      // SiLU(BN(.)) of the producer applied to the tile in place, once per element; padding stays zero
+      const int sy0 = G::src0(ty * TY), sx0 = G::src0(tx * TX);
+      float a0, a1, b0, b1;
+      f2_unpack(pa, a0, a1);
+      f2_unpack(pb, b0, b1);
+      if (lane < cww) {
+        for (int pix = warp; pix < G::SY * SX; pix += 8) {
+          const int ry = pix / SX, rx = pix - ry * SX;
+          const bool inside = (unsigned)(sy0 + ry) < (unsigned)p.SH && (unsigned)(sx0 + rx) < (unsigned)p.SW;
+          uint32_t* q = tile + pix * cww + lane;
+          const uint32_t u = *q;
+          const float lo = silu_f(fmaf(a0, __uint_as_float(u << 16), b0));
+          const float hi = silu_f(fmaf(a1, __uint_as_float(u & 0xffff0000u), b1));
+          *q = inside ? f2_to_bf2(lo, hi) : 0u;
+        }
       }
-      const int ix_base = ox0 * S - PAD;
+      fence_proxy_async();   // these generic-proxy writes precede the TMA refill of this stage two items later
+      __syncthreads();
+    }
+
+    const uint32_t* const src = tile + ((posy * G::STEPY) * SX + posx * G::STEPX) * cww + lane;
+    const int dx0 = tx * TX + posx * PX, dy0 = ty * TY + posy * PY;
+
+    if (MODE == DW_WGRAD) {
+      f2 g[PY][PX];
 #pragma unroll
-      for (int kyi = 0; kyi < NKY; ++kyi) {
-        const int iy = oy * S - PAD + ky0 + kyi;
-        if (iy < 0 || iy >= H) continue;
+      for (int py = 0; py < PY; ++py)
 #pragma unroll
-        for (int j = 0; j < NIN; ++j) {
-          const int ix = ix_base + j;
-          if (ix < 0 || ix >= W) continue;
-          float v[8];
-          load8bf(xin + ((size_t)iy * W + ix) * C, v);
-          if (has_bn) {
+        for (int px = 0; px < PX; ++px) g[py][px] = bf2_to_f2(aux[((posy * PY + py) * TX + posx * PX + px) * cww + lane]);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = silu_f(fmaf(fa[k], v[k], fb[k]));
+      for (int q = 0; q < QY; ++q) {
+        f2 row[QX];
+#pragma unroll
+        for (int j = 0; j < QX; ++j) row[j] = bf2_to_f2(src[(q * SX + j) * cww]);
+#pragma unroll
+        for (int py = 0; py < PY; ++py) {
+          const int ky = G::tap(py, q);
+          if (ky >= 0 && ky < K) {
+#pragma unroll
+            for (int px = 0; px < PX; ++px)
+#pragma unroll
+              for (int j = 0; j < QX; ++j) {
+                const int kx = G::tap(px, j);
+                if (kx >= 0 && kx < K) w[ky][kx] = f2_fma(g[py][px], row[j], w[ky][kx]);
+              }
           }
+        }
+      }
+    } else {
+      f2 acc[PY][PX];
 #pragma unroll
-          for (int p = 0; p < DW_PX; ++p) {
-            const int kx = j - p * S;
-            if (kx >= 0 && kx < K) {
+      for (int py = 0; py < PY; ++py)
 #pragma unroll
-              for (int k = 0; k < 8; ++k) acc[kyi * K + kx][k] = fmaf(gd[p][k], v[k], acc[kyi * K + kx][k]);
-            }
+        for (int px = 0; px < PX; ++px) acc[py][px] = 0;
+#pragma unroll
+      for (int q = 0; q < QY; ++q) {
+        f2 row[QX];
+#pragma unroll
+        for (int j = 0; j < QX; ++j) row[j] = bf2_to_f2(src[(q * SX + j) * cww]);
+#pragma unroll
+        for (int py = 0; py < PY; ++py) {
+          const int ky = G::tap(py, q);
+          if (ky >= 0 && ky < K) {
+#pragma unroll
+            for (int px = 0; px < PX; ++px)
+#pragma unroll
+              for (int j = 0; j < QX; ++j) {
+                const int kx = G::tap(px, j);
+                if (kx >= 0 && kx < K) acc[py][px] = f2_fma(w[ky][kx], row[j], acc[py][px]);
+              }
           }
+        }
+      }
+      // epilogue: the warp shares its position, so the bounds tests are warp-uniform
+      bf16* const out = p.dst + (size_t)n * p.DH * p.DW * p.C + c_lo;
+      const bool bwd_bn = MODE == DW_BWD && p.a_in != nullptr;
+#pragma unroll
+      for (int py = 0; py < PY; ++py) {
+        const int dy = dy0 + py;
+        if (dy >= p.DH) continue;
+#pragma unroll
+        for (int px = 0; px < PX; ++px) {
+          const int dx = dx0 + px;
+          if (dx >= p.DW) continue;
+          float lo, hi;
+          f2_unpack(acc[py][px], lo, hi);
+          if (bwd_bn) {
+            // dh = dAct * SiLU'(a x + b); BatchNorm-backward sums over dh and dh * xhat
+            float x0, x1, a0, a1, b0, b1, m0, m1, r0, r1;
+            f2_unpack(bf2_to_f2(aux[((posy * PY + py) * TX + posx * PX + px) * cww + lane]), x0, x1);
+            f2_unpack(pa, a0, a1);
+            f2_unpack(pb, b0, b1);
+            f2_unpack(pmu, m0, m1);
+            f2_unpack(prs, r0, r1);
+            lo *= silu_grad_f(fmaf(a0, x0, b0));
+            hi *= silu_grad_f(fmaf(a1, x1, b1));
+            st1 = f2_add(st1, f2_pack(lo, hi));
+            st2 = f2_fma(f2_pack(lo, hi), f2_pack((x0 - m0) * r0, (x1 - m1) * r1), st2);
+          } else if (MODE == DW_FWD) {
+            st1 = f2_add(st1, acc[py][px]);
+            st2 = f2_fma(acc[py][px], acc[py][px], st2);
+          }
+          if (chan_ok) *reinterpret_cast<uint32_t*>(out + ((size_t)dy * p.DW + dx) * p.C) = f2_to_bf2(lo, hi);
         }
       }
     }
   }
-#pragma unroll
-  for (int kyi = 0; kyi < NKY; ++kyi)
-#pragma unroll
-    for (int kx = 0; kx < K; ++kx)
-      cta_channel_reduce_atomic(m, acc[kyi * K + kx], red, dw + (size_t)((ky0 + kyi) * K + kx) * C);
+  flush();
 }
 
 // scratch [K*K][C] fp32 → weight gradient [C][K*K] bf16
@@ -317,43 +347,84 @@ __global__ void dw_wgrad_cast_kernel(const float* __restrict__ scratch, bf16* __
   dw[i] = __float2bfloat16_rn(scratch[(size_t)t * C + c]);
 }
 
-static int dw_items_ctas(int N, int items) {
-  int want = (148 * 8 + N - 1) / N;
-  int maxc = (items + 15) / 16;
-  if (want > maxc) want = maxc;
-  return want < 1 ? 1 : want;
+template <int K, int S, int MODE, int CWW>
+int launch_dw_inst(const CUtensorMap& src_map, const CUtensorMap& aux_map, const DwParams& p, size_t smem, int grid, cudaStream_t stream) {
+  if (int rc = rt1_ensure_dyn_smem((const void*)dw_tile_kernel<K, S, MODE, CWW>, 200 * 1024)) return rc;
+  dw_tile_kernel<K, S, MODE, CWW><<<grid, DW_THREADS, smem, stream>>>(src_map, aux_map, p);
+  return 0;
 }
 
-#define DW_DISPATCH(KERNEL, ...)                                                                     \
+// src: the haloed operand [N,SH,SW,C]; aux: the operand read at destination coordinates [N,DH,DW,C] (or null)
+template <int K, int S, int MODE>
+int launch_dw(const void* src, const void* aux, DwParams p, cudaStream_t stream, const char* what) {
+  using G = DwGeom<K, S, MODE>;
+  RT1_REQUIRE(p.C % 8 == 0, "%s: C=%d must be a multiple of 8", what, p.C);
+  p.cw = p.C >= 64 ? 64 : p.C;
+  p.cww = p.cw / 2;
+  const int chunks = (p.C + p.cw - 1) / p.cw;
+  p.tiles_x = (p.DW + G::TX - 1) / G::TX;
+  p.tiles_y = (p.DH + G::TY - 1) / G::TY;
+  const long items = (long)chunks * p.N * p.tiles_x * p.tiles_y;
+  RT1_REQUIRE(items > 0 && items < (1L << 30), "%s: bad problem size", what);
+  p.items = (int)items;
+  p.src_bytes = G::SY * G::SX * p.cw * 2;
+  p.aux_bytes = aux != nullptr ? G::TY * G::TX * p.cw * 2 : 0;
+  p.src_region = (p.src_bytes + 127) & ~127;
+  p.aux_region = (p.aux_bytes + 127) & ~127;
+  const size_t smem = 2 * (size_t)(p.src_region + p.aux_region) + 256;  // alignment slack + over-read slack of idle lanes
+  RT1_REQUIRE(smem <= 200 * 1024, "%s: tile needs %zu bytes of shared memory", what, smem);
+  const size_t static_smem = (MODE == DW_WGRAD ? 8 * 32 * 2 * K : 8 * 32 * 4) * sizeof(float) + 64 + 1024;  // + per-CTA reserve
+  int per_sm = (int)((227 * 1024) / (smem + static_smem));
+  const int cap = (K == 3 && MODE != DW_BWD) ? 3 : 2;
+  per_sm = per_sm < 1 ? 1 : (per_sm > cap ? cap : per_sm);
+  int grid = rt1_sm_count() * per_sm;
+  if ((long)grid > items) grid = (int)items;
+  p.per_cta = (int)((items + grid - 1) / grid);
+  grid = (int)((items + p.per_cta - 1) / p.per_cta);
+  CUtensorMap src_map, aux_map;
+  int rc = rt1_make_tmap_bf16_nhwc(&src_map, src, (uint64_t)p.N, (uint64_t)p.SH, (uint64_t)p.SW, (uint64_t)p.C, G::SY, G::SX, (uint32_t)p.cw);
+  if (rc) return rc;
+  if (aux != nullptr) {
+    rc = rt1_make_tmap_bf16_nhwc(&aux_map, aux, (uint64_t)p.N, (uint64_t)p.DH, (uint64_t)p.DW, (uint64_t)p.C, G::TY, G::TX, (uint32_t)p.cw);
+    if (rc) return rc;
+  } else {
+    aux_map = src_map;
+  }
+  if (p.cww == 32) rc = launch_dw_inst<K, S, MODE, 32>(src_map, aux_map, p, smem, grid, stream);
+  else rc = launch_dw_inst<K, S, MODE, 0>(src_map, aux_map, p, smem, grid, stream);
+  if (rc) return rc;
+  return rt1_check_launch(what);
+}
+
+#define DW_DISPATCH(MODE, ...)                                                                       \
   do {                                                                                               \
-    if (k == 3 && stride == 1) KERNEL<3, 1> __VA_ARGS__;                                              \
-    else if (k == 3 && stride == 2) KERNEL<3, 2> __VA_ARGS__;                                         \
-    else if (k == 5 && stride == 1) KERNEL<5, 1> __VA_ARGS__;                                         \
-    else if (k == 5 && stride == 2) KERNEL<5, 2> __VA_ARGS__;                                         \
-    else RT1_REQUIRE(false, "depthwise conv: unsupported kernel %d stride %d", k, stride);            \
+    if (k == 3 && stride == 1) return launch_dw<3, 1, MODE>(__VA_ARGS__);                             \
+    if (k == 3 && stride == 2) return launch_dw<3, 2, MODE>(__VA_ARGS__);                             \
+    if (k == 5 && stride == 1) return launch_dw<5, 1, MODE>(__VA_ARGS__);                             \
+    if (k == 5 && stride == 2) return launch_dw<5, 2, MODE>(__VA_ARGS__);                             \
+    RT1_REQUIRE(false, "depthwise conv: unsupported kernel %d stride %d", k, stride);                 \
   } while (0)
+
+int dw_wgrad_impl(const void* dout, const void* x, const float* a_in, const float* b_in, float* scratch, int N, int H, int W, int C,
+                  int k, int stride, cudaStream_t stream) {
+  const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+  DwParams p = {};
+  p.a_in = a_in; p.b_in = b_in; p.dw = scratch;
+  p.N = N; p.C = C; p.SH = H; p.SW = W; p.DH = Ho; p.DW = Wo;
+  DW_DISPATCH(DW_WGRAD, x, dout, p, stream, "rt1_dwconv_wgrad");
+}
+
+}  // namespace
 
 // x [N,H,W,C] raw (a_in/b_in = producer BN scale/shift, SiLU applied on load) or already-activated (a_in = null);
 // y [N,Ho,Wo,C] raw output; sum/sumsq fp32 [C] (caller-zeroed) or null.
 RT1_API int rt1_dwconv_fwd(const void* x, const float* a_in, const float* b_in, const void* w, void* y, float* sum, float* sumsq,
                            int N, int H, int W, int C, int k, int stride, cudaStream_t stream) {
-  RT1_REQUIRE(C % 8 == 0, "rt1_dwconv_fwd: C=%d must be a multiple of 8", C);
-  if (a_in == nullptr && rt1_dw2_enabled()) return rt1_dw2_fwd(x, w, y, sum, sumsq, N, H, W, C, k, stride, stream);
   const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
-  const int items = Ho * ((Wo + DW_PX - 1) / DW_PX);
-  dim3 grid(dw_items_ctas(N, items), N, dw_chunks(C));
-  const size_t smem = ((size_t)k * k * DW_MAXV * 8 + CNN_THREADS * 8) * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set) {
-    const int mx = (25 * DW_MAXV * 8 + CNN_THREADS * 8) * 4;
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_fwd_kernel<5, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_fwd_kernel<5, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_fwd_kernel<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_fwd_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    attr_set = true;
-  }
-  DW_DISPATCH(dwconv_fwd_kernel, <<<grid, CNN_THREADS, smem, stream>>>((const bf16*)x, a_in, b_in, (const bf16*)w, (bf16*)y, sum, sumsq, H, W, Ho, Wo, C));
-  return rt1_check_launch("rt1_dwconv_fwd");
+  DwParams p = {};
+  p.w = (const bf16*)w; p.dst = (bf16*)y; p.a_in = a_in; p.b_in = b_in; p.s1 = sum; p.s2 = sumsq;
+  p.N = N; p.C = C; p.SH = H; p.SW = W; p.DH = Ho; p.DW = Wo;
+  DW_DISPATCH(DW_FWD, x, nullptr, p, stream, "rt1_dwconv_fwd");
 }
 
 // dout [N,Ho,Wo,C]; x_raw [N,H,W,C] + a_in/b_in/mean/rstd (or all null when the conv input was not BN+SiLU);
@@ -362,152 +433,30 @@ RT1_API int rt1_dwconv_fwd(const void* x, const float* a_in, const float* b_in, 
 RT1_API int rt1_dwconv_bwd_data(const void* dout, const void* w, const void* x_raw, const float* a_in, const float* b_in,
                                 const float* mean, const float* rstd, void* din, float* sums, int N, int H, int W, int C, int k,
                                 int stride, cudaStream_t stream) {
-  RT1_REQUIRE(C % 8 == 0, "rt1_dwconv_bwd_data: C=%d must be a multiple of 8", C);
-  if (stride == 1 && rt1_dw2_enabled())
-    return rt1_dw2_bwd_data_s1(dout, w, x_raw, a_in, b_in, mean, rstd, din, sums, N, H, W, C, k, stream);
   const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
-  const int items = H * ((W + DW_PX - 1) / DW_PX);
-  dim3 grid(dw_items_ctas(N, items), N, dw_chunks(C));
-  const size_t smem = ((size_t)k * k * DW_MAXV * 8 + CNN_THREADS * 8) * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set) {
-    const int mx = (25 * DW_MAXV * 8 + CNN_THREADS * 8) * 4;
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_bwd_data_kernel<5, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_bwd_data_kernel<5, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_bwd_data_kernel<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(dwconv_bwd_data_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-    attr_set = true;
-  }
-  DW_DISPATCH(dwconv_bwd_data_kernel, <<<grid, CNN_THREADS, smem, stream>>>((const bf16*)dout, (const bf16*)w, (const bf16*)x_raw, a_in, b_in, mean, rstd, (bf16*)din, sums, H, W, Ho, Wo, C));
-  return rt1_check_launch("rt1_dwconv_bwd_data");
+  DwParams p = {};
+  p.w = (const bf16*)w; p.dst = (bf16*)din; p.a_in = a_in; p.b_in = b_in; p.mean = mean; p.rstd = rstd;
+  p.s1 = (a_in != nullptr) ? sums : nullptr; p.s2 = (a_in != nullptr && sums != nullptr) ? sums + C : nullptr;
+  p.N = N; p.C = C; p.SH = Ho; p.SW = Wo; p.DH = H; p.DW = W;
+  const void* aux = a_in != nullptr ? x_raw : nullptr;
+  DW_DISPATCH(DW_BWD, dout, aux, p, stream, "rt1_dwconv_bwd_data");
 }
 
 // scratch: fp32 [k*k*C], zeroed by this call; dw: bf16 [C, k, k]
 RT1_API int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in, const float* b_in, float* scratch, void* dw, int N,
                              int H, int W, int C, int k, int stride, cudaStream_t stream) {
-  RT1_REQUIRE(C % 8 == 0, "rt1_dwconv_wgrad: C=%d must be a multiple of 8", C);
-  const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
-  const int items = Ho * ((Wo + DW_PX - 1) / DW_PX);
   RT1_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)k * k * C, stream));
-  if (a_in == nullptr && rt1_dw2_enabled()) {
-    int rc2 = rt1_dw2_wgrad(dout, x, scratch, N, H, W, C, k, stride, stream);
-    if (rc2) return rc2;
-    dw_wgrad_cast_kernel<<<rt1_cdiv((long)C * k * k, 256), 256, 0, stream>>>(scratch, (bf16*)dw, C, k * k);
-    return rt1_check_launch("rt1_dwconv_wgrad(cast)");
-  }
-  int ctas = dw_items_ctas(N, items);
-  const int zsplit = k;   // kernel rows split over blockIdx.z
-  ctas = (ctas + zsplit - 1) / zsplit;
-  dim3 grid((ctas < 1 ? 1 : ctas) * zsplit, N, dw_chunks(C));
-  DW_DISPATCH(dwconv_wgrad_kernel, <<<grid, CNN_THREADS, 0, stream>>>((const bf16*)dout, (const bf16*)x, a_in, b_in, scratch, H, W, Ho, Wo, C));
-  int rc = rt1_check_launch("rt1_dwconv_wgrad");
+  int rc = dw_wgrad_impl(dout, x, a_in, b_in, scratch, N, H, W, C, k, stride, stream);
   if (rc) return rc;
   dw_wgrad_cast_kernel<<<rt1_cdiv((long)C * k * k, 256), 256, 0, stream>>>(scratch, (bf16*)dw, C, k * k);
   return rt1_check_launch("rt1_dwconv_wgrad(cast)");
 }
 
-// ------------------------------------------------------------------------------------------------- stem 3x3 s2
-// x [N,H,W,8] bf16 (channels 0..2 used), w [CO,3,3,3] bf16 → y [N,Ho,Wo,CO] raw + stats.  CO multiple of 8, <= 64.
-__global__ void __launch_bounds__(CNN_THREADS) stem_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, bf16* __restrict__ y,
-                                                               float* __restrict__ sum, float* __restrict__ sumsq, int H, int W, int Ho,
-                                                               int Wo, int CO) {
-  __shared__ float wsm[27 * 64];
-  __shared__ float red[CNN_THREADS * 8];
-  for (int i = threadIdx.x; i < 27 * CO; i += blockDim.x) {
-    const int co = i / 27, t = i % 27;        // t = ci*9 + ky*3 + kx  (torch [CO,3,3,3])
-    wsm[t * CO + co] = __bfloat162float(w[i]);
-  }
-  __syncthreads();
-  const ChanMap m = make_dw_map(CO / 8, 0);
-  const int n = blockIdx.y, items = Ho * Wo;
-  int ib, ie;
-  cta_rows(items, ib, ie);
-  float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (m.active) {
-    const int cl = (threadIdx.x % m.c8) * 8;
-    const bf16* xin = x + (size_t)n * H * W * 8;
-    for (int it = ib + m.r0; it < ie; it += m.rows_per_pass) {
-      const int oy = it / Wo, ox = it % Wo;
-      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const int iy = oy * 2 - 1 + ky;
-        if (iy < 0 || iy >= H) continue;
-#pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const int ix = ox * 2 - 1 + kx;
-          if (ix < 0 || ix >= W) continue;
-          float v[8];
-          load8bf(xin + ((size_t)iy * W + ix) * 8, v);
-#pragma unroll
-          for (int ci = 0; ci < 3; ++ci) {
-            const float* wp = wsm + (ci * 9 + ky * 3 + kx) * CO + cl;
-#pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] = fmaf(wp[k], v[ci], acc[k]);
-          }
-        }
-      }
-      store8bf(y + ((size_t)n * items + it) * CO + cl, acc);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        s1[k] += acc[k];
-        s2[k] += acc[k] * acc[k];
-      }
-    }
-  }
-  if (sum != nullptr) {
-    cta_channel_reduce_atomic(m, s1, red, sum);
-    cta_channel_reduce_atomic(m, s2, red, sumsq);
-  }
-}
-
-// dw[co][ci][ky][kx] = sum dY[n,oy,ox,co] * x[n,2oy-1+ky,2ox-1+kx,ci]; blockIdx.z = ky; scratch layout [27][CO] fp32
-__global__ void __launch_bounds__(CNN_THREADS) stem_wgrad_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
-                                                                 float* __restrict__ scratch, int H, int W, int Ho, int Wo, int CO) {
-  __shared__ float red[CNN_THREADS * 8];
-  const int ky = blockIdx.z;
-  const ChanMap m = make_dw_map(CO / 8, 0);
-  const int n = blockIdx.y, items = Ho * Wo;
-  int ib, ie;
-  cta_rows(items, ib, ie);
-  float acc[9][8];  // [ci*3 + kx]
-#pragma unroll
-  for (int q = 0; q < 9; ++q)
-#pragma unroll
-    for (int k = 0; k < 8; ++k) acc[q][k] = 0.f;
-  if (m.active) {
-    const int cl = (threadIdx.x % m.c8) * 8;
-    const bf16* xin = x + (size_t)n * H * W * 8;
-    for (int it = ib + m.r0; it < ie; it += m.rows_per_pass) {
-      const int oy = it / Wo, ox = it % Wo, iy = oy * 2 - 1 + ky;
-      if (iy < 0 || iy >= H) continue;
-      float g[8];
-      load8bf(dy + ((size_t)n * items + it) * CO + cl, g);
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        const int ix = ox * 2 - 1 + kx;
-        if (ix < 0 || ix >= W) continue;
-        float v[8];
-        load8bf(xin + ((size_t)iy * W + ix) * 8, v);
-#pragma unroll
-        for (int ci = 0; ci < 3; ++ci)
-#pragma unroll
-          for (int k = 0; k < 8; ++k) acc[ci * 3 + kx][k] = fmaf(g[k], v[ci], acc[ci * 3 + kx][k]);
-      }
-    }
-  }
-#pragma unroll
-  for (int ci = 0; ci < 3; ++ci)
-#pragma unroll
-    for (int kx = 0; kx < 3; ++kx)
-      cta_channel_reduce_atomic(m, acc[ci * 3 + kx], red, scratch + (size_t)(ci * 9 + ky * 3 + kx) * CO);
-}
-
 // ---- stem as a tensor-core GEMM: im2col of the 3x3 stride-2 window -------------------------------------------------
 // x [N,H,W,8] bf16 (channels 0..2 used) → cols [N*Ho*Wo, 32] bf16, column ci*9 + ky*3 + kx (the flattening of the torch
-// weight [CO,3,3,3]); columns 27..31 are zero.  The direct kernels above run at ~7 % of DRAM bandwidth (L1-bound window
-// loads, like the depthwise kernels); 64 bytes per output pixel of extra traffic buy a K = 32 tcgen05 GEMM for the forward
-// (with the BatchNorm statistics in its epilogue) and a split-K GEMM for the weight gradient.
+// weight [CO,3,3,3]); columns 27..31 are zero.  64 bytes per output pixel of extra traffic buy a K = 32 tcgen05 GEMM for the
+// forward (with the BatchNorm statistics in its epilogue) and a split-K GEMM for the weight gradient; a direct CUDA-core stem
+// (round 1) ran at ~7 % of DRAM bandwidth.
 __global__ void __launch_bounds__(256) stem_im2col_kernel(const bf16* __restrict__ x, bf16* __restrict__ cols, int H, int W, int Ho,
                                                           int Wo, long total) {
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -542,26 +491,4 @@ RT1_API int rt1_stem_im2col(const void* x, void* cols, int N, int H, int W, cuda
   const long total = (long)N * Ho * Wo;
   stem_im2col_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>((const bf16*)x, (bf16*)cols, H, W, Ho, Wo, total);
   return rt1_check_launch("rt1_stem_im2col");
-}
-
-RT1_API int rt1_stem_fwd(const void* x, const void* w, void* y, float* sum, float* sumsq, int N, int H, int W, int CO,
-                         cudaStream_t stream) {
-  RT1_REQUIRE(CO % 8 == 0 && CO <= 64, "rt1_stem_fwd: CO=%d must be a multiple of 8 and <= 64", CO);
-  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  dim3 grid(dw_items_ctas(N, Ho * Wo / 4), N, 1);
-  stem_fwd_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, sum, sumsq, H, W, Ho, Wo, CO);
-  return rt1_check_launch("rt1_stem_fwd");
-}
-
-// scratch fp32 [27*CO] zeroed by this call; dw bf16 [CO,3,3,3]
-RT1_API int rt1_stem_wgrad(const void* dy, const void* x, float* scratch, void* dw, int N, int H, int W, int CO, cudaStream_t stream) {
-  RT1_REQUIRE(CO % 8 == 0 && CO <= 64, "rt1_stem_wgrad: CO=%d must be a multiple of 8 and <= 64", CO);
-  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  RT1_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(float) * 27 * (size_t)CO, stream));
-  dim3 grid(dw_items_ctas(N, Ho * Wo / 8), N, 3);
-  stem_wgrad_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, scratch, H, W, Ho, Wo, CO);
-  int rc = rt1_check_launch("rt1_stem_wgrad");
-  if (rc) return rc;
-  dw_wgrad_cast_kernel<<<rt1_cdiv(27L * CO, 256), 256, 0, stream>>>(scratch, (bf16*)dw, CO, 27);
-  return rt1_check_launch("rt1_stem_wgrad(cast)");
 }

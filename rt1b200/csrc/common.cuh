@@ -10,6 +10,11 @@
 // ---- host-side status plumbing --------------------------------------------------------------------------
 void rt1_set_error(const char* fmt, ...);
 int rt1_check_launch(const char* what);   // cudaGetLastError() → status + message
+int rt1_ensure_dyn_smem(const void* kernel, size_t bytes);   // per-(kernel, device) opt-in to > 48 KB dynamic shared memory
+int rt1_sm_count();                       // SM count of the current device (cached per device)
+// Device word added to every dropout seed (or null): lets a CAPTURED step draw fresh masks on every replay — the seeds
+// baked into the graph's kernel arguments stay fixed, the word is advanced by a node of the graph itself.
+const uint32_t* rt1_seed_epoch_ptr();
 
 #define RT1_CHECK_CUDA(expr)                                                                  \
   do {                                                                                        \

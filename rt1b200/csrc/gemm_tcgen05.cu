@@ -38,6 +38,7 @@ struct GemmParams {
   float alpha;
   float dropout_p;
   uint32_t seed;
+  const uint32_t* seed_epoch;   // device word added to `seed` (or null), see rt1_seed_epoch_ptr()
   // optional per-column statistics of the (post-bias) fp32 output: sum and sum of squares, atomically added
   float* col_sum;
   float* col_sumsq;
@@ -213,7 +214,7 @@ __global__ void __launch_bounds__(128, 8) gemm_tcgen05_kernel(const __grid_const
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
         const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c0 + j));
-        v[j] = rt1_hash_u32(idx, p.seed) >= thresh ? v[j] * keep_scale : 0.f;
+        v[j] = rt1_hash_u32(idx, p.seed + (p.seed_epoch != nullptr ? __ldg(p.seed_epoch) : 0u)) >= thresh ? v[j] * keep_scale : 0.f;
       }
     }
     if (p.residual != nullptr) {
@@ -525,7 +526,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
               const uint32_t idx = (uint32_t)((long)row * p.N + (n0 + c8 + k));
-              v[k] = rt1_hash_u32(idx, p.seed) >= thresh ? v[k] * keep_scale : 0.f;
+              v[k] = rt1_hash_u32(idx, p.seed + (p.seed_epoch != nullptr ? __ldg(p.seed_epoch) : 0u)) >= thresh ? v[k] * keep_scale : 0.f;
             }
           }
           if (!PLAIN && p.residual != nullptr && row_ok) {
@@ -598,43 +599,6 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-rt1_encode_tiled_fn rt1_get_encode_tiled() {
-  static rt1_encode_tiled_fn fn = nullptr;
-  if (fn) return fn;
-  void* f = nullptr;
-  cudaDriverEntryPointQueryResult q;
-  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
-      q != cudaDriverEntryPointSuccess)
-    return nullptr;
-  fn = (rt1_encode_tiled_fn)f;
-  return fn;
-}
-
-int rt1_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
-                          uint32_t box_cols) {
-  // The driver-API encoder needs a current context on the calling thread; autograd's backward threads may not
-  // have touched the runtime yet, so bind the primary context once per thread.
-  static thread_local bool ctx_bound = false;
-  if (!ctx_bound) {
-    RT1_CHECK_CUDA(cudaFree(0));
-    ctx_bound = true;
-  }
-  rt1_encode_tiled_fn enc = rt1_get_encode_tiled();
-  RT1_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
-  RT1_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0, "TMA operand must be 16-byte aligned (base %p, ld %llu)",
-              base, (unsigned long long)ld);
-  cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstr[1] = {ld * 2};
-  cuuint32_t box[2] = {box_cols, box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  RT1_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rows %llu cols %llu ld %llu box %ux%u)", (int)r,
-              (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols);
-  return 0;
-}
-
 static bool gemm_v2_enabled() {
   static int on = -1;
   if (on < 0) {
@@ -663,7 +627,7 @@ static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, c
   p.kb_per_split = (K + BLOCK_K - 1) / BLOCK_K;
   p.out = out; p.ldo = ldo; p.out_fp32 = 0; p.atomic_out = 0;
   p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
-  p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed;
+  p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed; p.seed_epoch = dropout_p > 0.f ? rt1_seed_epoch_ptr() : nullptr;
   p.col_sum = col_sum; p.col_sumsq = col_sumsq;
   {
     const char* e = getenv("RT1B200_GEMM_DBG");
@@ -692,18 +656,9 @@ static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, c
   rc = rt1_make_tmap_bf16_2d(&to, out, (uint64_t)M, (uint64_t)N, (uint64_t)ldo, BLOCK_M, 64);
   if (rc) return rc;
 
-  static size_t configured = 0;
-  if (smem > configured) {
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_persistent_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_persistent_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
-  static int sm_count = 0;
-  if (sm_count == 0) {
-    int dev = 0;
-    RT1_CHECK_CUDA(cudaGetDevice(&dev));
-    RT1_CHECK_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-  }
+  if ((rc = rt1_ensure_dyn_smem((const void*)gemm_tcgen05_persistent_kernel<true>, smem))) return rc;
+  if ((rc = rt1_ensure_dyn_smem((const void*)gemm_tcgen05_persistent_kernel<false>, smem))) return rc;
+  const int sm_count = rt1_sm_count();
   const long tiles = (long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn);
   const int grid = (int)(tiles < sm_count ? tiles : sm_count);
   const bool plain = alpha == 1.f && bias == nullptr && residual == nullptr && dropout_p <= 0.f;
@@ -724,6 +679,11 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   RT1_REQUIRE(split_k >= 1, "rt1_gemm_bf16: split_k must be >= 1");
   RT1_REQUIRE(split_k == 1 || out_fp32, "rt1_gemm_bf16: split-K needs an fp32 output");
   RT1_REQUIRE(!(accumulate && !out_fp32), "rt1_gemm_bf16: accumulate needs an fp32 output");
+  // every split (and every accumulating call) runs the whole epilogue on its partial sum: an epilogue term would be
+  // applied `splits` times and column statistics would be taken over partial sums
+  RT1_REQUIRE(!((split_k > 1 || accumulate) && (bias != nullptr || residual != nullptr || dropout_p > 0.f || col_sum != nullptr ||
+                                                col_sumsq != nullptr)),
+              "rt1_gemm_bf16: split-K / accumulate cannot be combined with bias, residual, dropout or column statistics");
   GemmParams p;
   p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn;
   // The persistent kernel pays ~10 us of set-up (TMEM allocation, barrier init, pipeline fill) and runs ONE CTA per SM:
@@ -756,7 +716,7 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   p.stages = stages;
   p.out = out; p.ldo = ldo; p.out_fp32 = out_fp32; p.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
   p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
-  p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed;
+  p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed; p.seed_epoch = dropout_p > 0.f ? rt1_seed_epoch_ptr() : nullptr;
   p.col_sum = col_sum; p.col_sumsq = col_sumsq; p.dbg = 0; p.b_resident = 0;
 
   CUtensorMap ta, tb;
@@ -769,11 +729,7 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   if (rc) return rc;
 
   const size_t smem = (size_t)stages * stage_bytes + (2 * stages + 2) * 8 + 1024;
-  static size_t configured = 0;
-  if (smem > configured) {
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if ((rc = rt1_ensure_dyn_smem((const void*)gemm_tcgen05_kernel, smem))) return rc;
   dim3 grid(((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn), 1, splits);
   gemm_tcgen05_kernel<<<grid, 128, smem, stream>>>(ta, tb, p);
   return rt1_check_launch("rt1_gemm_bf16");

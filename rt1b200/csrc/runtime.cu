@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 static thread_local char g_err[1024] = "";
@@ -19,6 +21,67 @@ int rt1_check_launch(const char* what) {
     rt1_set_error("%s: %s", what, cudaGetErrorString(e));
     return (int)e;
   }
+  return 0;
+}
+
+// cudaFuncSetAttribute and device attributes are PER DEVICE: caches are keyed by the current device so that a second GPU
+// driven from the same process gets its own opt-in to > 48 KB of dynamic shared memory.
+namespace {
+constexpr int kMaxDev = 64, kMaxKernels = 256;
+struct SmemOptIn {
+  const void* kernel;
+  size_t bytes[kMaxDev];
+};
+SmemOptIn g_optin[kMaxKernels];
+int g_optin_n = 0;
+std::mutex g_optin_mu;
+int g_sm_count[kMaxDev] = {0};
+}  // namespace
+
+int rt1_ensure_dyn_smem(const void* kernel, size_t bytes) {
+  if (bytes <= 48 * 1024) return 0;
+  int dev = 0;
+  RT1_CHECK_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(g_optin_mu);
+  SmemOptIn* e = nullptr;
+  for (int i = 0; i < g_optin_n; ++i)
+    if (g_optin[i].kernel == kernel) e = &g_optin[i];
+  if (e == nullptr && g_optin_n < kMaxKernels) {
+    e = &g_optin[g_optin_n++];
+    e->kernel = kernel;
+    memset(e->bytes, 0, sizeof(e->bytes));
+  }
+  if (e != nullptr && dev >= 0 && dev < kMaxDev && e->bytes[dev] >= bytes) return 0;
+  RT1_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  if (e != nullptr && dev >= 0 && dev < kMaxDev) e->bytes[dev] = bytes;
+  return 0;
+}
+
+int rt1_sm_count() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return 148;
+  if (g_sm_count[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    g_sm_count[dev] = n;
+  }
+  return g_sm_count[dev];
+}
+
+namespace {
+const uint32_t* g_seed_epoch[kMaxDev] = {nullptr};
+}
+const uint32_t* rt1_seed_epoch_ptr() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return nullptr;
+  return g_seed_epoch[dev];
+}
+// Register (or clear, with null) the current device's seed-epoch word: a caller-owned uint32 in device memory.
+RT1_API int rt1_set_seed_epoch(const void* dev_u32) {
+  int dev = 0;
+  RT1_CHECK_CUDA(cudaGetDevice(&dev));
+  RT1_REQUIRE(dev >= 0 && dev < kMaxDev, "rt1_set_seed_epoch: device %d out of range", dev);
+  g_seed_epoch[dev] = (const uint32_t*)dev_u32;
   return 0;
 }
 

@@ -68,6 +68,15 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
       : "memory");
 }
 
+// 4-D tiled load (NHWC activations: c0 = channel, c1 = x, c2 = y, c3 = frame); coordinates may be negative or run past
+// the tensor — out-of-bounds elements arrive as zeros, which is exactly a convolution's zero padding
+__device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
 // 2-D tiled store shared → global (bulk async group of the issuing thread); out-of-bounds box elements are clipped
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, uint32_t src_smem, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(reinterpret_cast<uint64_t>(m)),
@@ -162,3 +171,6 @@ rt1_encode_tiled_fn rt1_get_encode_tiled();
 // 2-D bf16 row-major tensor [rows, cols] (row stride `ld` elements), box = [box_rows, 64 cols], SWIZZLE_128B, zero OOB fill.
 int rt1_make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
                           uint32_t box_cols);
+// 4-D bf16 NHWC tensor [N, H, W, C] (dense), box = [1, box_h, box_w, box_c], no swizzle, zero OOB fill.
+int rt1_make_tmap_bf16_nhwc(CUtensorMap* out, const void* base, uint64_t N, uint64_t H, uint64_t W, uint64_t C, uint32_t box_h,
+                            uint32_t box_w, uint32_t box_c);

@@ -321,11 +321,7 @@ RT1_API int rt1_token_learner_fwd(const void* feats, const void* ln_w, const voi
   RT1_REQUIRE(C % 8 == 0 && C <= 512 && T <= 16, "rt1_token_learner_fwd: unsupported C=%d T=%d", C, T);
   const size_t smem = tl_smem_bytes(P, C, T, false);
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_token_learner_fwd: P=%d C=%d needs %zu B of shared memory", P, C, smem);
-  static size_t configured = 0;
-  if (smem > configured) {
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(tl_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if (int rc = rt1_ensure_dyn_smem((const void*)tl_fwd_kernel, smem)) return rc;
   TLDims d{P, C, T, eps};
   tl_fwd_kernel<<<n, TL_THREADS, smem, stream>>>((const bf16*)feats, (const bf16*)ln_w, (const bf16*)ln_b, (const bf16*)w1,
                                                  (const bf16*)b1, (const bf16*)w2, (const bf16*)b2, (bf16*)tokens, out_stride, d);
@@ -340,11 +336,7 @@ RT1_API int rt1_token_learner_bwd(const void* feats, const void* ln_w, const voi
   RT1_REQUIRE(C % 8 == 0 && C <= 512 && T <= 16, "rt1_token_learner_bwd: unsupported C=%d T=%d", C, T);
   const size_t smem = tl_smem_bytes(P, C, T, true);
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_token_learner_bwd: P=%d C=%d needs %zu B of shared memory", P, C, smem);
-  static size_t configured = 0;
-  if (smem > configured) {
-    RT1_CHECK_CUDA(cudaFuncSetAttribute(tl_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  if (int rc = rt1_ensure_dyn_smem((const void*)tl_bwd_kernel, smem)) return rc;
   const long ns = tl_scratch_floats(C, T);
   RT1_CHECK_CUDA(cudaMemsetAsync(scratch, 0, ns * sizeof(float), stream));
   TLDims d{P, C, T, eps};

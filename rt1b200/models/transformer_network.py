@@ -168,18 +168,27 @@ class TransformerNetwork(nn.Module):
         }
 
     # ------------------------------------------------------------- tokenizers
-    def _crop_shift(self, h: int, w: int) -> Tuple[int, int]:
+    def _crop_shift(self, h: int, w: int, device=None):
         if self._crop_shift_override is not None:
             return self._crop_shift_override
         if self._eval_center_crop and not self.training:
             return preprocessors.crop_pads(h, w)           # centred window == the un-shifted image
+        if getattr(self, "_device_rng", False) and device is not None and device.type == "cuda":
+            # sampled by the device RNG and read by the kernel when it runs (a captured step re-samples on every replay)
+            cache = self.__dict__.setdefault("_crop_hi_cache", {})
+            hi = cache.get((h, w, device))
+            if hi is None:                                   # built once, outside any capture (host → device copy)
+                ud, lr = preprocessors.crop_pads(h, w)
+                hi = cache[(h, w, device)] = torch.tensor([2 * ud + 1, 2 * lr + 1], device=device, dtype=torch.float32)
+            return torch.minimum((torch.rand(2, device=device) * hi).floor(), hi - 1).to(torch.int32)
         return preprocessors.sample_shift(h, w)
 
     def _encode_frames(self, image: torch.Tensor, context: Optional[torch.Tensor]) -> torch.Tensor:
         """``image`` ``[b, t, 3, h, w]`` → image tokens ``[b, t, n_tok, emb]`` (pre-processing included)."""
         b, t, c, h, w = image.shape
-        shift = self._crop_shift(h, w)
-        if ops.use_kernels(self._transformer._token_emb.weight) and image.is_cuda and context is not None:
+        use_k = ops.use_kernels(self._transformer._token_emb.weight) and image.is_cuda and context is not None
+        shift = self._crop_shift(h, w, image.device if use_k else None)
+        if use_k:
             frames = ops.preprocess_nhwc(image.reshape(b * t, c, h, w), shift)          # [bt,h,w,8] bf16
             return self._image_tokenizer.forward_nhwc(frames, context.to(torch.bfloat16), b, t)
         frames = preprocessors.convert_dtype_and_crop_images(image.reshape(b * t, c, h, w), shift=shift)

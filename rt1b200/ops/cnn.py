@@ -10,8 +10,9 @@ through the NHWC kernels in ``rt1b200.ops.kernels`` (K2–K8 of SURVEY §2.6):
               → [BN + stochastic depth + residual + FiLM affine]
   head      : 1x1 384→1536 + BN + SiLU → 1x1 1536→512 → FiLM
 
-Stages whose kernels are not enabled (``RT1B200_CNN_KERNELS`` mask, or a shape a kernel does not cover) run
-as channels-last PyTorch ops on the same bf16 tensors so the pipeline is always complete.
+``film_efficientnet_forward_torch`` is the same network on stock channels-last PyTorch ops (cuDNN / cuBLAS bf16).  It is
+NOT a product path: it exists as the library baseline of ``bench.py --cnn cudnn`` and as the bisecting arm of the tests
+(``force_torch_encoder``); on a GPU the product path is always the sm_100a kernels, and a missing library raises.
 """
 from __future__ import annotations
 
@@ -84,9 +85,26 @@ def film_efficientnet_forward_torch(encoder, image_nhwc: torch.Tensor, context: 
     return x.permute(0, 2, 3, 1).contiguous()
 
 
+_FORCE_TORCH = os.environ.get("RT1B200_CNN_BENCH_CUDNN", "0") == "1"     # set by `bench.py --cnn cudnn` only
+
+
+class force_torch_encoder:
+    """Test/bench helper: run the encoder on stock PyTorch ops inside the ``with`` block."""
+
+    def __enter__(self):
+        global _FORCE_TORCH
+        self._prev, _FORCE_TORCH = _FORCE_TORCH, True
+
+    def __exit__(self, *exc):
+        global _FORCE_TORCH
+        _FORCE_TORCH = self._prev
+
+
 def film_efficientnet_forward(encoder, image_nhwc: torch.Tensor, context: torch.Tensor) -> torch.Tensor:
     from . import _lib
-    if _lib.available() and os.environ.get("RT1B200_CNN_KERNELS", "1") != "0":
-        from . import kernels_cnn
-        return kernels_cnn.film_efficientnet_forward(encoder, image_nhwc, context)
-    return film_efficientnet_forward_torch(encoder, image_nhwc, context)
+    if _FORCE_TORCH or os.environ.get("RT1B200_CNN_BENCH_CUDNN", "0") == "1":
+        return film_efficientnet_forward_torch(encoder, image_nhwc, context)
+    if not _lib.available():
+        raise RuntimeError(f"rt1b200: the native kernel library is not loadable ({_lib.load_error()})")
+    from . import kernels_cnn
+    return kernels_cnn.film_efficientnet_forward(encoder, image_nhwc, context)

@@ -287,15 +287,37 @@ def action_ce_loss(logits, labels, num_items: float):
 
 # ----------------------------------------------------------------------------------------- pre-processing
 def preprocess_nhwc(image: torch.Tensor, shift, ratio: float = 0.07) -> torch.Tensor:
+    """``shift`` is ``(dh, dw)`` as Python ints, or an int32 device tensor ``[2]`` read by the kernel when it runs."""
     N, C, H, W = image.shape
     assert C == 3
     if image.dtype not in (torch.uint8, torch.float32):
         image = image.float()
     image = _c(image)
     out = torch.empty(N, H, W, 8, dtype=BF16, device=image.device)
-    call("rt1_preprocess_nhwc", ptr(image), i32(image.dtype == torch.uint8), ptr(out), i32(N), i32(H), i32(W),
-         i32(shift[0]), i32(shift[1]), i32(int(H * ratio)), i32(int(W * ratio)), stream())
+    if isinstance(shift, torch.Tensor):
+        assert shift.is_cuda and shift.dtype == torch.int32 and shift.numel() == 2
+        call("rt1_preprocess_nhwc_dev", ptr(image), i32(image.dtype == torch.uint8), ptr(out), i32(N), i32(H), i32(W),
+             ptr(shift), i32(int(H * ratio)), i32(int(W * ratio)), stream())
+    else:
+        call("rt1_preprocess_nhwc", ptr(image), i32(image.dtype == torch.uint8), ptr(out), i32(N), i32(H), i32(W),
+             i32(shift[0]), i32(shift[1]), i32(int(H * ratio)), i32(int(W * ratio)), stream())
     return out
+
+
+_seed_epoch = {}
+
+
+def seed_epoch_tensor(device) -> torch.Tensor:
+    """The device word added to every dropout seed on ``device`` (created and registered with the library on first use).
+    ``t.add_(odd constant)`` inside a captured step gives each replay its own dropout masks."""
+    device = torch.device(device)
+    t = _seed_epoch.get(device.index)
+    if t is None:
+        t = torch.zeros(1, dtype=torch.int32, device=device)
+        with torch.cuda.device(device):
+            call("rt1_set_seed_epoch", ptr(t))
+        _seed_epoch[device.index] = t
+    return t
 
 
 # ---------------------------------------------------------------------------------------------- optimizer

@@ -26,6 +26,8 @@ from ._lib import call, f32, i32, i64, ptr, stream
 from .kernels import BF16, _grad_slot, _ready, gemm, wgrad_lane
 
 F32 = torch.float32
+# BatchNorm+SiLU of the expand conv applied inside the depthwise tile (1) or materialised by an elementwise pass (0)
+_DW_ACT_ON_LOAD = os.environ.get("RT1B200_DW_ACT_ON_LOAD", "1") != "0"
 
 
 class _ZeroArena:
@@ -146,19 +148,14 @@ class _EncoderFn(Function):
         Ho, Wo = (H + 2 - 3) // 2 + 1, (W + 2 - 3) // 2 + 1
         stem_raw = _empty(N, Ho, Wo, C0, device=dev)
         bn0 = _BN(bn0m, dev)
-        stem_cols = None
-        if os.environ.get("RT1B200_STEM_GEMM", "1") != "0":
-            # 3x3 s2 stem as im2col (K = 27 padded to 32) + tcgen05 GEMM with the BatchNorm statistics in its epilogue
-            stem_cols = _empty(N * Ho * Wo, 32, device=dev)
-            call("rt1_stem_im2col", ptr(x8), ptr(stem_cols), i32(N), i32(H), i32(W), stream())
-            w32 = torch.nn.functional.pad(conv0.weight.detach().view(C0, 27), (0, 5))
-            gemm(stem_cols, w32, stem_raw.view(N * Ho * Wo, C0), N * Ho * Wo, C0, 32,
-                 col_sum=bn0.sum if training else None, col_sumsq=bn0.sumsq if training else None)
-            if not training:
-                stem_cols = None
-        else:
-            call("rt1_stem_fwd", ptr(x8), ptr(conv0.weight), ptr(stem_raw), ptr(bn0.sum if training else None),
-                 ptr(bn0.sumsq if training else None), i32(N), i32(H), i32(W), i32(C0), stream())
+        # 3x3 s2 stem as im2col (K = 27 padded to 32) + tcgen05 GEMM with the BatchNorm statistics in its epilogue
+        stem_cols = _empty(N * Ho * Wo, 32, device=dev)
+        call("rt1_stem_im2col", ptr(x8), ptr(stem_cols), i32(N), i32(H), i32(W), stream())
+        w32 = torch.nn.functional.pad(conv0.weight.detach().view(C0, 27), (0, 5))
+        gemm(stem_cols, w32, stem_raw.view(N * Ho * Wo, C0), N * Ho * Wo, C0, 32,
+             col_sum=bn0.sum if training else None, col_sumsq=bn0.sumsq if training else None)
+        if not training:
+            stem_cols = None
         bn0.finalize(N * Ho * Wo, training)
         x = _empty(N, Ho, Wo, C0, device=dev)
         call("rt1_bn_act_scale", ptr(stem_raw), ptr(bn0.a), ptr(bn0.b), ptr(None), ptr(x), i32(N), i32(Ho * Wo), i32(C0), i32(1),
@@ -178,12 +175,16 @@ class _EncoderFn(Function):
                 gemm(x.view(M, Cin), _conv_w2d(blk.expand[0]), e_raw.view(M, Ce), M, Ce, Cin,
                      col_sum=bn1.sum if training else None, col_sumsq=bn1.sumsq if training else None)
                 bn1.finalize(M, training)
-                # the depthwise window re-reads every input k*k/stride^2 times: activating on load would make the
-                # kernel MUFU-bound, so SiLU(BN1(.)) is materialised once (one extra read+write of the tensor)
-                e_act = _empty(N, Hc, Wc, Ce, device=dev)
-                call("rt1_bn_act_scale", ptr(e_raw), ptr(bn1.a), ptr(bn1.b), ptr(None), ptr(e_act), i32(N), i32(Hc * Wc), i32(Ce),
-                     i32(1), stream())
-                dw_in, a_in, b_in = e_act, None, None
+                if _DW_ACT_ON_LOAD:
+                    # SiLU(BN1(.)) is applied to the depthwise kernel's shared-memory tile (once per element and CTA):
+                    # the activated expand tensor never exists in HBM
+                    dw_in, a_in, b_in = e_raw, bn1.a, bn1.b
+                    e_act = None
+                else:
+                    e_act = _empty(N, Hc, Wc, Ce, device=dev)
+                    call("rt1_bn_act_scale", ptr(e_raw), ptr(bn1.a), ptr(bn1.b), ptr(None), ptr(e_act), i32(N), i32(Hc * Wc),
+                         i32(Ce), i32(1), stream())
+                    dw_in, a_in, b_in = e_act, None, None
                 st["e_raw"], st["e_act"], st["bn1"] = e_raw, e_act, bn1
             else:
                 dw_in, a_in, b_in = x, None, None
@@ -354,12 +355,14 @@ class _EncoderFn(Function):
             # depthwise conv
             dwc = blk.depthwise[0]
             has_exp = blk.expand is not None
-            dw_in = st["e_act"] if has_exp else x_in
+            act_on_load = has_exp and st["e_act"] is None
+            dw_in = (st["e_raw"] if act_on_load else st["e_act"]) if has_exp else x_in
+            wa, wb = (bn1.a, bn1.b) if act_on_load else (None, None)
             dw_slot = _grad_slot(dwc.weight)
 
-            def _dw_wgrad(dd_raw=dd_raw, dw_in=dw_in, dw_slot=dw_slot, k=k, s=s, Ce=Ce, Hin=Hin, Win=Win):
+            def _dw_wgrad(dd_raw=dd_raw, dw_in=dw_in, dw_slot=dw_slot, k=k, s=s, Ce=Ce, Hin=Hin, Win=Win, wa=wa, wb=wb):
                 scratch = _empty(k * k * Ce, device=dev, dtype=F32)
-                call("rt1_dwconv_wgrad", ptr(dd_raw), ptr(dw_in), ptr(None), ptr(None),
+                call("rt1_dwconv_wgrad", ptr(dd_raw), ptr(dw_in), ptr(wa), ptr(wb),
                      ptr(scratch), ptr(dw_slot), i32(N), i32(Hin), i32(Win), i32(Ce), i32(k), i32(s), stream())
             lane.run(_dw_wgrad, dd_raw, dw_in)
             ready.append(dwc.weight)
@@ -405,15 +408,10 @@ class _EncoderFn(Function):
              ptr(sums), i32(0), ptr(c1), ptr(c2), ptr(_grad_slot(b0.weight)), ptr(_grad_slot(b0.bias)), ptr(dstem), i32(N), i32(Hs * Ws),
              i32(C0), i32(1), stream())
         conv0 = net.convNormAct0[0]
-        if stem_cols is not None:
-            Ms = N * Hs * Ws
-            acc = _zeros(C0, 32, device=dev)
-            gemm(dstem.view(Ms, C0), stem_cols, acc, C0, 32, Ms, a_mn=True, b_mn=True, split_k=min(296, (Ms + 63) // 64))
-            _grad_slot(conv0.weight).view(C0, 27).copy_(acc[:, :27])
-        else:
-            scratch = _empty(27 * C0, device=dev, dtype=F32)
-            call("rt1_stem_wgrad", ptr(dstem), ptr(x8), ptr(scratch), ptr(_grad_slot(conv0.weight)), i32(N), i32(x8.shape[1]),
-                 i32(x8.shape[2]), i32(C0), stream())
+        Ms = N * Hs * Ws
+        acc = _zeros(C0, 32, device=dev)
+        gemm(dstem.view(Ms, C0), stem_cols, acc, C0, 32, Ms, a_mn=True, b_mn=True, split_k=min(296, (Ms + 63) // 64))
+        _grad_slot(conv0.weight).view(C0, 27).copy_(acc[:, :27])
         _ready([b0.weight, b0.bias, conv0.weight])
 
         # ---- FiLM projections: dW = dgb^T @ context, db = colsum(dgb) ---------------------------------------
@@ -451,8 +449,10 @@ def film_efficientnet_forward(enc, image_nhwc: torch.Tensor, context: torch.Tens
     sd = None
     if enc.training:
         # per-(block, frame) stochastic-depth scale keep/(1-p), "row" mode like torchvision's StochasticDepth
-        p = torch.tensor([b.drop_rate if b.has_skip else 0.0 for b in net.blocks], device=image_nhwc.device, dtype=F32)
-        keep = 1.0 - p
+        keep = enc.__dict__.get("_sd_keep")
+        if keep is None or keep.device != image_nhwc.device:      # built once (a host → device copy cannot be graph-captured)
+            p = torch.tensor([b.drop_rate if b.has_skip else 0.0 for b in net.blocks], device=image_nhwc.device, dtype=F32)
+            keep = enc.__dict__["_sd_keep"] = 1.0 - p
         sd = torch.bernoulli(keep[:, None].expand(-1, N)) / keep[:, None]
     anchors = [net.convNormAct0[0].weight] if torch.is_grad_enabled() and enc.training else []
     return _EncoderFn.apply(enc, image_nhwc.contiguous(), context, sd, *anchors)

@@ -51,8 +51,7 @@ def keep_bn_stats_fp32(model: nn.Module):
 class DataParallelEngine:
     def __init__(self, model: nn.Module, lr: float = 5e-4, betas: Tuple[float, float] = (0.9, 0.999),
                  eps: float = 1e-8, weight_decay: float = 0.0, param_dtype: Optional[torch.dtype] = None,
-                 backend: str = "auto", bucket_mb: Optional[float] = None, process_group=None, overlap: bool = True,
-                 grad_accum_steps: int = 1):
+                 backend: str = "auto", bucket_mb: Optional[float] = None, process_group=None, overlap: bool = True):
         self.model = model
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.step_count = 0
@@ -62,13 +61,20 @@ class DataParallelEngine:
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
         dev = next(model.parameters()).device
         self.device = dev
+        eff_dtype = param_dtype if param_dtype is not None else next(model.parameters()).dtype
+        # the fused P2P kernels exchange bf16 gradients and write bf16 parameters into peer-mapped buffers: they exist
+        # for the bf16 model only (fp32 parameters alias the master buffer, which is not symmetric memory)
+        p2p_ok = dev.type == "cuda" and _lib.available() and eff_dtype == torch.bfloat16
         if backend == "auto":
             if self.world == 1:
                 backend = "local"
-            elif dev.type == "cuda" and _lib.available():
+            elif p2p_ok:
                 backend = "p2p"
             else:
                 backend = "torchdist"
+        elif backend == "p2p" and not p2p_ok:
+            raise ValueError("backend='p2p' needs CUDA, the native library and bfloat16 parameters "
+                             f"(device {dev}, param dtype {eff_dtype}); use backend='torchdist' for fp32 parameters")
         self.backend = backend
         self.comm = None
         grad_alloc = None
@@ -76,10 +82,11 @@ class DataParallelEngine:
             from .symm import SymmetricComm
             self.comm = SymmetricComm(process_group)
             grad_alloc = self.comm.alloc_tensor
-        if param_dtype is not None and param_dtype != next(model.parameters()).dtype:
-            model.to(param_dtype)
-            keep_bn_stats_fp32(model)
+        # No `model.to(param_dtype)` here: FlatParams builds the fp32 master from the parameters as they are (full
+        # precision) and re-homes every parameter as a `param_dtype` view of its flat buffer; the only other floating
+        # tensors of this model are BatchNorm running statistics, which stay fp32 on purpose.
         self.flat = FlatParams(model, param_dtype=param_dtype, device=dev, grad_alloc=grad_alloc)
+        keep_bn_stats_fp32(model)
         elem = self.flat.grad.element_size()
         if bucket_mb is None:
             # Few, large buckets: every fused exchange pays two cross-GPU barriers (~15 us) and the whole gradient
@@ -125,7 +132,7 @@ class DataParallelEngine:
         self._ready_count = [0] * len(self.buckets)
         self._launched = [False] * len(self.buckets)
         self._hook_handles = []
-        self._eager = False       # set by begin_step(); hooks are inert otherwise (e.g. grad accumulation)
+        self._eager = False       # set by begin_step(); hooks are inert otherwise
         if not hasattr(torch.Tensor, "register_post_accumulate_grad_hook"):
             return
         self._expected = [0] * len(self.buckets)
@@ -160,8 +167,10 @@ class DataParallelEngine:
         self.flat.rebind_grads()
 
     def begin_step(self, lr: Optional[float] = None, never_ready: Tuple[str, ...] = ("_action_token_emb",)):
-        """Arm the overlap path: call right before ``loss.backward()`` of the step's last micro-batch.
-        Parameters whose names match ``never_ready`` get no gradient in this model; they are pre-counted."""
+        """Arm the overlap path: call right before the step's ONE ``loss.backward()``.  (The kernel wrappers WRITE parameter
+        gradients into the flat buffer rather than accumulating, so a step is exactly one backward pass; accumulate
+        micro-batches by enlarging the batch.)  Parameters whose names match ``never_ready`` get no gradient in this
+        model; they are pre-counted."""
         if not self.overlap:
             return
         self._step_lr = self.lr if lr is None else lr
@@ -246,6 +255,9 @@ class DataParallelEngine:
         if self.world == 1:
             return t
         if self.backend == "p2p":
+            # the small collectives share the flag pad and epoch counter of the fused buckets, which run on the side stream
+            # between begin_step() and step(): a collective issued in that window would interleave epochs across streams
+            assert not self._eager, "all_reduce_mean() must not be called between begin_step() and step()"
             return self.comm.allreduce_small(t.float()) / self.world
         dist = _dist()
         t = t.clone()

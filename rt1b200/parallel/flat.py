@@ -97,8 +97,11 @@ class FlatParams:
         self.by_name: Dict[str, Slot] = {s.name: s for s in self.slots}
 
         self.master = torch.zeros(self.numel, dtype=torch.float32, device=self.device)
-        for s, p in zip(self.slots, self.params):
-            self.master[s.offset:s.offset + s.numel].copy_(p.detach().reshape(-1).to(self.device, torch.float32))
+        # one multi-tensor copy (a handful of launches) instead of one conversion + one copy kernel per parameter
+        dst = [self.master[s.offset:s.offset + s.numel] for s in self.slots]
+        src = [p.detach().reshape(-1).to(self.device) for p in self.params]
+        torch._foreach_copy_(dst, src)
+        del dst, src
         if self.param_dtype == torch.float32:
             self.param = self.master                      # fp32 training: parameters ARE the master copy
         elif grad_alloc is not None:                       # peer-visible parameter buffer (P2P all-gather target)

@@ -147,9 +147,95 @@ class TensorBoardLogger:
             self.writer.flush()
 
 
+def _tree_leaves(b):
+    if isinstance(b, dict):
+        for v in b.values():
+            yield from _tree_leaves(v)
+    else:
+        yield b
+
+
+def _tree_map(fn, b):
+    return {k: _tree_map(fn, v) for k, v in b.items()} if isinstance(b, dict) else fn(b)
+
+
+class GraphedTrainStep:
+    """Forward + backward of one training step as ONE CUDA-graph replay.
+
+    An RT-1 step is ~1 100 kernel launches of 5-300 µs; issued one by one from Python the host, not the GPU, sets the
+    step time (measured: 28.9 ms per step for ~20 ms of GPU work).  The step is therefore captured once — over static
+    input buffers, with the weight-gradient lane as a parallel branch of the graph — and replayed with a single launch.
+    What varies from step to step lives in device memory and is advanced by nodes of the graph itself: the pad-shift
+    crop offset (device RNG → ``rt1_preprocess_nhwc_dev``), the stochastic-depth masks (torch's graph-safe Philox
+    state) and the dropout seed epoch (``rt1_set_seed_epoch``).  Gradients land in the engine's flat buffer; the fused
+    gradient exchange + AdamW runs right after the replay (its learning rate, bias corrections and cross-GPU epoch
+    flags change every step, so it stays outside the graph)."""
+
+    def __init__(self, trainer: "Trainer", template_batch):
+        from ..ops import kernels
+        self.tr = trainer
+        dev = trainer.device
+        self.static = _tree_map(lambda t: torch.empty_like(t), template_batch)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.seed_epoch = kernels.seed_epoch_tensor(dev)
+        self.stream = torch.cuda.Stream(device=dev)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self._encoders = None
+
+    def _body(self):
+        tr = self.tr
+        self.seed_epoch.add_(0x61C88647)                         # fresh dropout masks on every replay
+        loss = tr.module.training_step(self.static, 0)
+        loss.backward()
+        self.loss.copy_(loss.detach().float())
+
+    def _fill(self, batch):
+        for d, s in zip(_tree_leaves(self.static), _tree_leaves(batch)):
+            d.copy_(s, non_blocking=True)
+
+    def capture(self, batch):
+        """Warm up once on the capture stream (lazy per-stream state: the weight-gradient lane, tensor-map caches, function
+        attributes), then record."""
+        tr = self.tr
+        dev = tr.device
+        tr.module.model._device_rng = True
+        main = torch.cuda.current_stream(dev)
+        self._fill(batch)
+        self.stream.wait_stream(main)
+        with torch.cuda.stream(self.stream):
+            tr.engine.zero_grad()
+            self._body()
+            tr.engine.zero_grad()                                 # the warm-up's gradients are not a training step
+        main.wait_stream(self.stream)
+        torch.cuda.synchronize(dev)
+        self._undo_counters()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, stream=self.stream):
+            self._body()
+        self._undo_counters()
+
+    def _bn_encoders(self):
+        if self._encoders is None:
+            from ..models.film_efficientnet import EfficientNetEncoder
+            self._encoders = [m for m in self.tr.module.modules() if isinstance(m, EfficientNetEncoder)]
+        return self._encoders
+
+    def _undo_counters(self):
+        for m in self._bn_encoders():                             # warm-up / capture are not optimisation steps
+            m._nbt_pending = max(0, getattr(m, "_nbt_pending", 0) - 1)
+
+    def run(self, batch) -> torch.Tensor:
+        self._fill(batch)
+        self.graph.replay()
+        for m in self._bn_encoders():                             # the Python-side step counter of the BatchNorm buffers
+            m._nbt_pending = getattr(m, "_nbt_pending", 0) + 1
+        return self.loss
+
+
 class Trainer:
     def __init__(self, module: RT1Module, args: Namespace, device=None, backend: str = "auto",
-                 param_dtype: Optional[torch.dtype] = None, loggers=None, verbose: bool = True):
+                 param_dtype: Optional[torch.dtype] = None, loggers=None, verbose: bool = True,
+                 graph: Optional[bool] = None):
         self.module, self.args = module, args
         self.device = torch.device(device) if device is not None else torch.device("cpu")
         module.to(self.device)
@@ -165,6 +251,14 @@ class Trainer:
         self.ckpt_dir = os.path.join(args.ckpt_dir, args.exp_name)
         self.log_every = max(1, getattr(args, "log_every_n_steps", 50))
         self.last_metrics: Dict[str, float] = {}
+        # CUDA-graph the step (bf16 kernel path only); RT1B200_TRAIN_GRAPH=0 or graph=False keeps the eager schedule
+        if graph is None:
+            graph = os.environ.get("RT1B200_TRAIN_GRAPH", "1") != "0"
+        from ..ops import _lib as _native
+        self._graph_on = bool(graph and self.device.type == "cuda" and param_dtype == torch.bfloat16 and _native.available())
+        self._graphs: Dict[tuple, GraphedTrainStep] = {}
+        self._graph_seen: Dict[tuple, int] = {}
+        self.graph_warmup_steps = 2          # eager steps per batch signature before its graph is captured
 
     def _default_loggers(self):
         a = self.args
@@ -209,6 +303,13 @@ class Trainer:
         batch = self._to_device(batch)
         self.module.train()
         lr = self.sched.get_lr()
+        g = self._graph_for(batch) if self._graph_on else None
+        if g is not None:
+            loss = g.run(batch)                       # forward + backward: one graph replay
+            self._stage_loss(loss)
+            self.engine.step(lr)                      # fused gradient exchange + AdamW (clears the gradients)
+            self.global_step += 1
+            return loss
         loss = self.module.training_step(batch, self.global_step)
         self._stage_loss(loss)
         self.engine.begin_step(lr)
@@ -216,6 +317,33 @@ class Trainer:
         self.engine.step(lr)
         self.global_step += 1
         return loss.detach()
+
+    def _graph_for(self, batch) -> Optional[GraphedTrainStep]:
+        """The captured step for this batch signature, once ``graph_warmup_steps`` eager steps have run with it."""
+        key = tuple((tuple(t.shape), t.dtype) for t in _tree_leaves(batch))
+        g = self._graphs.get(key)
+        if g is not None:
+            return g
+        n = self._graph_seen.get(key, 0)
+        self._graph_seen[key] = n + 1
+        if n < self.graph_warmup_steps:
+            return None
+        g = GraphedTrainStep(self, batch)
+        try:
+            g.capture(batch)
+        except Exception as e:                         # keep training on the eager schedule rather than die in set-up
+            self._graph_on = False
+            self.module.model._device_rng = False
+            torch.cuda.synchronize(self.device)
+            self.engine.zero_grad()
+            if self.verbose or os.environ.get("RT1B200_TRAIN_GRAPH_STRICT", "0") == "1":
+                print(f"[rt1b200] CUDA-graph capture of the training step failed ({type(e).__name__}: {e}); "
+                      "continuing with the eager schedule", flush=True)
+            if os.environ.get("RT1B200_TRAIN_GRAPH_STRICT", "0") == "1":
+                raise
+            return None
+        self._graphs[key] = g
+        return g
 
     def _stage_loss(self, loss: torch.Tensor):
         """Copy the step's loss to pinned host memory on a side stream as soon as the FORWARD has produced it, so that

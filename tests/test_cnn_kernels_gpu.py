@@ -73,24 +73,29 @@ def test_dwconv_fwd_bwd_wgrad(k, s, with_bn, C, H, W):
         assert _rel(_nchw(din), xr.grad) < 2e-2
 
 
-def test_stem_fwd_wgrad():
+def test_stem_im2col_gemm_fwd_wgrad():
+    """The stem runs as im2col (K = 27 -> 32) + tcgen05 GEMM; the weight gradient is the split-K GEMM over the same columns."""
+    from rt1b200.ops.kernels import gemm
     N, H, W, CO = 2, 64, 96, 40
     x8 = torch.zeros(N, H, W, 8, dtype=BF, device=DEV)
     x8[..., :3] = _bf(N, H, W, 3, seed=1)
     w = _bf(CO, 3, 3, 3, scale=0.3, seed=2)
     Ho, Wo = H // 2, W // 2
+    M = N * Ho * Wo
+    cols = torch.empty(M, 32, dtype=BF, device=DEV)
+    call("rt1_stem_im2col", ptr(x8), ptr(cols), i32(N), i32(H), i32(W), stream())
+    w32 = F.pad(w.view(CO, 27), (0, 5))
     y = torch.empty(N, Ho, Wo, CO, dtype=BF, device=DEV)
     s1, s2 = torch.zeros(CO, device=DEV), torch.zeros(CO, device=DEV)
-    call("rt1_stem_fwd", ptr(x8), ptr(w), ptr(y), ptr(s1), ptr(s2), i32(N), i32(H), i32(W), i32(CO), stream())
+    gemm(cols, w32, y.view(M, CO), M, CO, 32, col_sum=s1, col_sumsq=s2)
     wr = w.float().requires_grad_()
     yr = F.conv2d(_nchw(x8[..., :3]), wr, None, 2, 1)
     assert _rel(_nchw(y), yr) < 1e-2 and _rel(s1, yr.sum((0, 2, 3))) < 2e-2
     g = _bf(N, Ho, Wo, CO, seed=3)
     yr.backward(_nchw(g))
-    scratch = torch.empty(27 * CO, device=DEV)
-    dw = torch.empty_like(w)
-    call("rt1_stem_wgrad", ptr(g), ptr(x8), ptr(scratch), ptr(dw), i32(N), i32(H), i32(W), i32(CO), stream())
-    assert _rel(dw, wr.grad) < 2e-2
+    acc = torch.zeros(CO, 32, device=DEV)
+    gemm(g.view(M, CO), cols, acc, CO, 32, M, a_mn=True, b_mn=True, split_k=8)
+    assert _rel(acc[:, :27].reshape(CO, 3, 3, 3), wr.grad) < 2e-2
 
 
 @pytest.mark.parametrize("skip,film,bn", [(True, True, True), (False, True, True), (False, True, False), (True, False, True)])
@@ -253,12 +258,9 @@ def test_full_encoder_matches_fp32_module(training):
     torch_bf16 = copy.deepcopy(fast)
     for p_ in torch_bf16.parameters():
         p_.grad = None
-    os.environ["RT1B200_CNN_KERNELS"] = "0"
-    try:
+    with ops.cnn.force_torch_encoder():
         out_t = torch_bf16.forward_nhwc(x8, ctx, b, t)
         out_t.backward(g)
-    finally:
-        os.environ["RT1B200_CNN_KERNELS"] = "1"
     bad, n_cmp = [], 0
     for (n, pr), pf, pt in zip(ref.named_parameters(), fast.parameters(), torch_bf16.parameters()):
         assert pf.grad is not None, n

@@ -8,15 +8,65 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _trainer(seed=0, hw=(64, 96)):
+def _trainer(seed=0, hw=(64, 96), graph=False, dropout=0.0):
     from rt1b200.models.factory import RT1Config
     from rt1b200.train.trainer import RT1Module, Trainer
     torch.manual_seed(seed)
     (H, W), T = hw, 3
     args = Namespace(height=H, width=W, seq_len=T, lr=1e-3, milestones=[], exp_name="t", log_dir="/tmp/rt1_t/logs",
                      ckpt_dir="/tmp/rt1_t/ckpt", log_every_n_steps=10 ** 9, ckpt_every_n_epochs=1, max_epochs=1)
-    cfg = RT1Config.language_table(height=H, width=W, seq_len=T, num_layers=2, dropout_rate=0.0)
-    return Trainer(RT1Module(args, cfg), args, device=torch.device("cuda", 0), param_dtype=torch.bfloat16, loggers=[], verbose=False)
+    cfg = RT1Config.language_table(height=H, width=W, seq_len=T, num_layers=2, dropout_rate=dropout)
+    return Trainer(RT1Module(args, cfg), args, device=torch.device("cuda", 0), param_dtype=torch.bfloat16, loggers=[], verbose=False,
+                   graph=graph)
+
+
+def test_graphed_step_matches_eager_schedule(monkeypatch):
+    """The captured step (one graph replay + the fused optimizer) trains like the eager kernel schedule: same losses over
+    several steps with the randomness switched off, and the BatchNorm step counters advance once per optimisation step."""
+    from rt1b200.data.dataset import SyntheticBatchSource
+    from rt1b200.ops.kernels_cnn import flush_bn_counters
+    monkeypatch.setenv("RT1B200_TRAIN_GRAPH_STRICT", "1")
+    src = SyntheticBatchSource(2, 3, 64, 96, pool=2, seed=4, image_dtype=torch.uint8, pin=False)
+    a, b = _trainer(seed=5, graph=False), _trainer(seed=5, graph=True)
+    for tr in (a, b):
+        tr.module.model._crop_shift_override = (3, 5)
+        for m in tr.module.modules():
+            if hasattr(m, "drop_rate"):
+                m.drop_rate = 0.0
+    la, lb = [], []
+    for i in range(6):
+        la.append(float(a.train_step(src.pool[i % 2])))
+        lb.append(float(b.train_step(src.pool[i % 2])))
+    torch.cuda.synchronize()
+    assert len(b._graphs) == 1 and b._graph_on, "the step was not captured"
+    torch.testing.assert_close(torch.tensor(lb), torch.tensor(la), rtol=3e-2, atol=2e-4)
+    for tr in (a, b):
+        flush_bn_counters(tr.module.model)
+    na = [int(m.num_batches_tracked) for m in a.module.modules() if isinstance(m, torch.nn.BatchNorm2d)]
+    nb = [int(m.num_batches_tracked) for m in b.module.modules() if isinstance(m, torch.nn.BatchNorm2d)]
+    assert na == nb and na[0] == 6
+
+
+def test_graphed_step_resamples_randomness_per_replay():
+    """Replays of the captured step must not repeat the crop offset or the dropout masks: the same batch gives different
+    losses from replay to replay (and the seed-epoch word advances)."""
+    from rt1b200.data.dataset import SyntheticBatchSource
+    from rt1b200.ops import kernels
+    src = SyntheticBatchSource(2, 3, 64, 96, pool=1, seed=6, image_dtype=torch.uint8, pin=False)
+    tr = _trainer(seed=7, graph=True, dropout=0.1)
+    for _ in range(3):
+        tr.train_step(src.pool[0])
+    assert len(tr._graphs) == 1
+    g = next(iter(tr._graphs.values()))
+    e0 = int(kernels.seed_epoch_tensor(tr.device).item())
+    snap = tr.engine.flat.master.clone(), tr.engine.flat.param.clone()
+    losses = []
+    for _ in range(4):                                      # same weights, same batch: only the sampled randomness differs
+        tr.engine.flat.master.copy_(snap[0]); tr.engine.flat.param.copy_(snap[1])
+        tr.engine.flat.exp_avg.zero_(); tr.engine.flat.exp_avg_sq.zero_()
+        losses.append(float(tr.train_step(src.pool[0])))
+    assert int(kernels.seed_epoch_tensor(tr.device).item()) != e0
+    assert len(set(round(l, 7) for l in losses)) > 1, losses
 
 
 def test_prefetch_and_read_loss_match_inline_path():

@@ -37,8 +37,8 @@ out_r.backward(g.float()); out_f.backward(g)
 t16 = copy.deepcopy(fast)
 for p in t16.parameters():
     p.grad = None
-os.environ["RT1B200_CNN_KERNELS"] = "0"
-out_t = t16.forward_nhwc(x8, ctx, b, t); out_t.backward(g)
+with ops.cnn.force_torch_encoder():
+    out_t = t16.forward_nhwc(x8, ctx, b, t); out_t.backward(g)
 rows = []
 for (n, pr), pf, pt in zip(ref.named_parameters(), fast.parameters(), t16.parameters()):
     if float(pr.grad.norm()) < 1e-8:

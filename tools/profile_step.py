@@ -10,7 +10,7 @@ import torch  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--batch", type=int, default=8)
-ap.add_argument("--warmup", type=int, default=2)
+ap.add_argument("--warmup", type=int, default=4)
 a = ap.parse_args()
 from argparse import Namespace  # noqa: E402
 from rt1b200.data.dataset import SyntheticBatchSource, to_device  # noqa: E402
