@@ -1,12 +1,74 @@
-"""State (de)serialisation helpers (reference ``environments/utils/utils_pybullet.py:252-446``): object/arm state
-records and gz-compressed JSON state files.  The URDF loading / Bullet ray-cast helpers of the original have no
-counterpart (no physics engine on this box)."""
+"""Camera-ray geometry and state (de)serialisation helpers of the reference's ``environments/utils/utils_pybullet.py``.
+
+* view-matrix decomposition, pixel → view ray → world ray, ray/plane intersection and the workspace plane
+  (reference ``:115-206``) — plain linear algebra, no Bullet client involved;
+* object/arm state records and gz-compressed JSON state files (reference ``:252-446``).
+``load_urdf`` of the original is replaced by the parsers in ``rt1b200.envs.assets`` (no physics engine on this box).
+"""
 import dataclasses
 import gzip
 import json
 from typing import Any, Dict, List, Optional
 
 import numpy as np
+
+from rt1b200.envs import camera as _cam
+
+
+def pybullet_mat_to_numpy_4x4(pybullet_matrix):
+    """16-element column-major matrix (Bullet / OpenGL order) → 4x4 numpy array."""
+    return _cam.mat4(pybullet_matrix)
+
+
+def decompose_view_matrix(pybullet_view_matrix):
+    """Rigid view matrix → (camera position in the world, camera orientation as an (x, y, z, w) quaternion)."""
+    view_to_world = np.linalg.inv(pybullet_mat_to_numpy_4x4(pybullet_view_matrix))
+    return view_to_world[:3, 3].copy(), _cam.quaternion_from_matrix(view_to_world[:3, :3])
+
+
+def world_obj_to_view(world_xyz_obj, world_quat_obj, camera_view, client=None):
+    """Pose of an object expressed in the camera (view) frame; ``client`` is accepted for signature parity and unused."""
+    world_to_view = pybullet_mat_to_numpy_4x4(camera_view)
+    xyz = world_to_view[:3, :3] @ np.asarray(world_xyz_obj, np.float64) + world_to_view[:3, 3]
+    rot = world_to_view[:3, :3] @ _cam.matrix_from_quaternion(world_quat_obj)
+    return xyz, _cam.quaternion_from_matrix(rot)
+
+
+def image_xy_to_view_ray(xy, cam_width, cam_height, proj_mat_inv):
+    """Pixel (x right, y down) → ray through it in view space: (origin = camera centre, unit direction)."""
+    ndc = np.array([2.0 * xy[0] / cam_width - 1.0, 1.0 - 2.0 * xy[1] / cam_height, 0.0, 1.0])
+    eye = np.asarray(proj_mat_inv, np.float64) @ ndc
+    d = eye[:3]
+    return np.zeros(3), d / max(float(np.linalg.norm(d)), 1e-6)
+
+
+def view_ray_to_world_ray(origin, vec, view_mat_inv):
+    m = np.asarray(view_mat_inv, np.float64)
+    return (m @ np.append(origin, 1.0))[:3], (m @ np.append(vec, 0.0))[:3]
+
+
+def ray_to_plane_test(ray_origin, ray_vec, plane_origin, plane_normal):
+    """Intersection point of a ray with a plane, or ``None`` (parallel, or the plane is behind the origin)."""
+    ray_origin, ray_vec = np.asarray(ray_origin, np.float64), np.asarray(ray_vec, np.float64)
+    plane_origin, plane_normal = np.asarray(plane_origin, np.float64), np.asarray(plane_normal, np.float64)
+    denom = float(plane_normal @ ray_vec)
+    if abs(denom) < np.finfo(np.float32).eps:
+        return None
+    t = float(plane_normal @ (plane_origin - ray_origin)) / denom
+    return ray_origin + t * ray_vec if t >= 0 else None
+
+
+def get_workspace(env=None):
+    """Origin and normal of the board plane (the reference queries Bullet for the pose of ``workspace_real.urdf``,
+    which it spawns at (0.35, 0, 0) with identity orientation: ``language_table.py:560-563``)."""
+    return np.array([0.35, 0.0, 0.0]), np.array([0.0, 0.0, 1.0])
+
+
+def pixel_to_workspace(xy, viewm, projm, cam_width, cam_height):
+    """Where the ray through pixel ``xy`` meets the board — the composition the reference's GUI tools perform."""
+    o, d = image_xy_to_view_ray(xy, cam_width, cam_height, np.linalg.inv(pybullet_mat_to_numpy_4x4(projm)))
+    o, d = view_ray_to_world_ray(o, d, np.linalg.inv(pybullet_mat_to_numpy_4x4(viewm)))
+    return ray_to_plane_test(o, d, *get_workspace())
 
 
 @dataclasses.dataclass

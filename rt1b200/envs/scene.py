@@ -1,11 +1,15 @@
 """Scene description of the Language-Table board: block outlines → prism meshes, the pinhole camera, and projection of
 every environment's triangles to screen space.
 
-Stand-in for the URDF/OBJ assets + PyBullet camera of the reference (``language_table/environments/assets``,
-``language_table.py:365-397``, ``constants.py:43-58``).  The meshes are procedural (square, regular pentagon, five-point
-star, crescent) rather than the vendored OBJ files; the camera reproduces the reference's parameters exactly:
-position (0.75, 0, 0.5), orientation Euler (pi/5, pi, -pi/2) in PyBullet's convention, look direction R·(0,0,1), up
-R·(0,-1,0), focal length 0.803·W pixels, 320x180 image.
+Replaces the URDF/OBJ loading + PyBullet camera of the reference (``language_table/environments/assets``,
+``language_table.py:365-397,550-570,648-662``, ``constants.py:43-58``).  When the reference's asset directory is
+installed (``rt1b200.envs.assets.find_asset_dir``) the scene is built from the SAME files: the four block meshes
+(cube/moon 112, pentagon 105, star 175 faces) with the colours of the 16 block URDFs, the purple pole, the board plane of
+``workspace_real.urdf`` and the cylinder effector of ``suction/cylinder_real.urdf``; faces are flat-shaded (ambient +
+Lambert term, the coefficients PyBullet's TinyRenderer defaults to) with the block's current yaw.  Without the assets
+the meshes are procedural prisms (square, regular pentagon, five-point star, crescent).  The camera reproduces the
+reference's parameters exactly: position (0.75, 0, 0.5), orientation Euler (pi/5, pi, -pi/2) in PyBullet's convention,
+look direction R·(0,0,1), up R·(0,-1,0), focal length 0.803·W pixels, 320x180 image.
 """
 from __future__ import annotations
 
@@ -18,12 +22,17 @@ import torch
 from language_table.environments import blocks as blocks_module
 from language_table.environments import constants as C
 
+from . import assets
+
 TABLE_RGB = (196.0, 180.0, 150.0)
 BOARD_RGB = (230.0, 222.0, 205.0)
 BACKGROUND_RGB = (90.0, 90.0, 96.0)
 EFFECTOR_RGB = (40.0, 40.0, 44.0)
 EFFECTOR_SIDES = 12
 EFFECTOR_TOP = 0.10
+EFFECTOR_CLEARANCE = 0.012                       # lowest point of the effector mesh above the board (asset scene)
+LIGHT_DIR = np.array([1.0, 1.0, 1.0]) / math.sqrt(3.0)
+LIGHT_AMBIENT, LIGHT_DIFFUSE = 0.6, 0.35          # TinyRenderer's default coefficients (specular left out)
 
 
 def _regular(n: int, r: float, phase: float = 0.0) -> np.ndarray:
@@ -99,36 +108,65 @@ def camera() -> Dict[str, np.ndarray]:
 class SceneBuilder:
     """Builds the per-environment triangle list [E, T, 12] (screen x, y, 1/depth per vertex + RGB) on any device."""
 
-    def __init__(self, block_names: List[str], device="cpu"):
+    def __init__(self, block_names: List[str], device="cpu", use_assets=None):
         self.device = torch.device(device)
         self.block_names = list(block_names)
         cam = camera()
         self.cam = {k: torch.as_tensor(v, dtype=torch.float32, device=self.device) for k, v in cam.items()}
         static = []
+        board = assets.workspace_mesh() if (assets.find_asset_dir() is not None and use_assets is not False) else None
         # table slab (a little larger than the workspace) and the board surface, both at z = 0 (+epsilon ordering by size)
         for (x0, x1, y0, y1, z, rgb) in ((C.X_MIN - 0.25, C.X_MAX + 0.25, C.Y_MIN - 0.35, C.Y_MAX + 0.35, -0.002, TABLE_RGB),
                                           (C.X_MIN - 0.02, C.X_MAX + 0.02, C.Y_MIN - 0.02, C.Y_MAX + 0.02, 0.0, BOARD_RGB)):
             q = np.array([[x0, y0, z], [x1, y0, z], [x1, y1, z], [x0, y1, z]], np.float32)
             static += [(q[[0, 1, 2]], rgb), (q[[0, 2, 3]], rgb)]
+        if board is not None:                       # the board plane of workspace_real.urdf, placed at (0.35, 0, 0)
+            bt = board["tris"] + np.array([0.35, 0.0, 0.0], np.float32)
+            static = static[:2] + [(t, tuple(LIGHT_AMBIENT * 255.0 * 0 + c for c in board["rgb"])) for t in bt]
         self.static_tris = torch.as_tensor(np.stack([t for t, _ in static]), device=self.device)
         self.static_rgb = torch.as_tensor(np.array([c for _, c in static], np.float32), device=self.device)
-        meshes, colors, owner = [], [], []
+        self.use_assets = (assets.find_asset_dir() is not None) if use_assets is None else bool(use_assets)
+        if self.use_assets and assets.find_asset_dir() is None:
+            raise FileNotFoundError("Language-Table assets requested but no asset directory was found (RT1B200_ASSET_DIR)")
+        meshes, colors, owner, normals = [], [], [], []
         for bi, name in enumerate(self.block_names):
             color, shape = name.split("_")
-            m = prism(shape)
+            got = assets.block_mesh(name) if self.use_assets else None
+            if got is not None:
+                m, rgb = got
+                colors.append(np.repeat(np.array(rgb, np.float32)[None], len(m), 0))
+                normals.append(assets.face_normals(m))
+            else:
+                m = prism(shape)
+                shade = np.ones((len(m), 1), np.float32)
+                shade[-2 * len(outline(shape)):] = 0.72                  # side walls darker than the top cap
+                colors.append(np.array(blocks_module.RGB[color], np.float32)[None] * shade)
+                normals.append(np.zeros((len(m), 3), np.float32))          # zero normal = colour already final
             meshes.append(m)
-            shade = np.ones((len(m), 1), np.float32)
-            shade[-2 * len(outline(shape)):] = 0.72                      # side walls darker than the top cap
-            colors.append(np.array(blocks_module.RGB[color], np.float32)[None] * shade)
             owner += [bi] * len(m)
         self.block_tris = torch.as_tensor(np.concatenate(meshes), device=self.device)          # [Tb, 3, 3] local
         self.block_rgb = torch.as_tensor(np.concatenate(colors), device=self.device)
+        self.block_nrm = torch.as_tensor(np.concatenate(normals), device=self.device)          # [Tb, 3] local, or 0
         self.block_owner = torch.as_tensor(owner, device=self.device, dtype=torch.long)
-        eff = prism("pole", EFFECTOR_TOP, C.EFFECTOR_RADIUS / 0.6)
-        self.eff_tris = torch.as_tensor(eff, device=self.device)
-        shade = np.ones((len(eff), 1), np.float32)
-        shade[-16:] = 0.75
-        self.eff_rgb = torch.as_tensor(np.array(EFFECTOR_RGB, np.float32)[None] * shade, device=self.device)
+        self.light = torch.as_tensor(LIGHT_DIR, dtype=torch.float32, device=self.device)
+        eff_vis = assets.effector_mesh() if self.use_assets else None
+        if eff_vis:
+            down = np.diag([-1.0, 1.0, -1.0])                             # tool z points at the board (rotvec [0, pi, 0])
+            parts = [(v["tris"].reshape(-1, 3) @ down.T).reshape(-1, 3, 3) for v in eff_vis]
+            zmin = min(float(p[..., 2].min()) for p in parts)
+            eff = np.concatenate(parts).astype(np.float32)
+            eff[..., 2] += EFFECTOR_CLEARANCE - zmin
+            n = assets.face_normals(eff)
+            shade = LIGHT_AMBIENT + LIGHT_DIFFUSE * np.clip(n @ LIGHT_DIR, 0.0, None)           # the effector never rotates
+            rgb = np.concatenate([np.repeat(np.array(v["rgb"], np.float32)[None], len(p), 0) for v, p in zip(eff_vis, parts)])
+            self.eff_tris = torch.as_tensor(eff, device=self.device)
+            self.eff_rgb = torch.as_tensor((rgb * shade[:, None]).astype(np.float32), device=self.device)
+        else:
+            eff = prism("pole", EFFECTOR_TOP, C.EFFECTOR_RADIUS / 0.6)
+            self.eff_tris = torch.as_tensor(eff, device=self.device)
+            shade = np.ones((len(eff), 1), np.float32)
+            shade[-16:] = 0.75
+            self.eff_rgb = torch.as_tensor(np.array(EFFECTOR_RGB, np.float32)[None] * shade, device=self.device)
         self.max_tris = len(self.static_tris) + len(self.block_tris) + len(self.eff_tris)
 
     def project(self, world: torch.Tensor) -> torch.Tensor:
@@ -155,7 +193,13 @@ class SceneBuilder:
         ew[..., 1] += effector_xy[:, None, None, 1]
         world = torch.cat([self.static_tris[None].expand(E, -1, -1, -1), bw, ew], 1)         # [E,T,3,3]
         scr = self.project(world).reshape(E, -1, 9)
-        rgb = torch.cat([self.static_rgb, self.block_rgb, self.eff_rgb], 0)[None].expand(E, -1, -1)
+        # flat shading with the block's current yaw (faces with a zero normal carry their final colour already)
+        nl = self.block_nrm
+        nw = torch.stack([nl[:, 0] * cy - nl[:, 1] * sy, nl[:, 0] * sy + nl[:, 1] * cy, nl[:, 2].expand(E, -1)], -1)   # [E,Tb,3]
+        lit = LIGHT_AMBIENT + LIGHT_DIFFUSE * (nw * self.light).sum(-1).clamp_min(0.0)
+        shade = torch.where((nl.abs().sum(-1) > 0)[None], lit, torch.ones_like(lit))
+        brgb = self.block_rgb[None] * shade[..., None]
+        rgb = torch.cat([self.static_rgb[None].expand(E, -1, -1), brgb, self.eff_rgb[None].expand(E, -1, -1)], 1)
         tris = torch.cat([scr, rgb], -1).contiguous()
         ntris = torch.full((E,), tris.shape[1], dtype=torch.int32, device=tris.device)
         return tris, ntris

@@ -63,8 +63,15 @@ _launches = 0
 
 
 def launch_count() -> int:
-    """Number of native kernel-launching calls made through :func:`call` in this process."""
+    """Number of native kernel-launching calls made in this process: calls through :func:`call`, plus — for every replay
+    of a captured step — the native calls that were recorded into its CUDA graph (:func:`add_launches`)."""
     return _launches
+
+
+def add_launches(n: int) -> None:
+    """Account for ``n`` native launches that a CUDA-graph replay just issued on the caller's behalf."""
+    global _launches
+    _launches += int(n)
 
 
 def call(name: str, *args) -> None:

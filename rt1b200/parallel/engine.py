@@ -161,6 +161,14 @@ class DataParallelEngine:
         if self.device.type == "cuda" and _lib.available():
             _kernels.GRAD_READY = on_ready
 
+    def remove_ready_hooks(self):
+        """Drop the per-parameter gradient-ready hooks (the bucket-by-bucket overlap with backward).  A captured training
+        step does not use them, and a registered hook keeps the parameter's AccumulateGrad node — and the stream it was
+        created on — alive, which would tie a later capture to the default stream."""
+        for h in self._hook_handles:
+            h.remove()
+        self._hook_handles = []
+
     # --------------------------------------------------------------------------------------- stepping
     def zero_grad(self):
         self.flat.grad.zero_()

@@ -180,13 +180,22 @@ class GraphedTrainStep:
         self.seed_epoch = kernels.seed_epoch_tensor(dev)
         self.stream = torch.cuda.Stream(device=dev)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.native_launches = 0
         self._encoders = None
 
     def _body(self):
         tr = self.tr
         self.seed_epoch.add_(0x61C88647)                         # fresh dropout masks on every replay
         loss = tr.module.training_step(self.static, 0)
-        loss.backward()
+        # torch.autograd.grad, not loss.backward(): AccumulateGrad nodes (kept alive by the engine's hooks) remember the
+        # stream they were created on — the default stream — and synchronising with it would invalidate the capture.
+        # The kernel wrappers write most parameter gradients straight into the flat buffer and hand autograd `None`;
+        # the few that do flow through autograd (e.g. the position embedding) are added here.
+        params = tr.engine.flat.params
+        grads = torch.autograd.grad(loss, params, allow_unused=True)
+        dst = [p.grad for p, g in zip(params, grads) if g is not None]
+        if dst:
+            torch._foreach_add_(dst, [g for g in grads if g is not None])
         self.loss.copy_(loss.detach().float())
 
     def _fill(self, batch):
@@ -196,9 +205,20 @@ class GraphedTrainStep:
     def capture(self, batch):
         """Warm up once on the capture stream (lazy per-stream state: the weight-gradient lane, tensor-map caches, function
         attributes), then record."""
+        import gc
         tr = self.tr
         dev = tr.device
-        tr.module.model._device_rng = True
+        model = tr.module.model
+        model._device_rng = True
+        # Nothing may keep an autograd graph of an earlier (default-stream) step alive: its AccumulateGrad nodes would be
+        # re-used by the captured step and synchronise the capture stream with the default stream, which is illegal
+        # inside a capture.  Hooks, the stored loss and the stored aux tensors are such references.
+        tr.engine.remove_ready_hooks()
+        model._loss = None
+        model._aux_info = {}
+        if hasattr(model, "_attention_scores"):
+            model._attention_scores = None
+        gc.collect()
         main = torch.cuda.current_stream(dev)
         self._fill(batch)
         self.stream.wait_stream(main)
@@ -209,9 +229,13 @@ class GraphedTrainStep:
         main.wait_stream(self.stream)
         torch.cuda.synchronize(dev)
         self._undo_counters()
+        from ..ops import _lib
         self.graph = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
         with torch.cuda.graph(self.graph, stream=self.stream):
             self._body()
+        self.native_launches = _lib.launch_count() - n0          # native calls recorded into the graph (not executed yet)
+        _lib.add_launches(-self.native_launches)
         self._undo_counters()
 
     def _bn_encoders(self):
@@ -225,8 +249,10 @@ class GraphedTrainStep:
             m._nbt_pending = max(0, getattr(m, "_nbt_pending", 0) - 1)
 
     def run(self, batch) -> torch.Tensor:
+        from ..ops import _lib
         self._fill(batch)
         self.graph.replay()
+        _lib.add_launches(self.native_launches)
         for m in self._bn_encoders():                             # the Python-side step counter of the BatchNorm buffers
             m._nbt_pending = getattr(m, "_nbt_pending", 0) + 1
         return self.loss
@@ -333,6 +359,11 @@ class Trainer:
             g.capture(batch)
         except Exception as e:                         # keep training on the eager schedule rather than die in set-up
             self._graph_on = False
+            try:
+                if g.graph is not None:
+                    g.graph.reset()
+            except Exception:
+                pass
             self.module.model._device_rng = False
             torch.cuda.synchronize(self.device)
             self.engine.zero_grad()
