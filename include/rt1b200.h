@@ -68,7 +68,10 @@ int rt1_layernorm_bwd_noalloc(const void* x, const void* w, const void* dy, cons
 long long rt1_layernorm_bwd_noalloc_max_d(void);
 
 /* ---- fused masked attention over the RT-1 token window (reference transformer.py:82-109) ------------------
- * qkv [B,S,3,H,DK] bf16 -> out [B,S,H*DK]; mask uint8 [S,S] (0 = blocked) or NULL. */
+ * qkv [B,S,3,H,DK] bf16 -> out [B,S,H*DK]; mask uint8 [S,S] (0 = blocked) or NULL.
+ * S <= 128 with DK in {64, 128} (RT-1: S = 66, DK = 128) runs on tcgen05 tensor cores: one CTA per (batch, head), TMA-loaded
+ * Q/K/V/dO tiles, scores and all five backward contractions accumulated in TMEM, softmax/mask/dropout thread-local on TMEM
+ * lanes (csrc/attention_tc.cu).  Other shapes (DK % 8 == 0, DK <= 256, S <= 160) use the generic CUDA-core kernels. */
 int rt1_attention_fwd(const void* qkv, const unsigned char* mask, void* out, int B, int S, int H, int DK, float p_drop,
                       unsigned seed, cudaStream_t stream);
 int rt1_attention_bwd(const void* qkv, const unsigned char* mask, const void* dout, void* dqkv, int B, int S, int H,
@@ -170,6 +173,15 @@ int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in, const f
 /* stem 3x3 stride 2 on the [N,H,W,8] frames produced by rt1_preprocess_nhwc (channels 0..2 used): */
 /* im2col of the stem window: cols bf16 [N*Ho*Wo, 32], column ci*9+ky*3+kx (27 used) — the stem then runs as rt1_gemm_bf16 */
 int rt1_stem_im2col(const void* x, void* cols, int N, int H, int W, cudaStream_t stream);
+
+/* ---- action (de)tokenisation (reference tokenizers/action_tokenizer.py:105-159) -------------------------------------------
+ * vals fp32 [R, A] (one column per token; discrete values as floats) <-> tokens int64 [R, A]; low/high fp32 [A] (for a
+ * discrete token high = n), discrete uint8 [A].  Box: clamp, affine to [0, vocab-1], int32 truncation; Discrete: identity,
+ * and on the way back `token > n ? 0 : token`. */
+int rt1_action_tokenize(const float* vals, const float* low, const float* high, const unsigned char* discrete, long long* tokens,
+                        long long R, int A, int vocab, cudaStream_t stream);
+int rt1_action_detokenize(const long long* tokens, const float* low, const float* high, const unsigned char* discrete, float* vals,
+                          long long R, int A, int vocab, cudaStream_t stream);
 
 /* ---- synthetic Language-Table frames (replaces the TinyRenderer call of reference language_table.py:579-597 and the
  *      crop + resize of eval/wrappers.py:88-96; oracle = the numpy restatement in rt1b200/envs/raster.py) ----------------

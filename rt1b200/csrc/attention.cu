@@ -1,5 +1,6 @@
 // Fused masked attention over the RT-1 token window (replaces 2 bmm + masked_fill + softmax +
-// dropout of K12).
+// dropout of K12) — GENERIC-SHAPE kernels on CUDA cores.  RT-1's own shapes (S <= 128, dk 64/128) are dispatched to the
+// tcgen05 kernels in attention_tc.cu; these serve every other head size / window (and RT1B200_ATTN_TC=0 for A/B runs).
 //
 // The whole problem of one (batch, head) — S = 66 tokens, dk = 128 — fits in one CTA's shared memory, so the
 // scores never touch HBM (the reference materialises [b, h, S, S] three times per layer).  Input is the fused
@@ -195,8 +196,16 @@ static size_t attn_smem(int S, int DK, bool bwd) {
   return bwd ? 4 * tile + 2 * pm : 3 * tile + pm;
 }
 
+// tensor-core path (attention_tc.cu): S <= 128, dk in {64, 128}
+bool rt1_attention_tc_supported(int S, int DK, const void* a, const void* b);
+int rt1_attention_tc_fwd(const void* qkv, const unsigned char* mask, void* out, int B, int S, int H, int DK, float p_drop,
+                         unsigned seed, cudaStream_t stream);
+int rt1_attention_tc_bwd(const void* qkv, const unsigned char* mask, const void* dout, void* dqkv, int B, int S, int H, int DK,
+                         float p_drop, unsigned seed, cudaStream_t stream);
+
 RT1_API int rt1_attention_fwd(const void* qkv, const unsigned char* mask, void* out, int B, int S, int H, int DK, float p_drop,
                               unsigned seed, cudaStream_t stream) {
+  if (rt1_attention_tc_supported(S, DK, qkv, out)) return rt1_attention_tc_fwd(qkv, mask, out, B, S, H, DK, p_drop, seed, stream);
   RT1_REQUIRE(DK % 8 == 0 && DK <= 256 && S <= 160, "rt1_attention_fwd: unsupported S=%d dk=%d", S, DK);
   const size_t smem = attn_smem(S, DK, false);
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_attention_fwd: S=%d dk=%d needs %zu B of shared memory", S, DK, smem);
@@ -208,6 +217,8 @@ RT1_API int rt1_attention_fwd(const void* qkv, const unsigned char* mask, void* 
 
 RT1_API int rt1_attention_bwd(const void* qkv, const unsigned char* mask, const void* dout, void* dqkv, int B, int S, int H,
                               int DK, float p_drop, unsigned seed, cudaStream_t stream) {
+  if (rt1_attention_tc_supported(S, DK, qkv, dout) && ((uintptr_t)dqkv & 15) == 0)
+    return rt1_attention_tc_bwd(qkv, mask, dout, dqkv, B, S, H, DK, p_drop, seed, stream);
   RT1_REQUIRE(DK % 8 == 0 && DK <= 256 && S <= 160, "rt1_attention_bwd: unsupported S=%d dk=%d", S, DK);
   const size_t smem = attn_smem(S, DK, true);
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_attention_bwd: S=%d dk=%d needs %zu B of shared memory", S, DK, smem);

@@ -97,7 +97,69 @@ class RT1ActionTokenizer:
                                       torch.as_tensor(np.asarray(sp.high), dtype=torch.float32, device=device))
         return self._bounds_cache[ck]
 
+    # ---- sm_100a path: one kernel for the whole clamp / affine / truncate chain (csrc/action_tokens.cu) ----------------
+    def _tables(self, device):
+        """Per-token (low, high-or-n, is_discrete) tables on ``device`` (built once per device)."""
+        ck = ("tables", str(device))
+        if ck not in self._bounds_cache:
+            low, high, disc = [], [], []
+            for k in self._action_order:
+                sp = self._action_space[k]
+                if _is_discrete(sp):
+                    low.append(0.0); high.append(float(sp.n)); disc.append(1)
+                else:
+                    lo = np.broadcast_to(np.asarray(sp.low, np.float32), sp.shape).reshape(-1)
+                    hi = np.broadcast_to(np.asarray(sp.high, np.float32), sp.shape).reshape(-1)
+                    low += lo.tolist(); high += hi.tolist(); disc += [0] * sp.shape[0]
+            self._bounds_cache[ck] = (torch.tensor(low, dtype=torch.float32, device=device),
+                                      torch.tensor(high, dtype=torch.float32, device=device),
+                                      torch.tensor(disc, dtype=torch.uint8, device=device))
+        return self._bounds_cache[ck]
+
+    @staticmethod
+    def _native(t: torch.Tensor) -> bool:
+        from ..ops import _lib
+        return t.is_cuda and _lib.available()
+
+    def _tokenize_native(self, action: Dict[str, torch.Tensor]) -> torch.Tensor:
+        from ..ops._lib import call, i32, i64, ptr, stream
+        parts = []
+        for k in self._action_order:
+            a = action[k].to(torch.float32)
+            parts.append(a.unsqueeze(-1) if _is_discrete(self._action_space[k]) else a)
+        vals = torch.cat(parts, dim=-1).contiguous()
+        low, high, disc = self._tables(vals.device)
+        out = torch.empty(vals.shape, dtype=torch.int64, device=vals.device)
+        A = vals.shape[-1]
+        call("rt1_action_tokenize", ptr(vals), ptr(low), ptr(high), ptr(disc), ptr(out), i64(vals.numel() // A), i32(A),
+             i32(self._vocab_size), stream())
+        return out
+
+    def _detokenize_native(self, action_tokens: torch.Tensor) -> Dict[str, torch.Tensor]:
+        from ..ops._lib import call, i32, i64, ptr, stream
+        tok = action_tokens.to(torch.int64).contiguous()
+        low, high, disc = self._tables(tok.device)
+        A = tok.shape[-1]
+        vals = torch.empty(tok.shape, dtype=torch.float32, device=tok.device)
+        call("rt1_action_detokenize", ptr(tok), ptr(low), ptr(high), ptr(disc), ptr(vals), i64(tok.numel() // A), i32(A),
+             i32(self._vocab_size), stream())
+        out: Dict[str, torch.Tensor] = {}
+        i = 0
+        for k in self._action_order:
+            sp = self._action_space[k]
+            if _is_discrete(sp):
+                out[k] = vals[..., i].to(torch.int64)
+                i += 1
+            else:
+                n = sp.shape[0]
+                out[k] = vals[..., i:i + n]
+                i += n
+        return out
+
     def tokenize(self, action: Dict[str, torch.Tensor]) -> torch.Tensor:
+        first = action[self._action_order[0]]
+        if self._native(first) and first.numel() > 0:
+            return self._tokenize_native(action)
         parts = []
         for k in self._action_order:
             a = action[k]
@@ -112,6 +174,8 @@ class RT1ActionTokenizer:
         return torch.cat(parts, dim=-1)
 
     def detokenize(self, action_tokens: torch.Tensor) -> Dict[str, torch.Tensor]:
+        if self._native(action_tokens) and action_tokens.numel() > 0 and action_tokens.shape[-1] == self._tokens_per_action:
+            return self._detokenize_native(action_tokens)
         out: Dict[str, torch.Tensor] = {}
         i = 0
         for k in self._action_order:

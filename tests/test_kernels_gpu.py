@@ -172,6 +172,29 @@ def test_attention_is_causal_and_blocks_action_keys():
     assert torch.equal(out[:, :40], out2[:, :40])
 
 
+def test_action_tokenizer_kernel_matches_torch_path():
+    """rt1_action_tokenize / rt1_action_detokenize (CUDA) against the PyTorch statement of the same rules on the CPU."""
+    import collections
+    from rt1b200 import spaces
+    from rt1b200.models.tokenizers import RT1ActionTokenizer
+    space = spaces.Dict(collections.OrderedDict(terminate_episode=spaces.Discrete(2),
+                                                action=spaces.Box(low=-0.1, high=0.1, shape=(2,), dtype="float32"),
+                                                gripper=spaces.Box(low=0.0, high=1.0, shape=(1,), dtype="float32")))
+    tk = RT1ActionTokenizer(space, vocab_size=256)
+    g = torch.Generator().manual_seed(3)
+    act = {"terminate_episode": torch.randint(0, 2, (8, 6), generator=g),
+           "action": (torch.rand(8, 6, 2, generator=g) - 0.5) * 0.3,          # some values outside the box: clamped
+           "gripper": torch.rand(8, 6, 1, generator=g) * 1.2 - 0.1}
+    want = tk.tokenize(act)                                                   # CPU tensors: PyTorch path
+    got = tk.tokenize({k: v.to(DEV) for k, v in act.items()})
+    assert got.dtype == torch.int64 and torch.equal(got.cpu(), want)
+    toks = torch.randint(0, 256, (8, 6, 4), generator=g)
+    toks[..., 0] = torch.randint(0, 4, (8, 6), generator=g)                   # includes out-of-vocabulary discrete tokens
+    back_c, back_g = tk.detokenize(toks), tk.detokenize(toks.to(DEV))
+    for k in back_c:
+        torch.testing.assert_close(back_g[k].cpu().to(back_c[k].dtype), back_c[k], rtol=1e-6, atol=1e-7)
+
+
 def test_action_ce_loss_fwd_bwd():
     R, A, V = 48, 3, 256
     logits = (_bf(R, A, V, seed=9) * 3).detach().requires_grad_()
