@@ -20,6 +20,8 @@ import torch
 from language_table.environments import blocks as blocks_module
 from language_table.environments import constants
 from language_table.environments.rewards import task_info
+from language_table.environments.utils import xarm_sim_robot
+from language_table.environments.utils.pose3d import Pose3d
 
 from rt1b200 import spaces
 from rt1b200.envs.board import BatchedLanguageTable
@@ -29,14 +31,20 @@ class LanguageTable:
     metadata = {"render.modes": ["rgb_array"]}
 
     def __init__(self, block_mode, reward_factory=None, control_frequency=10.0, shared_memory=False, seed=None,
-                 delay_reward_steps=0, render_text_in_image=True, training=True, device="cpu"):
+                 delay_reward_steps=0, render_text_in_image=True, training=True, device="cpu", arm_kinematics=True):
         if shared_memory:
             raise NotImplementedError("the PyBullet GUI / shared-memory visualiser is unavailable on this box")
         self._block_mode = blocks_module.LanguageTableBlockVariants(block_mode) if isinstance(block_mode, str) else block_mode
         self._training = training
         self._rng = np.random.RandomState(seed=seed)
         self._control_frequency = control_frequency
+        self._step_frequency = constants.STEP_FREQUENCY
+        self._sim_steps_per_step = int(self._step_frequency / self._control_frequency)     # 24, reference :114-124
         self._render_text_in_image = render_text_in_image
+        # the xArm6 that carries the cylinder: IK to the commanded pose, joint servo over the simulation sub-steps, so the
+        # effector lags its target within a control step like the motor-driven arm of the reference (:599-646)
+        self._robot = xarm_sim_robot.XArmSimRobot(initial_joint_positions=constants.INITIAL_JOINT_POSITIONS,
+                                                  end_effector="cylinder_real", color="white") if arm_kinematics else None
         self._board = BatchedLanguageTable(1, self._block_mode if self._block_mode in (
             blocks_module.LanguageTableBlockVariants.BLOCK_1, blocks_module.LanguageTableBlockVariants.BLOCK_4,
             blocks_module.LanguageTableBlockVariants.BLOCK_8, blocks_module.LanguageTableBlockVariants.N_CHOOSE_K)
@@ -140,6 +148,9 @@ class LanguageTable:
                     # absent blocks are parked far off the board
                     self._board.block_xy[0][~self._board.block_mask[0]] = torch.tensor([5.0, 5.0])
                 self._blocks_on_table = [n for n, m in zip(self._all_blocks, self._board.block_mask[0].tolist()) if m]
+            if reset_poses and self._robot is not None:
+                self._robot.reset_joints(constants.INITIAL_JOINT_POSITIONS)
+                self._robot.reset_joints(self._robot.inverse_kinematics(self._effector_pose(self._board.effector[0])))
             state = self._compute_state()
             if self._reward_calculator is None:
                 self._set_instruction("")
@@ -157,9 +168,35 @@ class LanguageTable:
         self._instruction_str = text
         self._instruction = self.encode_instruction(text)
 
+    @staticmethod
+    def _effector_pose(xy) -> Pose3d:
+        xy = np.asarray(xy.cpu() if hasattr(xy, "cpu") else xy, np.float64)
+        return Pose3d(rotation=constants.EFFECTOR_DOWN_ROTATION, translation=np.array([xy[0], xy[1], constants.EFFECTOR_HEIGHT]))
+
+    @property
+    def robot(self):
+        return self._robot
+
+    def _step_robot_and_sim(self, action) -> Optional[torch.Tensor]:
+        """Command the arm to the new (workspace-clipped) target and run the control step's simulation sub-steps; returns the
+        effector positions the board should sweep through, or ``None`` without an arm model."""
+        if self._robot is None:
+            return None
+        lo, hi = constants.WORKSPACE_BOUNDS
+        target = np.clip(self._board.effector_target[0].cpu().numpy().astype(np.float64) + np.asarray(action, np.float64), lo, hi)
+        self._robot.set_target_effector_pose(self._effector_pose(target))
+        n_wp = 4                                                # board contact resolution happens at 4 instants per step
+        per = max(1, self._sim_steps_per_step // n_wp)
+        path = []
+        for _ in range(n_wp):
+            self._robot.step_simulation(per, dt=1.0 / self._step_frequency)
+            path.append(self._robot.forward_kinematics().translation[:2])
+        return torch.as_tensor(np.asarray(path, np.float32))[None]
+
     def step(self, action):
+        path = self._step_robot_and_sim(np.asarray(action, np.float32).reshape(2))
         action = torch.as_tensor(np.asarray(action, np.float32)).reshape(1, 2)
-        self._board.step(action)
+        self._board.step(action, effector_path=path)
         state = self._compute_state()
         reward, done = (0.0, False)
         if self._reward_calculator is not None:

@@ -5,8 +5,9 @@
 Same entry point as the reference (``language_table/eval/main_rt1.py``: ``--workdir``, BLOCK_8 + block-to-block reward,
 seed 0, episodes of at most 80 steps, actions clipped to ±0.03, success counted per episode, result dict printed).
 Differences: the checkpoint path is a flag (upstream hard-codes it, ``:220``); ``--num_envs N > 1`` runs N boards on the
-GPU against one batched policy call per step (upstream: one board, batch 1); frames are written as PNG strips /
-``.npy`` under ``--workdir`` (imageio/mp4 is not installed).  Without ``--ckpt`` a randomly initialised policy is used,
+GPU against one batched policy call per step (upstream: one board, batch 1); every episode is written under ``--workdir``
+as an animated PNG (``--video_format gif`` for GIF; upstream writes mp4 through imageio/ffmpeg, ``:196-199``, which are
+not installed — the writers in ``rt1b200/utils/video.py`` need no codec).  Without ``--ckpt`` a randomly initialised policy is used,
 which exercises the full loop (no trained checkpoint can be downloaded here).
 """
 from __future__ import annotations
@@ -34,7 +35,8 @@ def get_ckpt_model(ckpt, device, dtype=None, height=256, width=456, seq_len=6):
 
 
 def evaluate_checkpoint(workdir, ckpt=None, num_envs=1, episodes=10, max_episode_steps=80, device=None, seed=0,
-                        height=256, width=456, seq_len=6, use_oracle=False):
+                        height=256, width=456, seq_len=6, use_oracle=False, video_format="png"):
+    from rt1b200.utils.video import write_video
     device = device or ("cuda" if torch.cuda.is_available() else "cpu")
     dtype = torch.bfloat16 if device.startswith("cuda") else None
     module = get_ckpt_model(ckpt, device, dtype, height, width, seq_len)
@@ -48,7 +50,7 @@ def evaluate_checkpoint(workdir, ckpt=None, num_envs=1, episodes=10, max_episode
                               seed=seed, image_hw=(height, width), record_frames=True, use_oracle=use_oracle)
         frames = res.pop("frames")
         if frames:
-            np.save(os.path.join(workdir, "blocktoblock_env0_frames.npy"), np.stack(frames))
+            write_video(os.path.join(workdir, f"blocktoblock_env0.{video_format}"), np.stack(frames), fps=10.0)
         results["blocktoblock"] = res
     else:
         # reference-shaped single-environment loop through the wrapper stack and the policy adapter
@@ -79,7 +81,7 @@ def evaluate_checkpoint(workdir, ckpt=None, num_envs=1, episodes=10, max_episode
                 if done:
                     break
             successes += int(base.succeeded)
-            np.save(os.path.join(workdir, f"blocktoblock_{ep}.npy"), np.stack(frames))
+            write_video(os.path.join(workdir, f"blocktoblock_{ep}.{video_format}"), np.stack(frames), fps=10.0)
         results["blocktoblock"] = {"episodes": episodes, "successes": successes, "success_rate": successes / max(1, episodes)}
     print(json.dumps(results))
     with open(os.path.join(workdir, "results.json"), "w") as f:
@@ -100,9 +102,10 @@ def main(argv=None):
     p.add_argument("--width", type=int, default=456)
     p.add_argument("--seq_len", type=int, default=6)
     p.add_argument("--oracle", action="store_true", help="drive the boards with the scripted oracle instead of the policy")
+    p.add_argument("--video_format", choices=["png", "gif"], default="png", help="episode videos: animated PNG (lossless) or GIF")
     a = p.parse_args(argv)
     return evaluate_checkpoint(a.workdir, a.ckpt, a.num_envs, a.episodes, a.max_episode_steps, a.device, a.seed, a.height, a.width,
-                               a.seq_len, a.oracle)
+                               a.seq_len, a.oracle, a.video_format)
 
 
 if __name__ == "__main__":

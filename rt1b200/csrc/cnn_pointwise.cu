@@ -406,22 +406,38 @@ __global__ void __launch_bounds__(CNN_THREADS) se_bn_bwd_reduce_kernel(const bf1
     load8f(mean + m.cv * 8, mu);
     load8f(rstd + m.cv * 8, rs);
     const size_t off = ((size_t)n * HW) * C + (size_t)m.cv * 8;
-    for (int r = rb + m.r0; r < re; r += m.rows_per_pass) {
-      float gg[8], f[8];
-      load8bf(g + off + (size_t)r * C, gg);
-      load8bf(x + off + (size_t)r * C, f);
+    // four rows per trip: eight 16-byte loads are in flight before the first one is consumed (one row per trip left the
+    // kernel latency-bound at 22 % of the copy bandwidth)
+    constexpr int RU = 4;
+    for (int r = rb + m.r0; r < re; r += RU * m.rows_per_pass) {
+      bf16x8 rawg[RU], rawx[RU];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float u = fmaf(fa[k], f[k], fb[k]);
-        const float sg = sigmoid_f(u);
-        const float d1 = sg * (1.f + u * (1.f - sg));      // SiLU'(u)
-        const float xh = (f[k] - mu[k]) * rs[k];
-        const float gd = gg[k] * d1;
-        ds[k] = fmaf(gg[k] * u, sg, ds[k]);
-        a1[k] += gd;
-        a2[k] += d1;
-        a3[k] = fmaf(gd, xh, a3[k]);
-        a4[k] = fmaf(d1, xh, a4[k]);
+      for (int q = 0; q < RU; ++q) {
+        const int rq = r + q * m.rows_per_pass;
+        if (rq < re) {
+          rawg[q] = *reinterpret_cast<const bf16x8*>(g + off + (size_t)rq * C);
+          rawx[q] = *reinterpret_cast<const bf16x8*>(x + off + (size_t)rq * C);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < RU; ++q) {
+        if (r + q * m.rows_per_pass >= re) continue;
+        float gg[8], f[8];
+        unpack8(rawg[q], gg);
+        unpack8(rawx[q], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float u = fmaf(fa[k], f[k], fb[k]);
+          const float sg = sigmoid_f(u);
+          const float d1 = sg * (1.f + u * (1.f - sg));      // SiLU'(u)
+          const float xh = (f[k] - mu[k]) * rs[k];
+          const float gd = gg[k] * d1;
+          ds[k] = fmaf(gg[k] * u, sg, ds[k]);
+          a1[k] += gd;
+          a2[k] += d1;
+          a3[k] = fmaf(gd, xh, a3[k]);
+          a4[k] = fmaf(d1, xh, a4[k]);
+        }
       }
     }
   }

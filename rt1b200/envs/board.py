@@ -105,15 +105,20 @@ class BatchedLanguageTable:
         idx = torch.arange(self.E, device=self.device)
         return (self.block_xy[idx, self.start_block] - self.block_xy[idx, self.target_block]).norm(dim=-1)
 
-    def step(self, action: torch.Tensor):
-        """``action`` [E,2] metres (Δx, Δy) added to the effector target. Returns (reward [E], done [E])."""
+    def step(self, action: torch.Tensor, effector_path: Optional[torch.Tensor] = None):
+        """``action`` [E,2] metres (Δx, Δy) added to the effector target. Returns (reward [E], done [E]).
+        ``effector_path`` [E, n, 2] (optional): where the effector actually is at n instants of this control step — an arm
+        model that lags its target supplies it (``LanguageTable`` with ``arm_kinematics``); without it the effector
+        reaches the target by linear interpolation."""
         action = action.to(self.device, torch.float32)
         lo = torch.tensor([C.X_MIN, C.Y_MIN], device=self.device)
         hi = torch.tensor([C.X_MAX, C.Y_MAX], device=self.device)
         self.effector_target = torch.minimum(torch.maximum(self.effector_target + action, lo), hi)
-        delta = (self.effector_target - self.effector) / SUBSTEPS
-        for _ in range(SUBSTEPS):
-            self.effector = self.effector + delta
+        if effector_path is None:
+            frac = torch.arange(1, SUBSTEPS + 1, device=self.device, dtype=torch.float32)[None, :, None] / SUBSTEPS
+            effector_path = self.effector[:, None] + (self.effector_target - self.effector)[:, None] * frac
+        for k in range(effector_path.shape[1]):
+            self.effector = effector_path[:, k].to(self.device, torch.float32)
             self.block_xy = resolve_contacts(self.effector, self.block_xy, self.block_mask, iters=2)
         self.steps += 1
         success = self.task_distance() < TARGET_BLOCK_DISTANCE

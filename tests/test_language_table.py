@@ -76,6 +76,52 @@ def test_oracle_solves_every_pushing_family(factory):
     assert done and reward == 100.0
 
 
+def test_oracle_end_effector_planner_and_potential_fallback():
+    """Reference push_oracle_rrt_slowdown.py:467-600: the effector's free-space route is planned around ALL blocks; when no
+    route exists (effector boxed in by blocks) the potential field takes over and planning is retried."""
+    O = push_oracle_rrt_slowdown
+    env = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8, block2block.BlockToBlockReward, seed=4,
+                                       render_text_in_image=False)
+    env.reset()
+    b = env._board
+    names = b.block_names
+    start, target = names.index(env._task_info.block1), names.index(env._task_info.block2)
+    # a wall of blocks between the effector and the pushed block: the direct line is blocked
+    b.block_xy[0, start] = torch.tensor([0.45, 0.0])
+    b.block_xy[0, target] = torch.tensor([0.45, 0.2])
+    others = [i for i in range(len(names)) if i not in (start, target)]
+    for k, i in enumerate(others):
+        b.block_xy[0, i] = torch.tensor([0.33, -0.10 + 0.045 * k])
+    b.effector[0] = b.effector_target[0] = torch.tensor([0.22, 0.0])
+    oracle = O.ObstacleOrientedPushOracleBoard2dRRT(env, use_ee_planner=True, rng=np.random.RandomState(0))
+    assert oracle.get_plan(env._compute_state()) and oracle.plan_success
+    wall = b.block_xy[0, others].clone()
+    done = False
+    for _ in range(250):
+        b.step(torch.as_tensor(oracle.action(env._compute_state())).reshape(1, 2))
+        _, done = env._reward_calculator.reward(env._compute_state())
+        if done:
+            break
+    assert done and not oracle.used_potential_fallback
+    assert float((b.block_xy[0, others] - wall).norm(dim=-1).max()) < 0.02          # went around the wall, not through it
+    # boxed in: four blocks hugging the effector leave RRT* no collision-free first step → potential-field fallback
+    env.reset()
+    b.effector[0] = b.effector_target[0] = torch.tensor([0.3, 0.0])
+    ring = [(0.018, 0.0), (-0.018, 0.0), (0.0, 0.018), (0.0, -0.018)]
+    free = [i for i in range(len(names)) if i not in (names.index(env._task_info.block1), names.index(env._task_info.block2))]
+    for (dx, dy), i in zip(ring, free):
+        b.block_xy[0, i] = torch.tensor([0.3 + dx, 0.0 + dy])
+    oracle = O.ObstacleOrientedPushOracleBoard2dRRT(env, use_ee_planner=True, rng=np.random.RandomState(0))
+    act = oracle.action(env._compute_state())
+    assert oracle.used_potential_fallback and np.isfinite(act).all() and np.linalg.norm(act) <= 0.03 + 1e-6
+    # helpers
+    pts = O.filter_subgoals([np.array([0.0, 0.0]), np.array([0.005, 0]), np.array([0.03, 0]), np.array([0.032, 0]), np.array([0.06, 0])], 0.025)
+    assert [round(float(p[0]), 3) for p in pts] == [0.0, 0.03, 0.06]
+    assert O.slowdown_factor(0.01) == 0.2 and O.slowdown_factor(0.07) == 0.5 and O.slowdown_factor(0.5) == 1.0
+    assert np.allclose(O.repulsive_push(np.array([0.0, 0.0]), np.array([0.1, 0.0])), 0)
+    assert O.repulsive_push(np.array([0.0, 0.0]), np.array([0.04, 0.0]))[0] < 0 < O.attractive_pull(np.zeros(2), np.array([0.1, 0.0]))[0]
+
+
 def test_point_separate_and_play_rewards():
     env = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8, point2block.PointToBlockReward, seed=2)
     env.reset()
@@ -108,16 +154,87 @@ def test_rrt_star_routes_around_an_obstacle():
 
 
 def test_robot_and_state_utils(tmp_path):
-    robot = xarm_sim_robot.XArmSimRobot()
+    """xArm6 kinematics restated without PyBullet: the figures of the reference's xarm_sim_robot_test.py:50-78."""
+    import math
     from scipy.spatial import transform
-    pose = pose3d.Pose3d(rotation=transform.Rotation.from_rotvec([0, np.pi, 0]), translation=np.array([0.3, 0.1, 0.145]))
+    from language_table.environments import constants
+    robot = xarm_sim_robot.XArmSimRobot()
+    robot.reset_joints([0, math.pi / 2, math.pi, 0, 0, 0])                  # pointing down the x axis
+    x, y, _ = robot.forward_kinematics().translation
+    assert abs(x - 0.714479) < 1e-3 and abs(y + 0.0006) < 1e-3
+    robot.reset_joints([math.pi / 2, math.pi / 2, math.pi, 0, 0, 0])        # pointing down the y axis
+    x, y, _ = robot.forward_kinematics().translation
+    assert abs(x - 0.0006) < 1e-3 and abs(y - 0.714479) < 1e-3
+    # inverse kinematics round trip (reference :64-78)
+    robot = xarm_sim_robot.XArmSimRobot()
+    initial = robot.forward_kinematics()
+    target = pose3d.Pose3d(rotation=transform.Rotation.from_rotvec([0, math.pi / 2, 0]), translation=np.array([0.5, 0.0, 0.10]))
+    robot.reset_joints(robot.inverse_kinematics(target))
+    got = robot.forward_kinematics()
+    assert not np.all(initial.vec7 == got.vec7)
+    np.testing.assert_almost_equal(got.vec7, target.vec7, decimal=2)
+    # the environment's initial joints are the tool-down pose at (0.3, -0.2, 0.145) that constants.py documents
+    robot = xarm_sim_robot.XArmSimRobot(initial_joint_positions=constants.INITIAL_JOINT_POSITIONS)
+    p0 = robot.forward_kinematics(link_frame=True)
+    np.testing.assert_allclose(p0.translation, [0.3, -0.2, 0.145], atol=2e-3)
+    np.testing.assert_allclose(np.abs(p0.rotation.as_rotvec()), [0, math.pi, 0], atol=2e-2)
+    # position control: the joints servo towards the IK solution, so the effector lags its target, then converges
+    pose = pose3d.Pose3d(rotation=constants.EFFECTOR_DOWN_ROTATION, translation=np.array([0.34, -0.17, constants.EFFECTOR_HEIGHT]))
     robot.set_target_effector_pose(pose)
-    assert robot.forward_kinematics() == pose                       # IK → FK round trip
+    start = robot.forward_kinematics().translation.copy()
+    robot.step_simulation(3)
+    mid = robot.forward_kinematics().translation
+    assert 1e-4 < np.linalg.norm(mid - start) < np.linalg.norm(pose.translation - start) - 1e-3
+    robot.step_simulation(60)
+    np.testing.assert_allclose(robot.forward_kinematics().translation, pose.translation, atol=5e-4)
     assert pose3d.Pose3d.deserialize(pose.serialize()) == pose
     st = utils_pybullet.XarmState(obj_id=1, base_pose=((0, 0, 0), (0, 0, 0, 1)), target_effector_pose=pose, goal_translation=np.zeros(3))
     path = str(tmp_path / "state.json.gz")
     utils_pybullet.write_state_file(path, [st.serialize()])
     assert utils_pybullet.read_state_file(path)[0]["obj_id"] == 1
+
+
+def test_camera_matrices_and_view_rays():
+    """View / projection matrices (reference language_table.py:365-397) and the ray helpers of utils_pybullet.py:115-196."""
+    import torch
+    from language_table.environments import constants as C
+    from rt1b200.envs import camera
+    from rt1b200.envs.scene import SceneBuilder
+    viewm, projm, pos, lookat, up = camera.calc_camera_params((C.IMAGE_HEIGHT, C.IMAGE_WIDTH), C.CAMERA_POSE, C.CAMERA_ORIENTATION,
+                                                              C.CAMERA_INTRINSICS)
+    assert len(viewm) == 16 and len(projm) == 16
+    pts = np.array([[0.3, 0.1, 0.0], [0.5, -0.2, 0.02], [0.2, 0.0, 0.04]])
+    px = camera.project_points(pts, viewm, projm, C.IMAGE_WIDTH, C.IMAGE_HEIGHT)
+    # the OpenGL matrices and the scene's pinhole projection are the same camera
+    sb = SceneBuilder(["red_moon"], use_assets=False)
+    np.testing.assert_allclose(px, sb.project(torch.tensor(pts, dtype=torch.float32))[:, :2].numpy(), atol=2e-3)
+    # pixel → view ray → world ray → board plane recovers a point on the board
+    hit = utils_pybullet.pixel_to_workspace(px[0], viewm, projm, C.IMAGE_WIDTH, C.IMAGE_HEIGHT)
+    np.testing.assert_allclose(hit, pts[0], atol=1e-6)
+    xyz, quat = utils_pybullet.decompose_view_matrix(viewm)
+    np.testing.assert_allclose(xyz, C.CAMERA_POSE, atol=1e-9)
+    assert abs(np.linalg.norm(quat) - 1) < 1e-9
+    # an object at the look-at point sits on the camera's -z axis, one unit away
+    v_xyz, _ = utils_pybullet.world_obj_to_view(lookat, [0, 0, 0, 1], viewm)
+    np.testing.assert_allclose(v_xyz, [0, 0, -1], atol=1e-6)
+    assert utils_pybullet.ray_to_plane_test([0, 0, 1], [1, 0, 0], [0, 0, 0], [0, 0, 1]) is None        # parallel
+    assert utils_pybullet.ray_to_plane_test([0, 0, 1], [0, 0, 1], [0, 0, 0], [0, 0, 1]) is None        # behind the origin
+    np.testing.assert_allclose(utils_pybullet.ray_to_plane_test([0, 0, 1], [0, 0, -1], [0, 0, 0], [0, 0, 1]), [0, 0, 0])
+
+
+def test_env_effector_lags_target_within_a_control_step():
+    env = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_4, block2block.BlockToBlockReward, seed=3)
+    obs = env.reset()
+    np.testing.assert_allclose(obs["effector_translation"], obs["effector_target_translation"], atol=1e-4)
+    np.testing.assert_allclose(env.robot.forward_kinematics().translation[:2], obs["effector_translation"], atol=1e-4)
+    obs, _, _, _ = env.step(np.array([0.03, -0.02], np.float32))
+    lag = np.linalg.norm(obs["effector_target_translation"] - obs["effector_translation"])
+    assert 1e-6 < lag < 5e-3                                            # behind the commanded target, but nearly there
+    no_arm = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_4, block2block.BlockToBlockReward, seed=3,
+                                          arm_kinematics=False)
+    o2 = no_arm.reset()
+    o2, _, _, _ = no_arm.step(np.array([0.03, -0.02], np.float32))
+    np.testing.assert_allclose(o2["effector_translation"], o2["effector_target_translation"], atol=1e-7)
 
 
 def test_wrappers_policy_and_entry_point(tmp_path):
