@@ -278,7 +278,16 @@ def run_reference(args):
     torch.manual_seed(0)
     import distribute_train as ref_train               # baseline/_ref/distribute_train.py (unmodified)
     targs = Namespace(height=HEIGHT, width=WIDTH, seq_len=SEQ_LEN, lr=5e-4, milestones=[50, 75, 90])
-    module = ref_train.RT1_Lightning(targs).to(dev)
+    module = ref_train.RT1_Lightning(targs)
+    if args.model == "scaled":
+        # BASELINE config 3 (24 layers, d_model 1024): the reference hard-codes its hyper-parameters inside RT1_Lightning
+        # (distribute_train.py:42-55), so the scaled variant is built through the reference's own TransformerNetwork
+        # constructor with the two changed arguments and swapped into the unmodified Lightning module
+        from pytorch_robotics_transformer.transformer_network import TransformerNetwork as RefNet
+        module.model = RefNet(input_tensor_space=module.state_space, output_tensor_space=module.action_space, vocab_size=256,
+                              token_embedding_size=512, num_layers=24, layer_size=128, num_heads=8, feed_forward_size=1024,
+                              dropout_rate=0.1, time_sequence_length=SEQ_LEN, crop_size=236, use_token_learner=True)
+    module = module.to(dev)
     module.train()
     # what Lightning's DDPStrategy(find_unused_parameters=True) + configure_optimizers() set up
     opt = torch.optim.Adam(module.parameters(), lr=targs.lr)
@@ -369,7 +378,9 @@ def run_reference(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16-autocast" if bf16 else "fp32",
             "data": "synthetic", "impl": "reference",
-            "config": {"model": "reference RT1_Lightning (unmodified, baseline/_ref)", "global_batch": B * world,
+            "config": {"model": "reference RT1_Lightning (unmodified, baseline/_ref)"
+                       + (" with TransformerNetwork(num_layers=24, feed_forward_size=1024)" if args.model == "scaled" else ""),
+                       "global_batch": B * world,
                        "per_gpu_batch": B, "seq_len": SEQ_LEN, "frames": f"{HEIGHT}x{WIDTH}",
                        "parallelism": f"dp{world}" + (" torch DDP(find_unused_parameters=True) over NCCL" if world > 1 else ""),
                        "optimizer": "torch.optim.Adam(lr 5e-4)",

@@ -84,28 +84,73 @@ def write_synthetic_dataset(root: str, n_train: int = 8, n_val: int = 2, n_test:
     return root
 
 
-def convert_rlds(episodes: Iterable[Iterable[Dict]], out_root: str, embed: Callable[[str], np.ndarray],
-                 splits=(("train", 7800), ("val", 100), ("test", 100)), decode=None) -> None:
-    """RLDS → npy conversion (reference ``rlds_np_convert.py``: first 8 000 episodes split 7 800/100/100, the
-    byte-encoded instruction replaced by its sentence embedding).  ``episodes`` yields episodes of RLDS step
-    dicts (``observation`` with ``rgb``/``instruction`` bytes, ``action``, ``is_first`` …); ``embed`` maps the
-    decoded instruction string to a 512-d vector (Universal Sentence Encoder upstream)."""
-    decode = decode or (lambda b: bytes(int(x) for x in np.asarray(b).tolist() if x != 0).decode("utf-8"))
+def _to_numpy(v):
+    """RLDS/TFDS hands out eager tensors (``.numpy()``); plain numpy / python values pass through."""
+    if hasattr(v, "numpy") and callable(v.numpy):
+        v = v.numpy()
+    return v
+
+
+def decode_instruction(inst) -> str:
+    """The Language-Table datasets store the instruction as zero-padded utf-8 byte values (reference ``rlds_np_convert.py:9-11``)."""
+    if isinstance(inst, (bytes, str)):
+        return inst.decode("utf-8") if isinstance(inst, bytes) else inst
+    arr = np.asarray(inst)
+    return bytes(int(x) for x in arr[arr != 0].tolist()).decode("utf-8")
+
+
+def flatten_rlds_episode(raw_episode) -> List[Dict]:
+    """One RLDS episode (``{"steps": iterable of {"observation": {...}, "action": ..., "is_first": ..., ...}}``, or the
+    bare iterable of steps) → list of flat step dicts: every step-level key except ``observation`` plus every observation key,
+    values as numpy — exactly what the reference's ``create_episode`` stores (``rlds_np_convert.py:13-26``)."""
+    steps = raw_episode["steps"] if isinstance(raw_episode, dict) and "steps" in raw_episode else raw_episode
+    out = []
+    for step in steps:
+        flat = {k: _to_numpy(v) for k, v in step.items() if k != "observation"}
+        for k, v in step.get("observation", {}).items():
+            flat[k] = _to_numpy(v)
+        out.append(flat)
+    return out
+
+
+def convert_rlds(episodes: Iterable, out_root: str, embed: Callable[[str], np.ndarray],
+                 splits=(("train", 7800), ("val", 100), ("test", 100)), raw_root: Optional[str] = None, decode=None) -> Dict[str, int]:
+    """RLDS → npy conversion (reference ``rlds_np_convert.py``): the first ``sum(counts)`` episodes are split
+    7 800 / 100 / 100; each becomes ``<out_root>/<split>/episode_<i>.npy`` with the byte-encoded instruction replaced by its
+    512-d sentence embedding (Universal Sentence Encoder upstream — ``embed`` here), all other step and observation keys kept.
+    With ``raw_root`` the un-embedded episodes are written too, as the reference does (its ``inst_*`` tree).  ``episodes`` is
+    any iterable of RLDS episodes (TFDS dataset, or numpy exports with the same nesting).  Returns episodes written per split."""
+    decode = decode or decode_instruction
     it = iter(episodes)
+    written: Dict[str, int] = {}
     for split, count in splits:
+        written[split] = 0
         for i in range(count):
             try:
-                ep = next(it)
+                raw = next(it)
             except StopIteration:
-                return
-            steps, cache = [], {}
-            for st in ep:
-                obs = st["observation"]
-                text = decode(obs["instruction"])
+                return written
+            steps = flatten_rlds_episode(raw)
+            if raw_root is not None:
+                save_episode(os.path.join(raw_root, split, f"episode_{i}.npy"), steps)
+            cache: Dict[str, np.ndarray] = {}
+            embedded = []
+            for st in steps:
+                text = decode(st["instruction"])
                 if text not in cache:
-                    cache[text] = np.asarray(embed(text), np.float32)
-                steps.append(make_step(obs["rgb"], cache[text], st["action"], st.get("is_first", False),
-                                       st.get("is_last", False), st.get("is_terminal", False),
-                                       st.get("reward", 0.0), obs.get("effector_translation"),
-                                       obs.get("effector_target_translation")))
-            save_episode(os.path.join(out_root, split, f"episode_{i}.npy"), steps)
+                    cache[text] = np.asarray(embed(text), np.float32).reshape(-1)
+                st = dict(st)
+                st["instruction"] = cache[text]
+                embedded.append(st)
+            save_episode(os.path.join(out_root, split, f"episode_{i}.npy"), embedded)
+            written[split] += 1
+    return written
+
+
+def iter_exported_episodes(source_dir: str):
+    """Episodes exported to disk with the RLDS nesting: ``<source_dir>/*.npy`` (pickled list of step dicts, or a dict with a
+    ``steps`` entry), in name order — the offline stand-in for ``tfds.builder_from_directory(...).as_dataset()``."""
+    for name in sorted(os.listdir(source_dir), key=lambda n: (len(n), n)):
+        if name.endswith(".npy"):
+            obj = np.load(os.path.join(source_dir, name), allow_pickle=True)
+            yield obj.item() if obj.dtype == object and obj.shape == () else list(obj)

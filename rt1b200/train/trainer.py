@@ -214,6 +214,7 @@ class GraphedTrainStep:
         # re-used by the captured step and synchronise the capture stream with the default stream, which is illegal
         # inside a capture.  Hooks, the stored loss and the stored aux tensors are such references.
         tr.engine.remove_ready_hooks()
+        tr.engine.use_single_bucket()                             # no overlap with backward any more: one fused exchange
         model._loss = None
         model._aux_info = {}
         if hasattr(model, "_attention_scores"):

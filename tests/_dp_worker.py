@@ -67,9 +67,9 @@ def main():
         assert eng.flat.params[0].grad.data_ptr() == eng.flat.grad.data_ptr()
     # 2. ranks still agree bit-for-bit
     if p2p:
-        pb = [torch.empty_like(eng.flat.param.view(torch.int16)) for _ in range(world)]
-        dist.all_gather(pb, eng.flat.param.view(torch.int16).contiguous())
-        assert all(torch.equal(pb[0], q) for q in pb), "bf16 parameters diverged"
+        pb = [torch.empty_like(eng.flat.param) for _ in range(world)]
+        dist.all_gather(pb, eng.flat.param.contiguous())           # NCCL moves bf16; the comparison below is bit-wise
+        assert all(torch.equal(pb[0].view(torch.int16), q.view(torch.int16)) for q in pb), "bf16 parameters diverged"
     gathered = [torch.empty_like(flat0) for _ in range(world)]
     dist.all_gather(gathered, eng.flat.master.contiguous())
     assert all(torch.equal(gathered[0], g) for g in gathered), "ranks diverged"

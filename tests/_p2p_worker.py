@@ -120,6 +120,11 @@ def main():
 
     # 4. optional sweep: bus bandwidth of P2P two-shot / one-shot vs NCCL, and the fused step's roofline fraction
     if "--sweep" in sys.argv:
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        from bench import ClockSampler
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
         rows = []
         sizes = [1 << k for k in range(10, 29)]          # 1 KB .. 256 MB
         big = comm.alloc_tensor((256 << 20) // 2 * 2, torch.bfloat16)
@@ -151,9 +156,12 @@ def main():
                            exp_avg_sq=torch.zeros(n_par, device=dev))
             h = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, bc1=0.1, bc2=0.001)
             import math
-            nb = min(4, max(1, math.ceil(n_par * 2 / 2 ** 20 / 48.0)))      # the engine's bucket policy
-            bucket = (n_par // nb + 63) // 64 * 64
-            bounds = [(a, min(n_par, a + bucket)) for a in range(0, n_par, bucket)]
+            nb_overlap = min(4, max(1, math.ceil(n_par * 2 / 2 ** 20 / 48.0)))      # the engine's bucket policy with overlap
+            bounds = []
+
+            def set_buckets(nb):
+                bucket = (n_par // nb + 63) // 64 * 64
+                bounds[:] = [(a, min(n_par, a + bucket)) for a in range(0, n_par, bucket)]
 
             def fused_step():
                 for k, (lo, hi) in enumerate(reversed(bounds)):
@@ -166,27 +174,33 @@ def main():
             for _ in range(3):
                 nccl_step()
             t_n = timed(nccl_step, 20, world, dev)
-            for algo in (["p2p", "nvls"] if comm.has_multicast else ["p2p"]):
-                for ctas in (64, 128, 148):
-                    comm.algo, comm.ctas_per_rank = algo, ctas
-                    for _ in range(3):
-                        fused_step()
-                    t_f = timed(fused_step, 20, world, dev)
-                    # bytes per direction per GPU: P2P pulls (W-1)/W of the grads and pushes (W-1)/W of the params;
-                    # NVLS sends N up for the in-switch reduce + N/W of parameters, receives N/W + N
-                    nbytes = n_par * 2
-                    link_bytes = 2 * (world - 1) / world * nbytes if algo == "p2p" else nbytes * (1 + 1 / world)
-                    t_link = link_bytes / 770e9 * 1e3
-                    hbm_bytes = n_par * (2 + 2) + n_par / world * (2 * world + 24 + 2)   # zero+incoming params, shard state
-                    t_hbm = hbm_bytes / 6551e9 * 1e3
-                    fused.append({"params": n_par, "world": world, "algo": algo, "ctas": ctas, "buckets": len(bounds), "fused_ms": t_f,
-                                  "nccl_plus_fused_adam_ms": t_n, "roof_link_ms": t_link, "roof_hbm_ms": t_hbm,
-                                  "roofline_fraction": max(t_link, t_hbm) / t_f})
+            for nb in sorted({1, nb_overlap}):
+                set_buckets(nb)
+                for algo in (["p2p", "nvls"] if comm.has_multicast else ["p2p"]):
+                    for ctas in (96, 148):
+                        comm.algo, comm.ctas_per_rank = algo, ctas
+                        for _ in range(3):
+                            fused_step()
+                        t_f = timed(fused_step, 20, world, dev)
+                        # bytes per direction per GPU: P2P pulls (W-1)/W of the grads and pushes (W-1)/W of the params;
+                        # NVLS sends N up for the in-switch reduce + N/W of parameters, receives N/W + N
+                        nbytes = n_par * 2
+                        link_bytes = 2 * (world - 1) / world * nbytes if algo == "p2p" else nbytes * (1 + 1 / world)
+                        t_link900, t_link770 = link_bytes / 900e9 * 1e3, link_bytes / 770e9 * 1e3
+                        hbm_bytes = n_par * (2 + 2) + n_par / world * (2 * world + 24 + 2)   # zero+incoming params, shard state
+                        t_hbm = hbm_bytes / 6551e9 * 1e3
+                        fused.append({"params": n_par, "world": world, "algo": algo, "ctas": ctas, "buckets": len(bounds),
+                                      "fused_ms": t_f, "nccl_plus_fused_adam_ms": t_n, "roof_link_ms_at_900GBs": t_link900,
+                                      "roof_link_ms_at_770GBs_measured_peer_copy": t_link770, "roof_hbm_ms": t_hbm,
+                                      "roofline_fraction_nominal_link_900": max(t_link900, t_hbm) / t_f,
+                                      "roofline_fraction_measured_link_770": max(t_link770, t_hbm) / t_f})
             comm.algo, comm.ctas_per_rank = "auto", 128
         if rank == 0:
+            clocks = sampler.stop()
             os.makedirs("gpurun_out", exist_ok=True)
             with open(f"gpurun_out/p2p_sweep_w{world}.json", "w") as f:
-                json.dump({"allreduce": rows, "fused_allreduce_adamw": fused}, f, indent=1)
+                json.dump({"allreduce": rows, "fused_allreduce_adamw": fused, "clocks": clocks,
+                           "timing": "CUDA events around 10-50 back-to-back calls, max over ranks"}, f, indent=1)
             for f_ in fused:
                 print(json.dumps(f_))
     dist.barrier()
