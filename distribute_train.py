@@ -56,6 +56,9 @@ def build_parser() -> ArgumentParser:
     p.add_argument("--max_steps", type=int, default=None)
     p.add_argument("--backend", choices=["auto", "p2p", "torchdist", "local"], default="auto")
     p.add_argument("--precision", choices=["bf16", "fp32"], default=None)
+    p.add_argument("--cpu_input", dest="gpu_input", action="store_false",
+                   help="crop + resize frames in the loader workers with PIL like the reference (default on a GPU: ship raw uint8 "
+                        "frames and crop/resize with a kernel)")
     return p
 
 
@@ -100,7 +103,12 @@ def make_loaders(args, rank: int, world: int):
             write_synthetic_dataset(args.dataset_dir, args.train_episode, args.eval_episode, args.test_episode)
         if world > 1:
             torch.distributed.barrier()
-    transform = DecodeAndRandomResizedCrop(args.random_crop_factor, (args.width, args.height))
+    if getattr(args, "gpu_input", True) and args.device in ("gpu", "cuda") and torch.cuda.is_available():
+        # workers ship raw uint8 frames + one crop box per frame; crop + bilinear resize run as a kernel on the GPU
+        from rt1b200.data.gpu_transforms import RawFramesWithBoxes
+        transform = RawFramesWithBoxes(args.random_crop_factor)
+    else:
+        transform = DecodeAndRandomResizedCrop(args.random_crop_factor, (args.width, args.height))
     out = []
     for split, n, shuffle in (("train", args.train_episode, True), ("test", args.test_episode, False),
                               ("val", args.eval_episode, False)):
@@ -128,6 +136,9 @@ def train(args):
     module = RT1Module(args)
     dtype = {None: None, "bf16": torch.bfloat16, "fp32": torch.float32}[args.precision]
     trainer = Trainer(module, args, device=device, backend=args.backend, param_dtype=dtype)
+    if device.type == "cuda" and getattr(args, "gpu_input", True):
+        from rt1b200.data.gpu_transforms import GpuCropResize
+        trainer.batch_transform = GpuCropResize(args.height, args.width)
     if rank == 0:
         print("Start training ...", flush=True)
     trainer.fit(train_loader, eval_loader, resume=args.resume, max_steps=args.max_steps)

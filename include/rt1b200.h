@@ -189,6 +189,11 @@ int rt1_action_detokenize(const long long* tokens, const float* low, const float
 int rt1_raster(const float* tris, const int* ntris, int max_tris, unsigned char* out, int E, int H, int W, float bg_r, float bg_g,
                float bg_b, cudaStream_t stream);
 int rt1_crop_resize(const unsigned char* in, float* out, int E, int H, int W, int OH, int OW, float crop, cudaStream_t stream);
+/* training input pipeline: per-frame crop box (top, left, height, width in source pixels; fp32 [E,4]) + bilinear resize of raw
+ * uint8 HWC frames to [E,3,OH,OW] (uint8, or fp32 in [0,1]) — replaces the per-frame PIL crop+resize of the reference's data
+ * loader workers (load_np_dataset.py:8-39) */
+int rt1_crop_resize_boxes(const unsigned char* in, const float* boxes, void* out, int out_uint8, int E, int H, int W, int OH, int OW,
+                          cudaStream_t stream);
 
 /* ---- NVLink / NVSwitch collectives fused with the optimizer (replaces DDP + NCCL all-reduce + Adam,
  *      reference distribute_train.py:99-110,231-238) ------------------------------------------------------------

@@ -107,15 +107,17 @@ class EmbodiedIntelligenceDataset(Dataset):
         eid, start = self.samples[idx]
         ep = self._episode(eid)
         sl = slice(start, start + self.window_length)
-        if self.transform is not None:
-            images = torch.stack([self.transform(f) for f in ep.rgb[sl]])
+        obs = {"natural_language_embedding": torch.from_numpy(ep.instruction[sl].copy())}
+        if self.transform is not None and getattr(self.transform, "windowed", False):
+            obs.update(self.transform(ep.rgb[sl]))            # raw uint8 frames + crop boxes: crop/resize happen on the GPU
+        elif self.transform is not None:
+            obs["image"] = torch.stack([self.transform(f) for f in ep.rgb[sl]])
         else:
-            images = torch.from_numpy(ep.rgb[sl]).permute(0, 3, 1, 2).float() / 255.0
+            obs["image"] = torch.from_numpy(ep.rgb[sl]).permute(0, 3, 1, 2).float() / 255.0
         return {
             "action_label": {"terminate_episode": torch.from_numpy(ep.is_terminal[sl].copy()),
                              "action": torch.from_numpy(ep.action[sl].copy())},
-            "train_observation": {"image": images,
-                                  "natural_language_embedding": torch.from_numpy(ep.instruction[sl].copy())},
+            "train_observation": obs,
         }
 
 
@@ -125,8 +127,7 @@ def collate_fn(batch: Sequence[Dict]) -> Dict:
     return {
         "action_label": {"terminate_episode": stack("action_label", "terminate_episode"),
                          "action": stack("action_label", "action")},
-        "train_observation": {"image": stack("train_observation", "image"),
-                              "natural_language_embedding": stack("train_observation", "natural_language_embedding")},
+        "train_observation": {k: stack("train_observation", k) for k in batch[0]["train_observation"]},
     }
 
 

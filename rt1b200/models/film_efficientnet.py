@@ -274,6 +274,36 @@ def EfficientNetB3(weights="imagenet", include_top=True, classes=1000, include_f
                                    include_film=include_film, **kwargs)
 
 
+class ILSVRCPredictor:
+    """Top-k ImageNet label names of a classifier output (reference ``film_efficientnet_encoder.py:445-459``).
+
+    The reference reads ``efficientnet_checkpoints/imagenet_classes.json`` (``{"281": ["n02123045", "tabby"], ...}``).  That
+    file is looked up next to this module, in the reference installation, or at ``class_index_path``; without it the category
+    names that torchvision ships with its EfficientNet-B3 weight metadata are used (same order, no download involved)."""
+
+    def __init__(self, top: int = 5, class_index_path: Optional[str] = None):
+        import json
+        self.top = top
+        candidates = [class_index_path, os.path.join(_CKPT_DIR, "imagenet_classes.json"),
+                      os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "baseline", "_ref",
+                                   "pytorch_robotics_transformer", "film_efficientnet", "efficientnet_checkpoints",
+                                   "imagenet_classes.json")]
+        self.class_index = None
+        for c in candidates:
+            if c and os.path.isfile(c):
+                with open(c, "r") as f:
+                    self.class_index = {int(k): v[1] for k, v in json.load(f).items()}
+                break
+        if self.class_index is None:
+            from torchvision.models import EfficientNet_B3_Weights
+            self.class_index = dict(enumerate(EfficientNet_B3_Weights.IMAGENET1K_V1.meta["categories"]))
+
+    def predict_topk(self, out: torch.Tensor):
+        assert out.shape[0] == 1, "Only accept tensor with batch size 1 to simplify implementation"
+        top = torch.argsort(out[0].detach().float().cpu(), descending=True)[:self.top].tolist()
+        return [self.class_index[i] for i in top]
+
+
 class EfficientNetEncoder(nn.Module):
     """EfficientNet-B3 (no top, FiLM after every block) → 1x1 conv 1536→``token_embedding_size`` → FiLM.
 

@@ -163,9 +163,11 @@ class Transformer(nn.Module):
         return self._token_emb(inputs) + self._position_emb(pos_ids).unsqueeze(0)
 
     def trunk(self, x: torch.Tensor, attention_mask) -> Tuple[torch.Tensor, List[torch.Tensor]]:
+        from ..utils import trace
         scores = []
-        for layer in self._layers:
-            x, s = layer(x, mask=attention_mask)
+        for i, layer in enumerate(self._layers):
+            with trace.range_(f"decoder/layer {i} fwd"):
+                x, s = layer(x, mask=attention_mask)
             if s is not None:
                 scores.append(s)
         return x, scores

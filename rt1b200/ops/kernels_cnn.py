@@ -24,6 +24,7 @@ from torch.autograd import Function
 from . import _lib
 from ._lib import call, f32, i32, i64, ptr, stream
 from .kernels import BF16, _grad_slot, _ready, gemm, wgrad_lane
+from ..utils import trace
 
 F32 = torch.float32
 # BatchNorm+SiLU of the expand conv applied inside the depthwise tile (1) or materialised by an elementwise pass (0)
@@ -165,6 +166,8 @@ class _EncoderFn(Function):
 
         # ---- MBConv blocks -------------------------------------------------------------------------------
         for bi, blk in enumerate(net.blocks):
+            if trace.ENABLED:
+                torch.cuda.nvtx.range_push(f"encoder/block {bi} fwd")
             st = {}
             Cin, Ce, Co, k, s = blk.in_size, blk.expand_size, blk.out_size, blk.kernel_size, blk.strides
             M = N * Hc * Wc
@@ -223,6 +226,8 @@ class _EncoderFn(Function):
             st.update(d_raw=d_raw, bn2=bn2, a2=a2, y_raw=y_raw, bn3=bn3, sd=sd, Ho=Ho, Wo=Wo)
             S.append(st)
             x, Hc, Wc = out, Ho, Wo
+            if trace.ENABLED:
+                torch.cuda.nvtx.range_pop()
 
         # ---- head: 1x1 → BN → SiLU → 1x1 → FiLM ------------------------------------------------------------
         convh, bnhm = net.convNormAct1[0], net.convNormAct1[1]
@@ -293,6 +298,8 @@ class _EncoderFn(Function):
         # ---- blocks, last to first -------------------------------------------------------------------------
         dout = dx.view(N, Hc, Wc, Cl)
         for bi in range(len(S) - 1, -1, -1):
+            if trace.ENABLED:
+                torch.cuda.nvtx.range_push(f"encoder/block {bi} bwd")
             st, blk = S[bi], net.blocks[bi]
             Cin, Ce, Co, k, s = blk.in_size, blk.expand_size, blk.out_size, blk.kernel_size, blk.strides
             Ho, Wo, Hin, Win = st["Ho"], st["Wo"], st["Hin"], st["Win"]
@@ -394,6 +401,8 @@ class _EncoderFn(Function):
             # release this block's saved activations as early as possible
             st.clear()
             dout = dxi.view(N, Hin, Win, Cin)
+            if trace.ENABLED:
+                torch.cuda.nvtx.range_pop()
 
         lane.flush()
 

@@ -32,6 +32,7 @@ import torch.nn as nn
 from ..models.factory import RT1Config, build_rt1
 from ..models.tokenizers import batched_space_sampler, np_to_tensor
 from ..parallel.engine import DataParallelEngine
+from ..utils import trace
 
 
 class RT1Module(nn.Module):
@@ -304,8 +305,10 @@ class Trainer:
             _, dev_batch, ev = pf
             self._prefetched = None
             torch.cuda.current_stream(self.device).wait_event(ev)
-            return dev_batch
-        return to_device(batch, self.device)
+        else:
+            dev_batch = to_device(batch, self.device)
+        tf = getattr(self, "batch_transform", None)      # device-side input transform (e.g. data.gpu_transforms.GpuCropResize)
+        return tf(dev_batch) if tf is not None else dev_batch
 
     def prefetch(self, batch):
         """Start the host→device copy of a (pinned) host batch on a copy stream while the current step computes; the next
@@ -332,16 +335,21 @@ class Trainer:
         lr = self.sched.get_lr()
         g = self._graph_for(batch) if self._graph_on else None
         if g is not None:
-            loss = g.run(batch)                       # forward + backward: one graph replay
+            with trace.range_("train_step/graph replay (forward + backward)"):
+                loss = g.run(batch)                   # forward + backward: one graph replay
             self._stage_loss(loss)
-            self.engine.step(lr)                      # fused gradient exchange + AdamW (clears the gradients)
+            with trace.range_("train_step/fused exchange + AdamW"):
+                self.engine.step(lr)                  # fused gradient exchange + AdamW (clears the gradients)
             self.global_step += 1
             return loss
-        loss = self.module.training_step(batch, self.global_step)
+        with trace.range_("train_step/forward"):
+            loss = self.module.training_step(batch, self.global_step)
         self._stage_loss(loss)
         self.engine.begin_step(lr)
-        loss.backward()
-        self.engine.step(lr)
+        with trace.range_("train_step/backward (+ overlapped exchange)"):
+            loss.backward()
+        with trace.range_("train_step/fused exchange + AdamW"):
+            self.engine.step(lr)
         self.global_step += 1
         return loss.detach()
 

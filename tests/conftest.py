@@ -34,6 +34,8 @@ class _Reference:
         if not refenv.available() and not refenv.try_install():
             pytest.skip(refenv.why_unavailable())
         saved_path = list(sys.path)
+        tops = ("pytorch_robotics_transformer", "distribute_train", "load_np_dataset", "language_table")   # names both trees define
+        saved_modules = {n: m for n, m in sys.modules.items() if n.split(".")[0] in tops}
         try:
             refenv.activate()
             import pytorch_robotics_transformer.transformer_network as tn
@@ -47,6 +49,25 @@ class _Reference:
             self.token_learner, self.film_efficientnet_encoder, self.preprocessors, self.spaces = tl, fe, pp, gs
         finally:
             sys.path[:] = saved_path
+            # activate() evicted this repository's same-named packages from sys.modules; put them back (and drop the
+            # reference's entries — its module objects stay alive as attributes of this handle), otherwise a later
+            # ``import language_table...`` would create a SECOND copy of our modules next to the ones already bound.
+            for n in [n for n in sys.modules if n.split(".")[0] in tops]:
+                del sys.modules[n]
+            sys.modules.update(saved_modules)
+
+
+@pytest.fixture(autouse=True)
+def _reset_dropout_seed_epoch():
+    """A captured training step registers a device word that is added to every dropout seed (rt1_set_seed_epoch); tests that
+    rebuild dropout masks on the host expect it to be zero."""
+    yield
+    try:
+        from rt1b200.ops import kernels
+        for t in kernels._seed_epoch.values():
+            t.zero_()
+    except Exception:
+        pass
 
 
 @pytest.fixture(scope="session")

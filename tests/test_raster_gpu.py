@@ -58,3 +58,19 @@ def test_graphed_policy_matches_eager_steps():
     assert int(gp.state["seq_idx"][0]) == T
     gp.reset()
     assert int(gp.state["seq_idx"].sum()) == 0
+
+
+def test_crop_resize_boxes_kernel_matches_its_pytorch_statement():
+    """rt1_crop_resize_boxes (per-frame crop box + bilinear resize of raw uint8 frames) vs the PyTorch statement of the same
+    sampling rule, uint8 and float outputs."""
+    from rt1b200.data.gpu_transforms import crop_resize_boxes, crop_resize_boxes_reference
+    g = torch.Generator().manual_seed(0)
+    frames = torch.randint(0, 256, (5, 45, 80, 3), dtype=torch.uint8, generator=g)
+    boxes = torch.tensor([[0, 0, 45, 80], [2, 3, 42.75, 76.0], [1.0, 4.0, 42.75, 76.0], [0, 0, 20, 30], [10, 20, 35, 60]], dtype=torch.float32)
+    want8 = crop_resize_boxes_reference(frames, boxes, (64, 114), as_uint8=True)
+    got8 = crop_resize_boxes(frames.cuda(), boxes.cuda(), (64, 114), as_uint8=True).cpu()
+    assert got8.dtype == torch.uint8 and int((got8.int() - want8.int()).abs().max()) <= 1      # fp rounding at .5 boundaries
+    assert float((got8.int() - want8.int()).abs().float().mean()) < 0.01
+    wantf = crop_resize_boxes_reference(frames, boxes, (64, 114), as_uint8=False)
+    gotf = crop_resize_boxes(frames.cuda(), boxes.cuda(), (64, 114), as_uint8=False).cpu()
+    torch.testing.assert_close(gotf, wantf, rtol=1e-5, atol=1e-5)

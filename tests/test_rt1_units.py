@@ -139,3 +139,29 @@ def test_policy_is_causal():
             out, _ = net._transformer(changed, net._default_attention_mask)
             assert torch.equal(out[:, :cut], base[:, :cut]), step
             assert not torch.equal(out[:, cut:], base[:, cut:])
+
+
+def test_gpu_input_transform_cpu_statement_matches_pil(tmp_path):
+    """RawFramesWithBoxes + crop_resize_boxes (CPU statement) against the reference-style PIL transform, same crop box:
+    enlarging 180x320 → 256x456, PIL's bilinear resize and the kernel's half-pixel sampling agree to a grey level."""
+    import numpy as np
+    from PIL import Image
+    from rt1b200.data.gpu_transforms import GpuCropResize, RawFramesWithBoxes, crop_resize_boxes_reference
+    rng = np.random.default_rng(0)
+    yy, xx = np.mgrid[0:180, 0:320]
+    frames = np.stack([np.stack([(xx * 0.7 + yy * 0.3 + 20 * k) % 256, (yy * 1.2 + 7 * k) % 256, (xx + yy) % 256], -1) for k in range(3)]).astype(np.uint8)
+    out = RawFramesWithBoxes(0.95, rng=np.random.default_rng(1))(frames)
+    assert out["image_raw"].shape == (3, 180, 320, 3) and out["crop_boxes"].shape == (3, 4)
+    got = crop_resize_boxes_reference(out["image_raw"], out["crop_boxes"], (256, 456), as_uint8=True)
+    for k in range(3):
+        top, left, h, w = out["crop_boxes"][k].tolist()
+        assert 0 <= top <= 9 and 0 <= left <= 16 and abs(h - 171.0) < 1e-4 and abs(w - 304.0) < 1e-4
+        pil = Image.fromarray(frames[k]).crop((left, top, left + w, top + h)).resize((456, 256), Image.BILINEAR)
+        want = np.asarray(pil).transpose(2, 0, 1).astype(int)
+        diff = np.abs(got[k].numpy().astype(int) - want)
+        # the synthetic ramp wraps at 256: ignore the few pixels that straddle a wrap, compare the rest to two grey levels
+        assert np.percentile(diff, 99) <= 2, np.percentile(diff, [50, 90, 99, 100])
+    batch = {"train_observation": {"image_raw": out["image_raw"][None], "crop_boxes": out["crop_boxes"][None],
+                                   "natural_language_embedding": torch.zeros(1, 3, 512)}, "action_label": {}}
+    tb = GpuCropResize(256, 456)(batch)
+    assert tb["train_observation"]["image"].shape == (1, 3, 3, 256, 456) and "image_raw" not in tb["train_observation"]

@@ -163,8 +163,13 @@ if __name__ == "__main__":
     ap.add_argument("--envs", type=int, default=64)
     ap.add_argument("--steps", type=int, default=30)
     a = ap.parse_args()
+    from bench import ClockSampler          # every recorded number carries the clocks seen while it was taken
+    sampler = ClockSampler(0)
+    sampler.start()
     try:
         out = {"ours": ours, "reference": reference, "raster": raster_bench, "graphed": graphed}[a.impl](a)
     except Exception as e:      # noqa: BLE001
         out = {"impl": a.impl, "error": f"{type(e).__name__}: {str(e)[:400]}"}
+    out["clocks"] = sampler.stop()
+    out["timing"] = "CUDA events per call, p50/p99 over --steps calls after 3 warm-up calls"
     print(json.dumps(out), flush=True)
