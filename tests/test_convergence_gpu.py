@@ -49,35 +49,53 @@ def test_bf16_kernel_training_tracks_fp32_reference(reference, monkeypatch):
         return real_randint(low, high, size, **kw) if high is not None else real_randint(low, size, **kw)
 
     tr = Trainer(module, args, device=dev, param_dtype=torch.bfloat16, loggers=[], verbose=False, graph=True)
-    ref = ref.to(dev).train()
-    opt = torch.optim.Adam(ref.parameters(), lr=LR)
+    # A second copy of the fp32 reference whose INITIAL weights are rounded to bf16: how far a rounding-sized perturbation
+    # moves the fp32 model's own trajectory on these batches is the yardstick for "the bf16 path tracks it".
+    import copy
+    ref_b = copy.deepcopy(ref)
+    with torch.no_grad():
+        for p_ in ref_b.parameters():
+            p_.copy_(p_.to(torch.bfloat16).float())
     src = SyntheticBatchSource(B, T, H, W, pool=6, seed=11, image_dtype=torch.float32, pin=False)
-    state = {"context_image_tokens": torch.zeros(B, T, 8, 512, device=dev), "action_tokens": torch.zeros(B, T, 3, dtype=torch.long, device=dev),
-             "seq_idx": torch.zeros(B, dtype=torch.long, device=dev)}
-    ours, theirs = [], []
-    for i in range(STEPS):
-        batch = to_device(src.pool[i % len(src.pool)], dev)
-        ours.append(float(tr.train_step(batch)))
-        monkeypatch.setattr(torch, "randint", centred_randint)
-        try:
-            ref.set_actions(batch["action_label"])
-            ref(batch["train_observation"], state)
-            loss = ref.get_actor_loss().mean()
-        finally:
-            monkeypatch.setattr(torch, "randint", real_randint)
-        opt.zero_grad(set_to_none=True)
-        loss.backward()
-        opt.step()
-        theirs.append(float(loss))
-    ours, theirs = np.array(ours), np.array(theirs)
+
+    def run_reference(net):
+        net = net.to(dev).train()
+        opt = torch.optim.Adam(net.parameters(), lr=LR)
+        state = {"context_image_tokens": torch.zeros(B, T, 8, 512, device=dev),
+                 "action_tokens": torch.zeros(B, T, 3, dtype=torch.long, device=dev), "seq_idx": torch.zeros(B, dtype=torch.long, device=dev)}
+        out = []
+        for i in range(STEPS):
+            batch = to_device(src.pool[i % len(src.pool)], dev)
+            monkeypatch.setattr(torch, "randint", centred_randint)
+            try:
+                net.set_actions(batch["action_label"])
+                net(batch["train_observation"], state)
+                loss = net.get_actor_loss().mean()
+            finally:
+                monkeypatch.setattr(torch, "randint", real_randint)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+            out.append(float(loss))
+        return np.array(out)
+
+    ours = np.array([float(tr.train_step(to_device(src.pool[i % len(src.pool)], dev))) for i in range(STEPS)])
+    theirs = run_reference(ref)
+    theirs_b = run_reference(ref_b)
     assert np.isfinite(ours).all() and np.isfinite(theirs).all()
     assert theirs[-10:].mean() < 0.7 * theirs[:5].mean(), "the reference itself did not learn these batches"
     # identical start (same weights, same batch): bf16 rounding only
     assert abs(ours[0] - theirs[0]) <= 0.02 * theirs[0], (ours[0], theirs[0])
-    # the curves stay together: windowed means within 10 % after the first ten steps (measured: up to 7 %, either sign — a
-    # 26-block BatchNorm network at batch 4 x 3 frames is noisy, and the fp32 reference itself moves by that much between
-    # runs with different atomics order), and the whole-run means within 5 %
-    for a in range(10, STEPS - 5, 5):
-        o, r = ours[a:a + 10].mean(), theirs[a:a + 10].mean()
-        assert abs(o - r) <= 0.10 * r, (a, o, r, ours.tolist(), theirs.tolist())
-    assert abs(ours[10:].mean() - theirs[10:].mean()) <= 0.05 * theirs[10:].mean(), (ours[10:].mean(), theirs[10:].mean())
+    # The curves stay together after the first ten steps.  Tolerance: 5 % on 10-step windowed means, widened to twice the
+    # spread the fp32 reference shows against ITSELF when only its initial weights are rounded to bf16 (a 26-block BatchNorm
+    # network at batch 4 x 3 frames, cycling six batches with Adam at 5e-4, amplifies rounding-sized perturbations: windows
+    # moved by 7-13 % between two boxes, either sign, with the whole-run means within 2 %).
+    windows = [(a, ours[a:a + 10].mean(), theirs[a:a + 10].mean(), theirs_b[a:a + 10].mean()) for a in range(10, STEPS - 5, 5)]
+    spread = max(abs(rb - r) / r for _, _, r, rb in windows)
+    tol = max(0.05, 2.0 * spread)
+    print(f"[convergence] fp32-vs-fp32(bf16-rounded init) spread {spread:.3f}; tolerance {tol:.3f}; "
+          f"ours/ref per window {[round(o / r, 3) for _, o, r, _ in windows]}")
+    assert tol <= 0.30, f"the fp32 reference is chaotic on this problem (spread {spread:.3f}): the comparison says nothing"
+    for a, o, r, _ in windows:
+        assert abs(o - r) <= tol * r, (a, o, r, tol)
+    assert abs(ours[10:].mean() - theirs[10:].mean()) <= max(0.05, spread) * theirs[10:].mean(), (ours[10:].mean(), theirs[10:].mean())
