@@ -44,6 +44,26 @@ int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long lo
                   long long ldo, int out_fp32, int M, int N, int K, const void* bias, const void* residual,
                   long long ldr, float alpha, float dropout_p, unsigned seed, int split_k, int accumulate,
                   float* col_sum, float* col_sumsq, cudaStream_t stream);
+/* BatchNorm "tail" of a statistics-producing kernel: the CTA that adds the LAST contribution to sum / sumsq (a ticket counter,
+ * no CTA waits for another) turns them into a = gamma*rstd, b = beta - mean*a, mean, rstd and updates the running statistics —
+ * what rt1_bn_finalize does as a launch of its own.  ticket: one uint32, zeroed by the caller before every use. */
+typedef struct Rt1BnTail {
+  const void* gamma;        /* bf16 [C] */
+  const void* beta;         /* bf16 [C] */
+  float* running_mean;      /* fp32 [C] or NULL */
+  float* running_var;
+  float* a;                 /* fp32 [C] outputs */
+  float* b;
+  float* mean;
+  float* rstd;
+  unsigned int* ticket;
+  float count;              /* elements per channel */
+  float momentum;
+  float eps;
+} Rt1BnTail;
+/* rt1_gemm_bf16 with bf16 output, no epilogue terms, column statistics AND their BatchNorm tail (host pointer to the struct) */
+int rt1_gemm_bf16_bn(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out, long long ldo,
+                     int M, int N, int K, float* col_sum, float* col_sumsq, const Rt1BnTail* tail, cudaStream_t stream);
 int rt1_colsum_bf16(const void* x, long long ld, int M, int N, void* out_bf16, cudaStream_t stream);
 int rt1_cast_f32_bf16(const float* in, void* out_bf16, long long n, cudaStream_t stream);
 int rt1_dropout_apply(const void* in, void* out, long long n, float p, unsigned seed, cudaStream_t stream);
@@ -84,18 +104,6 @@ int rt1_action_ce_fwd(const void* logits, const long long* labels, float* loss, 
 int rt1_action_ce_bwd(const void* logits, const long long* labels, const float* row_lse, const float* dloss,
                       void* dlogits, int R, int A, int V, float num_items, cudaStream_t stream);
 
-/* ---- TokenLearner (reference tokenizers/token_learner.py:64-95) --------------------------------------------
- * feats [n,P,C] bf16 -> tokens (row n at tokens + n*out_stride, [T,C]). 64-wide bottleneck. */
-int rt1_token_learner_fwd(const void* feats, const void* ln_w, const void* ln_b, const void* w1, const void* b1,
-                          const void* w2, const void* b2, void* tokens, long long out_stride, int n, int P, int C, int T,
-                          float eps, cudaStream_t stream);
-long long rt1_token_learner_scratch_floats(int C, int T);
-/* scratch: fp32 [rt1_token_learner_scratch_floats(C, T)]; cleared by the call, holds the parameter-gradient sums */
-int rt1_token_learner_bwd(const void* feats, const void* ln_w, const void* ln_b, const void* w1, const void* b1,
-                          const void* w2, const void* b2, const void* dtokens, long long dtok_stride, void* dfeats,
-                          float* scratch, void* dln_w, void* dln_b, void* dw1, void* db1, void* dw2, void* db2, int n, int P,
-                          int C, int T, float eps, cudaStream_t stream);
-
 /* ---- frame pre-processing (reference film_efficientnet/preprocessors.py:37-56) ---------------------------
  * in [N,3,H,W] uint8|f32 -> out [N,H,W,8] bf16 NHWC with the pad-and-shift crop (one offset per batch). */
 int rt1_preprocess_nhwc(const void* in, int in_is_uint8, void* out, int N, int H, int W, int shift_h, int shift_w,
@@ -109,7 +117,7 @@ int rt1_fused_adamw(void* param_bf16, float* master, void* grad, int grad_is_bf1
                     long long n, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
                     float bias_corr2, float grad_scale, int zero_grad, cudaStream_t stream);
 
-/* ---- TokenLearner, GEMM-composed path (reference tokenizers/token_learner.py:64-95) -------------------------------
+/* ---- TokenLearner (reference tokenizers/token_learner.py:64-95); C % 64 == 0, T <= 8, P <= 512 ----------------------
  * hpre [n*P,64] = LayerNorm(feats) . W1^T + b1 comes from rt1_layernorm_fwd + rt1_gemm_bf16; these finish the module:
  * softmax over the P positions of gelu(hpre).W2^T + b2 and the weighted pooling (fwd); dwmap → softmax backward → dhpre
  * plus dW2/db2 sums (bwd; scratch fp32 [T*64+T], zeroed by the call); dfeats += wmap.dtok (direct pooling gradient). */
@@ -143,28 +151,31 @@ int rt1_block_finalize_bwd(const void* dout, const void* y, const void* skip, co
 int rt1_se_scale_bwd_reduce(const void* g, const void* x, const float* a, const float* b, float* ds, int N, int HW, int C,
                             cudaStream_t stream);
 /* ONE pass over (g, x) for both the SE-scale gradient and the separable parts of the BatchNorm-backward sums of the same
- * tensor: out5 fp32 [5][N][C] = ds, A1..A4 (zeroed by the call); rt1_bn_sums_from_parts combines A1..A4 with s and dpool
- * (known only after the SE backward) into the [2,C] sums that rt1_bn_act_bwd accepts with sums_ready = 1. */
+ * tensor: out5 fp32 [5][N][C] = ds, A1..A4 (zeroed by the call); rt1_se_bwd combines A1..A4 with s and dpool (known only
+ * after the SE backward) into the [2,C] sums that rt1_bn_act_bwd accepts with sums_ready = 1. */
 int rt1_se_bn_bwd_reduce(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
                          float* out5, int N, int HW, int C, cudaStream_t stream);
-int rt1_bn_sums_from_parts(const float* parts, const float* s, const float* dpool, float* sums, int N, int C, cudaStream_t stream);
-/* backward of t = act(BN(x)) [* s + pooled gradient]: reduce pass (skipped when sums_ready), dgamma/dbeta, dx */
+/* backward of t = act(BN(x)) [* s + pooled gradient]: reduce pass into sums fp32 [2,C] (skipped when sums_ready: the depthwise
+ * data-gradient kernel or rt1_se_bwd filled them), then one apply pass that writes dx and dgamma / dbeta (16-byte aligned) */
 int rt1_bn_act_bwd(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
-                   const float* s, const float* dpool, float* sums, int sums_ready, float* c1, float* c2, void* dgamma, void* dbeta,
-                   void* dx, int N, int HW, int C, int silu, cudaStream_t stream);
+                   const float* s, const float* dpool, float* sums, int sums_ready, void* dgamma, void* dbeta, void* dx, int N,
+                   int HW, int C, int silu, cudaStream_t stream);
 /* squeeze-excite FC pair on per-frame vectors (z1, s fp32 outputs; Cs even, <= 128) and its backward + weight gradients */
 int rt1_se_fc_fwd(const float* pooled_sum, float inv_hw, const void* w1, const void* b1, const void* w2, const void* b2, float* z1,
                   float* s, int N, int C, int Cs, cudaStream_t stream);
-int rt1_se_fc_bwd(const float* ds, const float* s, const float* z1, const float* pooled_sum, float inv_hw, const void* w1,
-                  const void* w2, float* dz2, float* dz1, float* dpooled, void* dw1, void* db1, void* dw2, void* db2, int N, int C,
-                  int Cs, cudaStream_t stream);
-/* the parameter-gradient half of rt1_se_fc_bwd alone (call that one with dw1 = NULL): a leaf that can run on another stream */
-int rt1_se_wgrad(const float* dz2, const float* dz1, const float* z1, const float* pooled_sum, float inv_hw, void* dw1, void* db1,
-                 void* dw2, void* db2, int N, int C, int Cs, cudaStream_t stream);
+/* Backward of the FC pair, its parameter gradients and (parts != NULL) the BatchNorm-backward sums of the scaled tensor, as two
+ * launches in which a CTA owns a 32-channel slice for all frames.  dhid: fp32 [N, ceil4(Cs)] scratch ZEROED BY THE CALLER;
+ * dpooled fp32 [N,C] is the per-pixel gradient (already / HW); parts = out5 of rt1_se_bn_bwd_reduce, sums fp32 [2,C] out. */
+int rt1_se_bwd(const float* ds, const float* s, const float* z1, const float* pooled_sum, float inv_hw, const void* w1, const void* w2,
+               const float* parts, float* dhid, float* dpooled, float* sums, void* dw1, void* db1, void* dw2, void* db2, int N, int C,
+               int Cs, cudaStream_t stream);
 /* depthwise k x k (k in {3,5}, stride in {1,2}, pad (k-1)/2): forward (+ BN statistics of the output), data gradient
  * (x SiLU'(BN(x_raw)) + BN-backward sums when x_raw/a_in/... are given), weight gradient (scratch fp32 [k*k*C]) */
 int rt1_dwconv_fwd(const void* x, const float* a_in, const float* b_in, const void* w, void* y, float* sum, float* sumsq, int N,
                    int H, int W, int C, int k, int stride, cudaStream_t stream);
+/* rt1_dwconv_fwd + the BatchNorm tail of its output statistics */
+int rt1_dwconv_fwd_bn(const void* x, const float* a_in, const float* b_in, const void* w, void* y, float* sum, float* sumsq,
+                      const Rt1BnTail* tail, int N, int H, int W, int C, int k, int stride, cudaStream_t stream);
 int rt1_dwconv_bwd_data(const void* dout, const void* w, const void* x_raw, const float* a_in, const float* b_in, const float* mean,
                         const float* rstd, void* din, float* sums, int N, int H, int W, int C, int k, int stride,
                         cudaStream_t stream);

@@ -9,6 +9,8 @@
 __global__ void action_tokenize_kernel(const float* __restrict__ vals, const float* __restrict__ low, const float* __restrict__ high,
                                        const uint8_t* __restrict__ discrete, long long* __restrict__ tokens, long total, int A,
                                        float vmax) {
+  pdl_trigger();
+  pdl_wait();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int k = (int)(i % A);
@@ -27,6 +29,8 @@ __global__ void action_tokenize_kernel(const float* __restrict__ vals, const flo
 __global__ void action_detokenize_kernel(const long long* __restrict__ tokens, const float* __restrict__ low,
                                          const float* __restrict__ high, const uint8_t* __restrict__ discrete,
                                          float* __restrict__ vals, long total, int A, float vmax) {
+  pdl_trigger();
+  pdl_wait();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int k = (int)(i % A);
@@ -42,7 +46,7 @@ RT1_API int rt1_action_tokenize(const float* vals, const float* low, const float
                                 long long* tokens, long long R, int A, int vocab, cudaStream_t stream) {
   const long total = (long)R * A;
   if (total <= 0) return 0;
-  action_tokenize_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>(vals, low, high, discrete, tokens, total, A, (float)(vocab - 1));
+  rt1_launch(action_tokenize_kernel, rt1_cdiv(total, 256), 256, 0, stream, vals, low, high, discrete, tokens, total, A, (float)(vocab - 1));
   return rt1_check_launch("rt1_action_tokenize");
 }
 
@@ -51,6 +55,6 @@ RT1_API int rt1_action_detokenize(const long long* tokens, const float* low, con
                                   float* vals, long long R, int A, int vocab, cudaStream_t stream) {
   const long total = (long)R * A;
   if (total <= 0) return 0;
-  action_detokenize_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>(tokens, low, high, discrete, vals, total, A, (float)(vocab - 1));
+  rt1_launch(action_detokenize_kernel, rt1_cdiv(total, 256), 256, 0, stream, tokens, low, high, discrete, vals, total, A, (float)(vocab - 1));
   return rt1_check_launch("rt1_action_detokenize");
 }

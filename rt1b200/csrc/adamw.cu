@@ -12,6 +12,8 @@ template <bool GRAD_BF16>
 __global__ void __launch_bounds__(256) adamw_flat_kernel(bf16* __restrict__ p_lp, float* __restrict__ p, void* __restrict__ g_,
                                                          float* __restrict__ m, float* __restrict__ v, long n, AdamHyper h,
                                                          int zero_grad) {
+  pdl_trigger();
+  pdl_wait();
   const long n8 = n >> 3;
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long stride = (long)gridDim.x * blockDim.x;
@@ -76,8 +78,8 @@ RT1_API int rt1_fused_adamw(void* param_bf16, float* master, void* grad, int gra
   if (blocks > 148 * 16) blocks = 148 * 16;
   if (blocks < 1) blocks = 1;
   if (grad_is_bf16)
-    adamw_flat_kernel<true><<<blocks, 256, 0, stream>>>((bf16*)param_bf16, master, grad, exp_avg, exp_avg_sq, n, h, zero_grad);
+    rt1_launch(adamw_flat_kernel<true>, blocks, 256, 0, stream, (bf16*)param_bf16, master, grad, exp_avg, exp_avg_sq, n, h, zero_grad);
   else
-    adamw_flat_kernel<false><<<blocks, 256, 0, stream>>>((bf16*)param_bf16, master, grad, exp_avg, exp_avg_sq, n, h, zero_grad);
+    rt1_launch(adamw_flat_kernel<false>, blocks, 256, 0, stream, (bf16*)param_bf16, master, grad, exp_avg, exp_avg_sq, n, h, zero_grad);
   return rt1_check_launch("rt1_fused_adamw");
 }

@@ -73,6 +73,8 @@ __device__ __forceinline__ void scores_softmax(const bf16* q, const bf16* k, flo
 
 __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_kernel(const bf16* __restrict__ qkv, const uint8_t* __restrict__ mask,
                                                                bf16* __restrict__ out, AttnDims d) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t smem[];
   const int S = d.S, DK = d.DK, ld = DK + 8, ldp = S + 1;
   bf16* q = reinterpret_cast<bf16*>(smem);
@@ -118,6 +120,8 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_kernel(const bf16* __res
 __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_kernel(const bf16* __restrict__ qkv, const uint8_t* __restrict__ mask,
                                                                const bf16* __restrict__ dout, bf16* __restrict__ dqkv,
                                                                AttnDims d) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t smem[];
   const int S = d.S, DK = d.DK, ld = DK + 8, ldp = S + 1;
   bf16* q = reinterpret_cast<bf16*>(smem);
@@ -211,7 +215,7 @@ RT1_API int rt1_attention_fwd(const void* qkv, const unsigned char* mask, void* 
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_attention_fwd: S=%d dk=%d needs %zu B of shared memory", S, DK, smem);
   if (int rc = rt1_ensure_dyn_smem((const void*)attn_fwd_kernel, smem)) return rc;
   AttnDims d{B, S, H, DK, 1.f / sqrtf((float)DK), p_drop, seed, p_drop > 0.f ? rt1_seed_epoch_ptr() : nullptr};
-  attn_fwd_kernel<<<dim3(H, B), ATT_THREADS, smem, stream>>>((const bf16*)qkv, mask, (bf16*)out, d);
+  rt1_launch(attn_fwd_kernel, dim3(H, B), ATT_THREADS, smem, stream, (const bf16*)qkv, mask, (bf16*)out, d);
   return rt1_check_launch("rt1_attention_fwd");
 }
 
@@ -224,18 +228,20 @@ RT1_API int rt1_attention_bwd(const void* qkv, const unsigned char* mask, const 
   RT1_REQUIRE(smem <= 227 * 1024, "rt1_attention_bwd: S=%d dk=%d needs %zu B of shared memory", S, DK, smem);
   if (int rc = rt1_ensure_dyn_smem((const void*)attn_bwd_kernel, smem)) return rc;
   AttnDims d{B, S, H, DK, 1.f / sqrtf((float)DK), p_drop, seed, p_drop > 0.f ? rt1_seed_epoch_ptr() : nullptr};
-  attn_bwd_kernel<<<dim3(H, B), ATT_THREADS, smem, stream>>>((const bf16*)qkv, mask, (const bf16*)dout, (bf16*)dqkv, d);
+  rt1_launch(attn_bwd_kernel, dim3(H, B), ATT_THREADS, smem, stream, (const bf16*)qkv, mask, (const bf16*)dout, (bf16*)dqkv, d);
   return rt1_check_launch("rt1_attention_bwd");
 }
 
 // dropout mask re-application for the backward of a GEMM-epilogue dropout: out = keep ? in/(1-p) : 0
 __global__ void dropout_apply_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, long n, uint32_t thresh, float ks,
                                      uint32_t seed, const uint32_t* seed_epoch) {
+  pdl_trigger();
+  pdl_wait();
   if (seed_epoch != nullptr) seed += __ldg(seed_epoch);
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = rt1_hash_u32((uint32_t)i, seed) >= thresh ? __float2bfloat16_rn(__bfloat162float(in[i]) * ks) : __float2bfloat16_rn(0.f);
 }
 RT1_API int rt1_dropout_apply(const void* in, void* out, long long n, float p, unsigned seed, cudaStream_t stream) {
-  dropout_apply_kernel<<<rt1_cdiv(n, 256), 256, 0, stream>>>((const bf16*)in, (bf16*)out, n, rt1_drop_threshold(p), 1.f / (1.f - p), seed, rt1_seed_epoch_ptr());
+  rt1_launch(dropout_apply_kernel, rt1_cdiv(n, 256), 256, 0, stream, (const bf16*)in, (bf16*)out, n, rt1_drop_threshold(p), 1.f / (1.f - p), seed, rt1_seed_epoch_ptr());
   return rt1_check_launch("rt1_dropout_apply");
 }

@@ -155,6 +155,8 @@ __global__ void __launch_bounds__(TC_THREADS) attn_tc_fwd_kernel(const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *sm.tmem_slot;
+  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
+  pdl_wait();      // the previous kernel's writes are visible from here on
   const uint32_t t_s = tmem, t_o = tmem + 128;
 
   if (tid == 0) {
@@ -262,6 +264,8 @@ __global__ void __launch_bounds__(TC_THREADS) attn_tc_bwd_kernel(const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *sm.tmem_slot;
+  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
+  pdl_wait();      // the previous kernel's writes are visible from here on
   const uint32_t t_s = tmem, t_dp = tmem + 128, t_dv = tmem + 256, t_dq = tmem + 384, t_dk = tmem;   // dK reuses the S columns
 
   if (tid == 0) {
@@ -423,7 +427,7 @@ int rt1_attention_tc_fwd(const void* qkv, const unsigned char* mask, void* out, 
   if (rc) return rc;
   const size_t smem = tc_smem_bytes(DK, p.SP, false);
   if ((rc = rt1_ensure_dyn_smem((const void*)attn_tc_fwd_kernel, smem))) return rc;
-  attn_tc_fwd_kernel<<<dim3(H, B), TC_THREADS, smem, stream>>>(mq, mkv, p);
+  rt1_launch(attn_tc_fwd_kernel, dim3(H, B), TC_THREADS, smem, stream, mq, mkv, p);
   return rt1_check_launch("rt1_attention_fwd(tcgen05)");
 }
 
@@ -444,6 +448,6 @@ int rt1_attention_tc_bwd(const void* qkv, const unsigned char* mask, const void*
   if (rc) return rc;
   const size_t smem = tc_smem_bytes(DK, p.SP, true);
   if ((rc = rt1_ensure_dyn_smem((const void*)attn_tc_bwd_kernel, smem))) return rc;
-  attn_tc_bwd_kernel<<<dim3(H, B), TC_THREADS, smem, stream>>>(mq, mkv, mgo, p);
+  rt1_launch(attn_tc_bwd_kernel, dim3(H, B), TC_THREADS, smem, stream, mq, mkv, mgo, p);
   return rt1_check_launch("rt1_attention_bwd(tcgen05)");
 }

@@ -10,6 +10,8 @@ template <int VPL>
 __global__ void __launch_bounds__(256) ce_fwd_kernel(const bf16* __restrict__ logits, const long long* __restrict__ labels,
                                                      float* __restrict__ row_ce, float* __restrict__ row_lse,
                                                      long long* __restrict__ pred, int nrows, int V) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= nrows) return;
   const bf16x8* lr = reinterpret_cast<const bf16x8*>(logits + (size_t)row * V);
@@ -58,6 +60,8 @@ __global__ void __launch_bounds__(256) ce_fwd_kernel(const bf16* __restrict__ lo
 }
 
 __global__ void ce_fold_kernel(const float* __restrict__ row_ce, float* __restrict__ loss, int R, int A, float inv) {
+  pdl_trigger();
+  pdl_wait();
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R) return;
   float s = 0.f;
@@ -69,6 +73,8 @@ template <int VPL>
 __global__ void __launch_bounds__(256) ce_bwd_kernel(const bf16* __restrict__ logits, const long long* __restrict__ labels,
                                                      const float* __restrict__ row_lse, const float* __restrict__ dloss,
                                                      bf16* __restrict__ dlogits, int nrows, int A, int V, float inv) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= nrows) return;
   const float scale = dloss[row / A] * inv, lse = row_lse[row];
@@ -94,14 +100,14 @@ RT1_API int rt1_action_ce_fwd(const void* logits, const long long* labels, float
   RT1_REQUIRE(V % 256 == 0 && V <= 1024, "rt1_action_ce_fwd: V=%d must be a multiple of 256 and <= 1024", V);
   const int nrows = R * A, wpb = 8, grid = rt1_cdiv(nrows, wpb);
   switch (V / 256) {
-    case 1: ce_fwd_kernel<1><<<grid, wpb * 32, 0, stream>>>((const bf16*)logits, labels, row_ce, row_lse, pred, nrows, V); break;
-    case 2: ce_fwd_kernel<2><<<grid, wpb * 32, 0, stream>>>((const bf16*)logits, labels, row_ce, row_lse, pred, nrows, V); break;
-    case 4: ce_fwd_kernel<4><<<grid, wpb * 32, 0, stream>>>((const bf16*)logits, labels, row_ce, row_lse, pred, nrows, V); break;
+    case 1: rt1_launch(ce_fwd_kernel<1>, grid, wpb * 32, 0, stream, (const bf16*)logits, labels, row_ce, row_lse, pred, nrows, V); break;
+    case 2: rt1_launch(ce_fwd_kernel<2>, grid, wpb * 32, 0, stream, (const bf16*)logits, labels, row_ce, row_lse, pred, nrows, V); break;
+    case 4: rt1_launch(ce_fwd_kernel<4>, grid, wpb * 32, 0, stream, (const bf16*)logits, labels, row_ce, row_lse, pred, nrows, V); break;
     default: RT1_REQUIRE(false, "rt1_action_ce_fwd: unsupported V=%d", V);
   }
   int rc = rt1_check_launch("rt1_action_ce_fwd");
   if (rc) return rc;
-  ce_fold_kernel<<<rt1_cdiv(R, 128), 128, 0, stream>>>(row_ce, loss, R, A, 1.f / ((float)A * num_items));
+  rt1_launch(ce_fold_kernel, rt1_cdiv(R, 128), 128, 0, stream, row_ce, loss, R, A, 1.f / ((float)A * num_items));
   return rt1_check_launch("rt1_action_ce_fold");
 }
 
@@ -111,9 +117,9 @@ RT1_API int rt1_action_ce_bwd(const void* logits, const long long* labels, const
   const int nrows = R * A, wpb = 8, grid = rt1_cdiv(nrows, wpb);
   const float inv = 1.f / ((float)A * num_items);
   switch (V / 256) {
-    case 1: ce_bwd_kernel<1><<<grid, wpb * 32, 0, stream>>>((const bf16*)logits, labels, row_lse, dloss, (bf16*)dlogits, nrows, A, V, inv); break;
-    case 2: ce_bwd_kernel<2><<<grid, wpb * 32, 0, stream>>>((const bf16*)logits, labels, row_lse, dloss, (bf16*)dlogits, nrows, A, V, inv); break;
-    case 4: ce_bwd_kernel<4><<<grid, wpb * 32, 0, stream>>>((const bf16*)logits, labels, row_lse, dloss, (bf16*)dlogits, nrows, A, V, inv); break;
+    case 1: rt1_launch(ce_bwd_kernel<1>, grid, wpb * 32, 0, stream, (const bf16*)logits, labels, row_lse, dloss, (bf16*)dlogits, nrows, A, V, inv); break;
+    case 2: rt1_launch(ce_bwd_kernel<2>, grid, wpb * 32, 0, stream, (const bf16*)logits, labels, row_lse, dloss, (bf16*)dlogits, nrows, A, V, inv); break;
+    case 4: rt1_launch(ce_bwd_kernel<4>, grid, wpb * 32, 0, stream, (const bf16*)logits, labels, row_lse, dloss, (bf16*)dlogits, nrows, A, V, inv); break;
     default: RT1_REQUIRE(false, "rt1_action_ce_bwd: unsupported V=%d", V);
   }
   return rt1_check_launch("rt1_action_ce_bwd");

@@ -20,6 +20,7 @@
 //     gradient keeps its K*K accumulators in registers across all items of a chunk.
 #include "cnn_common.cuh"
 #include "sm100.cuh"
+#include "bn_tail.cuh"
 
 using namespace sm100;
 
@@ -89,6 +90,8 @@ struct DwParams {
   int tiles_x, tiles_y, cw, cww;
   int items, per_cta;
   int src_bytes, aux_bytes, src_region, aux_region;
+  int has_tail;            // forward: the CTA that lands the last statistics finalises the BatchNorm (bn_tail.cuh)
+  Rt1BnTail tail;
 };
 
 constexpr int DW_THREADS = 256;
@@ -100,7 +103,7 @@ dw_tile_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constan
   constexpr int PX = G::PX, PY = G::PY, QX = G::QX, QY = G::QY, SX = G::SX, TX = G::TX, TY = G::TY;
   extern __shared__ __align__(128) uint8_t dw_dyn[];
   __shared__ __align__(8) uint64_t full_bar[2];
-  __shared__ float red[8 * 32 * 2 * (MODE == DW_WGRAD ? K : 2)];
+  __shared__ __align__(16) float red[8 * 32 * 2 * (MODE == DW_WGRAD ? K : 2)];   // read back as float4
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int posx = warp % G::POSX, posy = warp / G::POSX;
@@ -118,6 +121,8 @@ dw_tile_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constan
     if (p.aux_bytes) tma_prefetch_desc(&aux_map);
   }
   __syncthreads();
+  pdl_trigger();
+  pdl_wait();   // barriers are initialised; nothing above touched global memory
 
   auto issue = [&](int it, int stage) {
     const int tx = it % p.tiles_x;
@@ -337,10 +342,16 @@ dw_tile_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constan
     }
   }
   flush();
+  if (MODE == DW_FWD && p.has_tail) {   // every CTA of the grid has items
+    __shared__ unsigned s_last;
+    bn_tail_run(p.tail, p.s1, p.s2, p.C, gridDim.x, &s_last);
+  }
 }
 
 // scratch [K*K][C] fp32 → weight gradient [C][K*K] bf16
 __global__ void dw_wgrad_cast_kernel(const float* __restrict__ scratch, bf16* __restrict__ dw, int C, int KK) {
+  pdl_trigger();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= C * KK) return;
   const int c = i / KK, t = i % KK;
@@ -350,7 +361,7 @@ __global__ void dw_wgrad_cast_kernel(const float* __restrict__ scratch, bf16* __
 template <int K, int S, int MODE, int CWW>
 int launch_dw_inst(const CUtensorMap& src_map, const CUtensorMap& aux_map, const DwParams& p, size_t smem, int grid, cudaStream_t stream) {
   if (int rc = rt1_ensure_dyn_smem((const void*)dw_tile_kernel<K, S, MODE, CWW>, 200 * 1024)) return rc;
-  dw_tile_kernel<K, S, MODE, CWW><<<grid, DW_THREADS, smem, stream>>>(src_map, aux_map, p);
+  rt1_launch(dw_tile_kernel<K, S, MODE, CWW>, grid, DW_THREADS, smem, stream, src_map, aux_map, p);
   return 0;
 }
 
@@ -427,6 +438,19 @@ RT1_API int rt1_dwconv_fwd(const void* x, const float* a_in, const float* b_in, 
   DW_DISPATCH(DW_FWD, x, nullptr, p, stream, "rt1_dwconv_fwd");
 }
 
+// rt1_dwconv_fwd whose last-arriving CTA also finalises the BatchNorm of the output (scale/shift, mean/rstd, running stats)
+RT1_API int rt1_dwconv_fwd_bn(const void* x, const float* a_in, const float* b_in, const void* w, void* y, float* sum, float* sumsq,
+                              const Rt1BnTail* tail, int N, int H, int W, int C, int k, int stride, cudaStream_t stream) {
+  RT1_REQUIRE(sum != nullptr && sumsq != nullptr && tail != nullptr && tail->ticket != nullptr,
+              "rt1_dwconv_fwd_bn: statistics buffers, tail and ticket are required");
+  const int pad = (k - 1) / 2, Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+  DwParams p = {};
+  p.w = (const bf16*)w; p.dst = (bf16*)y; p.a_in = a_in; p.b_in = b_in; p.s1 = sum; p.s2 = sumsq;
+  p.N = N; p.C = C; p.SH = H; p.SW = W; p.DH = Ho; p.DW = Wo;
+  p.has_tail = 1; p.tail = *tail;
+  DW_DISPATCH(DW_FWD, x, nullptr, p, stream, "rt1_dwconv_fwd_bn");
+}
+
 // dout [N,Ho,Wo,C]; x_raw [N,H,W,C] + a_in/b_in/mean/rstd (or all null when the conv input was not BN+SiLU);
 // din [N,H,W,C]: d/d(x_raw-normalised pre-activation) "dh" when BN is present, else d/d(input);
 // sums fp32 [2,C] (caller-zeroed) receives sum dh and sum dh*xhat (BN case).
@@ -448,7 +472,7 @@ RT1_API int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in,
   RT1_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)k * k * C, stream));
   int rc = dw_wgrad_impl(dout, x, a_in, b_in, scratch, N, H, W, C, k, stride, stream);
   if (rc) return rc;
-  dw_wgrad_cast_kernel<<<rt1_cdiv((long)C * k * k, 256), 256, 0, stream>>>(scratch, (bf16*)dw, C, k * k);
+  rt1_launch(dw_wgrad_cast_kernel, rt1_cdiv((long)C * k * k, 256), 256, 0, stream, scratch, (bf16*)dw, C, k * k);
   return rt1_check_launch("rt1_dwconv_wgrad(cast)");
 }
 
@@ -459,6 +483,8 @@ RT1_API int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in,
 // (round 1) ran at ~7 % of DRAM bandwidth.
 __global__ void __launch_bounds__(256) stem_im2col_kernel(const bf16* __restrict__ x, bf16* __restrict__ cols, int H, int W, int Ho,
                                                           int Wo, long total) {
+  pdl_trigger();
+  pdl_wait();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int ox = (int)(i % Wo), oy = (int)((i / Wo) % Ho);
@@ -489,6 +515,6 @@ __global__ void __launch_bounds__(256) stem_im2col_kernel(const bf16* __restrict
 RT1_API int rt1_stem_im2col(const void* x, void* cols, int N, int H, int W, cudaStream_t stream) {
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const long total = (long)N * Ho * Wo;
-  stem_im2col_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>((const bf16*)x, (bf16*)cols, H, W, Ho, Wo, total);
+  rt1_launch(stem_im2col_kernel, rt1_cdiv(total, 256), 256, 0, stream, (const bf16*)x, (bf16*)cols, H, W, Ho, Wo, total);
   return rt1_check_launch("rt1_stem_im2col");
 }

@@ -18,6 +18,8 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
                                    const bf16* __restrict__ gamma, const bf16* __restrict__ beta, float* __restrict__ running_mean,
                                    float* __restrict__ running_var, float momentum, float eps, int training, float* __restrict__ a,
                                    float* __restrict__ b, float* __restrict__ mean_out, float* __restrict__ rstd_out, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float mean, var;
@@ -44,7 +46,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
 RT1_API int rt1_bn_finalize(const float* sum, const float* sumsq, float count, const void* gamma, const void* beta,
                             float* running_mean, float* running_var, float momentum, float eps, int training, float* a, float* b,
                             float* mean, float* rstd, int C, cudaStream_t stream) {
-  bn_finalize_kernel<<<rt1_cdiv(C, 128), 128, 0, stream>>>(sum, sumsq, count, (const bf16*)gamma, (const bf16*)beta, running_mean,
+  rt1_launch(bn_finalize_kernel, rt1_cdiv(C, 128), 128, 0, stream, sum, sumsq, count, (const bf16*)gamma, (const bf16*)beta, running_mean,
                                                           running_var, momentum, eps, training, a, b, mean, rstd, C);
   return rt1_check_launch("rt1_bn_finalize");
 }
@@ -53,6 +55,8 @@ RT1_API int rt1_bn_finalize(const float* sum, const float* sumsq, float count, c
 __global__ void __launch_bounds__(CNN_THREADS) bn_act_pool_kernel(const bf16* __restrict__ x, const float* __restrict__ a,
                                                                   const float* __restrict__ b, float* __restrict__ pooled, int HW,
                                                                   int C) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -79,7 +83,7 @@ RT1_API int rt1_bn_act_pool(const void* x, const float* a, const float* b, float
                             cudaStream_t stream) {
   RT1_REQUIRE(C % 8 == 0, "rt1_bn_act_pool: C=%d must be a multiple of 8", C);
   dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
-  bn_act_pool_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)x, a, b, pooled, HW, C);
+  rt1_launch(bn_act_pool_kernel, grid, CNN_THREADS, 0, stream, (const bf16*)x, a, b, pooled, HW, C);
   return rt1_check_launch("rt1_bn_act_pool");
 }
 
@@ -88,6 +92,8 @@ RT1_API int rt1_bn_act_pool(const void* x, const float* a, const float* b, float
 __global__ void __launch_bounds__(CNN_THREADS) bn_act_scale_kernel(const bf16* __restrict__ x, const float* __restrict__ a,
                                                                    const float* __restrict__ b, const float* __restrict__ s,
                                                                    bf16* __restrict__ y, int HW, int C, int silu) {
+  pdl_trigger();
+  pdl_wait();
   const ChanMap m = make_chan_map(C / 8);
   if (!m.active) return;
   const int n = blockIdx.y;
@@ -117,7 +123,7 @@ RT1_API int rt1_bn_act_scale(const void* x, const float* a, const float* b, cons
                              cudaStream_t stream) {
   RT1_REQUIRE(C % 8 == 0, "rt1_bn_act_scale: C=%d must be a multiple of 8", C);
   dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
-  bn_act_scale_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)x, a, b, s, (bf16*)y, HW, C, silu);
+  rt1_launch(bn_act_scale_kernel, grid, CNN_THREADS, 0, stream, (const bf16*)x, a, b, s, (bf16*)y, HW, C, silu);
   return rt1_check_launch("rt1_bn_act_scale");
 }
 
@@ -129,6 +135,8 @@ __global__ void __launch_bounds__(CNN_THREADS) block_finalize_kernel(const bf16*
                                                                      const float* __restrict__ b, const bf16* __restrict__ skip,
                                                                      const float* __restrict__ sd, const bf16* __restrict__ gb,
                                                                      long gb_stride, long gb_off, bf16* __restrict__ out, int HW, int C) {
+  pdl_trigger();
+  pdl_wait();
   const ChanMap m = make_chan_map(C / 8);
   if (!m.active) return;
   const int n = blockIdx.y;
@@ -175,7 +183,7 @@ RT1_API int rt1_block_finalize(const void* y, const float* a, const float* b, co
                                long long gb_stride, long long gb_off, void* out, int N, int HW, int C, cudaStream_t stream) {
   RT1_REQUIRE(C % 8 == 0, "rt1_block_finalize: C=%d must be a multiple of 8", C);
   dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
-  block_finalize_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)y, a, b, (const bf16*)skip, sd, (const bf16*)gb, gb_stride,
+  rt1_launch(block_finalize_kernel, grid, CNN_THREADS, 0, stream, (const bf16*)y, a, b, (const bf16*)skip, sd, (const bf16*)gb, gb_stride,
                                                           gb_off, (bf16*)out, HW, C);
   return rt1_check_launch("rt1_block_finalize");
 }
@@ -187,6 +195,8 @@ __global__ void __launch_bounds__(CNN_THREADS) block_finalize_bwd_reduce_kernel(
                                                                                 const bf16* __restrict__ skip, const float* __restrict__ mean,
                                                                                 const float* __restrict__ rstd, float* __restrict__ S, int HW,
                                                                                 int C, int N) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -234,6 +244,8 @@ __global__ void __launch_bounds__(256) block_finalize_bwd_combine_kernel(const f
                                                   const bf16* __restrict__ beta3, bf16* __restrict__ dgb, bf16* __restrict__ dgamma3,
                                                   bf16* __restrict__ dbeta3, float* __restrict__ c1, float* __restrict__ c2, int N, int C,
                                                   float inv_count) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sdb[8][33], sdg[8][33];
   const int tx = threadIdx.x, ny = threadIdx.y;
   const int c = blockIdx.x * 32 + tx;
@@ -280,6 +292,8 @@ __global__ void __launch_bounds__(CNN_THREADS) block_finalize_bwd_apply_kernel(c
                                                                                const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                                const float* __restrict__ c1, const float* __restrict__ c2,
                                                                                bf16* __restrict__ dy, bf16* __restrict__ dskip, int HW, int C) {
+  pdl_trigger();
+  pdl_wait();
   const ChanMap m = make_chan_map(C / 8);
   if (!m.active) return;
   const int n = blockIdx.y;
@@ -329,16 +343,16 @@ RT1_API int rt1_block_finalize_bwd(const void* dout, const void* y, const void* 
   RT1_REQUIRE(C % 8 == 0, "rt1_block_finalize_bwd: C=%d must be a multiple of 8", C);
   RT1_CHECK_CUDA(cudaMemsetAsync(S, 0, sizeof(float) * 3 * (size_t)N * C, stream));
   dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
-  block_finalize_bwd_reduce_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)dout, (const bf16*)y, (const bf16*)skip, mean, rstd, S,
+  rt1_launch(block_finalize_bwd_reduce_kernel, grid, CNN_THREADS, 0, stream, (const bf16*)dout, (const bf16*)y, (const bf16*)skip, mean, rstd, S,
                                                                      HW, C, N);
   int rc = rt1_check_launch("rt1_block_finalize_bwd(reduce)");
   if (rc) return rc;
-  block_finalize_bwd_combine_kernel<<<rt1_cdiv(C, 32), dim3(32, 8), 0, stream>>>(S, (const bf16*)gb, gb_stride, gb_off, sd, (const bf16*)gamma3,
+  rt1_launch(block_finalize_bwd_combine_kernel, rt1_cdiv(C, 32), dim3(32, 8), 0, stream, S, (const bf16*)gb, gb_stride, gb_off, sd, (const bf16*)gamma3,
                                                                          (const bf16*)beta3, (bf16*)dgb, (bf16*)dgamma3, (bf16*)dbeta3, c1,
                                                                          c2, N, C, 1.f / ((float)N * HW));
   rc = rt1_check_launch("rt1_block_finalize_bwd(combine)");
   if (rc) return rc;
-  block_finalize_bwd_apply_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)dout, (const bf16*)y, (const bf16*)gb, gb_stride, gb_off, sd,
+  rt1_launch(block_finalize_bwd_apply_kernel, grid, CNN_THREADS, 0, stream, (const bf16*)dout, (const bf16*)y, (const bf16*)gb, gb_stride, gb_off, sd,
                                                                     a, mean, rstd, c1, c2, (bf16*)dy, (bf16*)dskip, HW, C);
   return rt1_check_launch("rt1_block_finalize_bwd(apply)");
 }
@@ -348,6 +362,8 @@ RT1_API int rt1_block_finalize_bwd(const void* dout, const void* y, const void* 
 __global__ void __launch_bounds__(CNN_THREADS) se_scale_bwd_reduce_kernel(const bf16* __restrict__ g, const bf16* __restrict__ x,
                                                                           const float* __restrict__ a, const float* __restrict__ b,
                                                                           float* __restrict__ ds, int HW, int C) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -375,7 +391,7 @@ RT1_API int rt1_se_scale_bwd_reduce(const void* g, const void* x, const float* a
   RT1_REQUIRE(C % 8 == 0, "rt1_se_scale_bwd_reduce: C=%d must be a multiple of 8", C);
   RT1_CHECK_CUDA(cudaMemsetAsync(ds, 0, sizeof(float) * (size_t)N * C, stream));
   dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
-  se_scale_bwd_reduce_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)g, (const bf16*)x, a, b, ds, HW, C);
+  rt1_launch(se_scale_bwd_reduce_kernel, grid, CNN_THREADS, 0, stream, (const bf16*)g, (const bf16*)x, a, b, ds, HW, C);
   return rt1_check_launch("rt1_se_scale_bwd_reduce");
 }
 
@@ -391,6 +407,8 @@ __global__ void __launch_bounds__(CNN_THREADS) se_bn_bwd_reduce_kernel(const bf1
                                                                        const float* __restrict__ a, const float* __restrict__ b,
                                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                        float* __restrict__ out, int N, int HW, int C) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -449,61 +467,30 @@ __global__ void __launch_bounds__(CNN_THREADS) se_bn_bwd_reduce_kernel(const bf1
   cta_channel_reduce_atomic(m, a4, sm, out + 4 * plane + row);
 }
 
-// sums[0,c] = sum_n s A1 + dpool A2 ; sums[1,c] = sum_n s A3 + dpool A4   (block (32 channels, 8 frame lanes))
-__global__ void __launch_bounds__(256) bn_sums_from_parts_kernel(const float* __restrict__ parts, const float* __restrict__ s,
-                                                                 const float* __restrict__ dpool, float* __restrict__ sums, int N, int C) {
-  __shared__ float p1[8][33], p2[8][33];
-  const int tx = threadIdx.x, ny = threadIdx.y, c = blockIdx.x * 32 + tx;
-  const size_t plane = (size_t)N * C;
-  float s1 = 0.f, s2 = 0.f;
-  if (c < C)
-    for (int n = ny; n < N; n += 8) {
-      const size_t i = (size_t)n * C + c;
-      const float sv = s[i], dp = dpool[i];
-      s1 += sv * parts[plane + i] + dp * parts[2 * plane + i];
-      s2 += sv * parts[3 * plane + i] + dp * parts[4 * plane + i];
-    }
-  p1[ny][tx] = s1;
-  p2[ny][tx] = s2;
-  __syncthreads();
-  if (ny == 0 && c < C) {
-    s1 = s2 = 0.f;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      s1 += p1[k][tx];
-      s2 += p2[k][tx];
-    }
-    sums[c] = s1;
-    sums[C + c] = s2;
-  }
-}
-
 RT1_API int rt1_se_bn_bwd_reduce(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
                                  float* out5, int N, int HW, int C, cudaStream_t stream) {
   RT1_REQUIRE(C % 8 == 0, "rt1_se_bn_bwd_reduce: C=%d must be a multiple of 8", C);
   RT1_CHECK_CUDA(cudaMemsetAsync(out5, 0, sizeof(float) * 5 * (size_t)N * C, stream));
   dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
-  se_bn_bwd_reduce_kernel<<<grid, CNN_THREADS, 0, stream>>>((const bf16*)g, (const bf16*)x, a, b, mean, rstd, out5, N, HW, C);
+  rt1_launch(se_bn_bwd_reduce_kernel, grid, CNN_THREADS, 0, stream, (const bf16*)g, (const bf16*)x, a, b, mean, rstd, out5, N, HW, C);
   return rt1_check_launch("rt1_se_bn_bwd_reduce");
-}
-
-// parts = out5 of rt1_se_bn_bwd_reduce; s, dpool fp32 [N,C]; sums fp32 [2,C] (overwritten) → pass to rt1_bn_act_bwd with sums_ready = 1
-RT1_API int rt1_bn_sums_from_parts(const float* parts, const float* s, const float* dpool, float* sums, int N, int C,
-                                   cudaStream_t stream) {
-  bn_sums_from_parts_kernel<<<rt1_cdiv(C, 32), dim3(32, 8), 0, stream>>>(parts, s, dpool, sums, N, C);
-  return rt1_check_launch("rt1_bn_sums_from_parts");
 }
 
 // ---------------------------------------------------------------- backward of  t = act(BN(x)) [* s + pooled grad]
 // dT = G * s[n,c] + dpool[n,c];  dh = silu ? dT * SiLU'(a*x+b) : dT;  xhat = (x - mean) * rstd
-// reduce: sums[0, c] += dh, sums[1, c] += dh * xhat          apply: dX = a * (dh - c1 - xhat * c2)
+// reduce: sums[0, c] += dh, sums[1, c] += dh * xhat
+// apply:  dX = a * (dh - c1 - xhat * c2) with c1 = sums[0,c] / M, c2 = sums[1,c] / M taken from the sums by every thread
+//         (two loads per channel — a launch of its own for this used to sit between the two passes of all 54 BatchNorm
+//         backwards of a step); the CTAs of frame 0 / row range 0 also write dbeta = sums[0], dgamma = sums[1].
 template <bool APPLY>
-__global__ void __launch_bounds__(CNN_THREADS) bn_act_bwd_kernel(const bf16* __restrict__ g, const bf16* __restrict__ x,
+__global__ void __launch_bounds__(CNN_THREADS, APPLY ? 3 : 2) bn_act_bwd_kernel(const bf16* __restrict__ g, const bf16* __restrict__ x,
                                                                  const float* __restrict__ a, const float* __restrict__ b,
                                                                  const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                  const float* __restrict__ s, const float* __restrict__ dpool,
-                                                                 const float* __restrict__ c1, const float* __restrict__ c2,
-                                                                 float* __restrict__ sums, bf16* __restrict__ dx, int HW, int C, int silu) {
+                                                                 float* __restrict__ sums, float inv_count, bf16* __restrict__ dgamma,
+                                                                 bf16* __restrict__ dbeta, bf16* __restrict__ dx, int HW, int C, int silu) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[APPLY ? 1 : CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -523,8 +510,20 @@ __global__ void __launch_bounds__(CNN_THREADS) bn_act_bwd_kernel(const bf16* __r
     if (s != nullptr) load8f(s + (size_t)n * C + m.cv * 8, fs);
     if (dpool != nullptr) load8f(dpool + (size_t)n * C + m.cv * 8, dp);
     if (APPLY) {
-      load8f(c1 + m.cv * 8, k1);
-      load8f(c2 + m.cv * 8, k2);
+      load8f(sums + m.cv * 8, k1);
+      load8f(sums + C + m.cv * 8, k2);
+      if (blockIdx.x == 0 && n == 0 && m.r0 == 0) {
+        store8bf(dbeta + m.cv * 8, k1);
+        store8bf(dgamma + m.cv * 8, k2);
+      }
+      // dX = a (dh - c1 - xhat c2) = a dh + P x + Q with P = -a rstd c2, Q = -a c1 - P mean: two constants per channel
+      // instead of four (mean, rstd, c1, c2) keeps the thread under 100 registers
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float pk = -fa[k] * rs[k] * k2[k] * inv_count;
+        k2[k] = -fa[k] * k1[k] * inv_count - pk * mu[k];     // Q
+        k1[k] = pk;                                          // P
+      }
     }
     const size_t off = ((size_t)n * HW) * C + (size_t)m.cv * 8;
     // two rows per trip: four 16-byte loads are in flight before the first one is consumed
@@ -548,11 +547,10 @@ __global__ void __launch_bounds__(CNN_THREADS) bn_act_bwd_kernel(const bf16* __r
         for (int k = 0; k < 8; ++k) {
           const float dT = fmaf(gg[k], fs[k], dp[k]);
           const float dh = silu ? dT * silu_grad_f(fmaf(fa[k], f[k], fb[k])) : dT;
-          const float xh = (f[k] - mu[k]) * rs[k];
-          if (APPLY) o[k] = fa[k] * (dh - k1[k] - xh * k2[k]);
+          if (APPLY) o[k] = fmaf(fa[k], dh, fmaf(k1[k], f[k], k2[k]));
           else {
             acc1[k] += dh;
-            acc2[k] += dh * xh;
+            acc2[k] += dh * (f[k] - mu[k]) * rs[k];
           }
         }
         if (APPLY) store8bf(dx + off + (size_t)(h ? r2 : r) * C, o);
@@ -565,38 +563,23 @@ __global__ void __launch_bounds__(CNN_THREADS) bn_act_bwd_kernel(const bf16* __r
   }
 }
 
-// sums → BN parameter gradients (bf16) and the constants c1 = sum_dh / M, c2 = sum_dh_xhat / M
-__global__ void bn_bwd_combine_kernel(const float* __restrict__ sums, float inv_count, bf16* __restrict__ dgamma, bf16* __restrict__ dbeta,
-                                      float* __restrict__ c1, float* __restrict__ c2, int C) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  const float s1 = sums[c], s2 = sums[C + c];
-  dbeta[c] = __float2bfloat16_rn(s1);
-  dgamma[c] = __float2bfloat16_rn(s2);
-  c1[c] = s1 * inv_count;
-  c2[c] = s2 * inv_count;
-}
-
-// Full backward of t = act(BN(x)) * s (+ pooled-gradient term): reduce → combine → apply.
-//   sums: fp32 [2, C] scratch.  If `sums_ready` the reduce pass is skipped (the producer — e.g. the depthwise
-//   backward-data kernel — already accumulated sums for the given `g`).
+// Full backward of t = act(BN(x)) * s (+ pooled-gradient term): reduce → apply (which also emits dgamma / dbeta).
+//   sums: fp32 [2, C].  If `sums_ready` the reduce pass is skipped: the producer — the depthwise backward-data kernel, or
+//   rt1_se_bwd_b for a squeeze-excite block — already accumulated the sums for the given `g`.
 RT1_API int rt1_bn_act_bwd(const void* g, const void* x, const float* a, const float* b, const float* mean, const float* rstd,
-                           const float* s, const float* dpool, float* sums, int sums_ready, float* c1, float* c2, void* dgamma,
-                           void* dbeta, void* dx, int N, int HW, int C, int silu, cudaStream_t stream) {
+                           const float* s, const float* dpool, float* sums, int sums_ready, void* dgamma, void* dbeta, void* dx,
+                           int N, int HW, int C, int silu, cudaStream_t stream) {
   RT1_REQUIRE(C % 8 == 0, "rt1_bn_act_bwd: C=%d must be a multiple of 8", C);
+  RT1_REQUIRE((((uintptr_t)dgamma | (uintptr_t)dbeta) & 15) == 0, "rt1_bn_act_bwd: dgamma / dbeta must be 16-byte aligned");
   dim3 grid(cnn_ctas_per_frame(N, HW, C), N, cnn_chan_chunks(C));
-  int rc;
+  const float inv_count = 1.f / ((float)N * HW);
   if (!sums_ready) {
     RT1_CHECK_CUDA(cudaMemsetAsync(sums, 0, sizeof(float) * 2 * (size_t)C, stream));
-    bn_act_bwd_kernel<false><<<grid, CNN_THREADS, 0, stream>>>((const bf16*)g, (const bf16*)x, a, b, mean, rstd, s, dpool, nullptr, nullptr,
-                                                               sums, nullptr, HW, C, silu);
-    rc = rt1_check_launch("rt1_bn_act_bwd(reduce)");
-    if (rc) return rc;
+    rt1_launch(bn_act_bwd_kernel<false>, grid, CNN_THREADS, 0, stream, (const bf16*)g, (const bf16*)x, a, b, mean, rstd, s, dpool, sums, inv_count,
+                                                               nullptr, nullptr, nullptr, HW, C, silu);
+    if (int rc = rt1_check_launch("rt1_bn_act_bwd(reduce)")) return rc;
   }
-  bn_bwd_combine_kernel<<<rt1_cdiv(C, 128), 128, 0, stream>>>(sums, 1.f / ((float)N * HW), (bf16*)dgamma, (bf16*)dbeta, c1, c2, C);
-  rc = rt1_check_launch("rt1_bn_act_bwd(combine)");
-  if (rc) return rc;
-  bn_act_bwd_kernel<true><<<grid, CNN_THREADS, 0, stream>>>((const bf16*)g, (const bf16*)x, a, b, mean, rstd, s, dpool, c1, c2, nullptr,
-                                                            (bf16*)dx, HW, C, silu);
+  rt1_launch(bn_act_bwd_kernel<true>, grid, CNN_THREADS, 0, stream, (const bf16*)g, (const bf16*)x, a, b, mean, rstd, s, dpool, sums, inv_count,
+                                                            (bf16*)dgamma, (bf16*)dbeta, (bf16*)dx, HW, C, silu);
   return rt1_check_launch("rt1_bn_act_bwd(apply)");
 }

@@ -38,6 +38,35 @@ typedef __nv_bfloat162 bf162;
 
 static inline int rt1_cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 
+// ---- programmatic dependent launch -------------------------------------------------------------------------
+// A training step is ~900 kernels of 5-50 us in ONE dependency chain: between two of them the GPU drains, the next grid is
+// launched, its CTAs are placed and run their prologue (barrier init, TMEM allocation, index math) before the first byte
+// moves — a few microseconds each time, a tenth of the step in total.  Every kernel of this library is therefore launched
+// with programmatic stream serialization: its CTAs may be placed while the previous kernel of the stream is still finishing,
+// run whatever does not touch global memory, and block in pdl_wait() until the previous grid has completed and its writes
+// are visible.  pdl_wait() precedes EVERY global access of a kernel (reads, and writes too: the allocator may hand a buffer
+// the predecessor still reads to its successor as output).  pdl_trigger() lets the NEXT kernel's CTAs be placed as soon as
+// all CTAs of this one are running.  Both are no-ops for a kernel launched without the attribute; stream capture records the
+// launches as programmatic graph edges.  RT1B200_PDL=0 launches everything fully serialised (A/B baseline).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool rt1_pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+static inline void rt1_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = rt1_pdl_enabled() ? 1 : 0;
+  (void)cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);   // the status is collected by rt1_check_launch()
+}
+
 // ---- device helpers -------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -19,6 +19,7 @@
 #include <stdlib.h>
 
 #include "sm100.cuh"
+#include "bn_tail.cuh"
 
 using namespace sm100;
 
@@ -43,6 +44,8 @@ struct GemmParams {
   float* col_sum;
   float* col_sumsq;
   int b_resident;        // persistent kernel: all B tiles stay in shared memory (small weights, huge M)
+  int has_tail;          // persistent kernel: the CTA that lands the last statistics finalises the BatchNorm (bn_tail.cuh)
+  Rt1BnTail tail;
   int dbg;               // bench-only switches (RT1B200_GEMM_DBG): 1 no copy-out, 2 no statistics, 4 no TMEM drain/staging, 8 no A loads, 16 no B loads
 };
 
@@ -97,6 +100,8 @@ __global__ void __launch_bounds__(128, 8) gemm_tcgen05_kernel(const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
+  pdl_wait();      // the previous kernel's writes are visible from here on
 
   if (num_kb > 0) {
     if (warp == 0 && lane == 0) {
@@ -375,6 +380,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
+  pdl_wait();      // the previous kernel's writes are visible from here on
 
   if (warp == 0) {
     if (lane == 0) {
@@ -596,6 +603,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
     }
   }
   if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+  if (n_stats > 0 && p.has_tail) bn_tail_run(p.tail, p.col_sum, p.col_sumsq, p.N, gridDim.x, tmem_slot + 1);   // spare word next to the TMEM slot
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -620,8 +628,11 @@ static long v2_min_tiles() {
 // bf16-output GEMMs: persistent kernel, one CTA per SM, TMA-store epilogue
 static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, const void* B, long long ldb, void* out,
                                   long long ldo, const void* bias, const void* residual, long long ldr, float alpha,
-                                  float dropout_p, unsigned seed, float* col_sum, float* col_sumsq, cudaStream_t stream) {
+                                  float dropout_p, unsigned seed, float* col_sum, float* col_sumsq, cudaStream_t stream,
+                                  const Rt1BnTail* tail = nullptr) {
   const int M = p.M, N = p.N, K = p.K;
+  p.has_tail = tail != nullptr ? 1 : 0;
+  if (tail != nullptr) p.tail = *tail;
   const int bn = N <= 128 ? ((N + 15) / 16) * 16 : 128;
   p.block_n = bn;
   p.kb_per_split = (K + BLOCK_K - 1) / BLOCK_K;
@@ -662,8 +673,8 @@ static int launch_gemm_persistent(GemmParams& p, const void* A, long long lda, c
   const long tiles = (long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn);
   const int grid = (int)(tiles < sm_count ? tiles : sm_count);
   const bool plain = alpha == 1.f && bias == nullptr && residual == nullptr && dropout_p <= 0.f;
-  if (plain) gemm_tcgen05_persistent_kernel<true><<<grid, V2_THREADS, smem, stream>>>(ta, tb, to, p);
-  else gemm_tcgen05_persistent_kernel<false><<<grid, V2_THREADS, smem, stream>>>(ta, tb, to, p);
+  if (plain) rt1_launch(gemm_tcgen05_persistent_kernel<true>, grid, V2_THREADS, smem, stream, ta, tb, to, p);
+  else rt1_launch(gemm_tcgen05_persistent_kernel<false>, grid, V2_THREADS, smem, stream, ta, tb, to, p);
   return rt1_check_launch("rt1_gemm_bf16(persistent)");
 }
 
@@ -717,7 +728,7 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   p.out = out; p.ldo = ldo; p.out_fp32 = out_fp32; p.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
   p.bias = (const bf16*)bias; p.residual = (const bf16*)residual; p.ldr = ldr;
   p.alpha = alpha; p.dropout_p = dropout_p; p.seed = seed; p.seed_epoch = dropout_p > 0.f ? rt1_seed_epoch_ptr() : nullptr;
-  p.col_sum = col_sum; p.col_sumsq = col_sumsq; p.dbg = 0; p.b_resident = 0;
+  p.col_sum = col_sum; p.col_sumsq = col_sumsq; p.dbg = 0; p.b_resident = 0; p.has_tail = 0;
 
   CUtensorMap ta, tb;
   int rc;
@@ -731,12 +742,34 @@ RT1_API int rt1_gemm_bf16(const void* A, long long lda, int a_mn, const void* B,
   const size_t smem = (size_t)stages * stage_bytes + (2 * stages + 2) * 8 + 1024;
   if ((rc = rt1_ensure_dyn_smem((const void*)gemm_tcgen05_kernel, smem))) return rc;
   dim3 grid(((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn), 1, splits);
-  gemm_tcgen05_kernel<<<grid, 128, smem, stream>>>(ta, tb, p);
+  rt1_launch(gemm_tcgen05_kernel, grid, 128, smem, stream, ta, tb, p);
   return rt1_check_launch("rt1_gemm_bf16");
+}
+
+// bf16-output GEMM whose epilogue takes the BatchNorm statistics of the result AND finalises them (see bn_tail.cuh): every
+// 1x1 convolution of the image tokenizer in training mode.  Shapes the persistent kernel does not take (unaligned output)
+// fall back to the plain call followed by the finalize launch.
+RT1_API int rt1_gemm_bf16_bn(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out, long long ldo,
+                             int M, int N, int K, float* col_sum, float* col_sumsq, const Rt1BnTail* tail, cudaStream_t stream) {
+  RT1_REQUIRE(M > 0 && N > 0 && K > 0, "rt1_gemm_bf16_bn: empty problem %dx%dx%d", M, N, K);
+  RT1_REQUIRE(col_sum != nullptr && col_sumsq != nullptr && tail != nullptr && tail->ticket != nullptr,
+              "rt1_gemm_bf16_bn: statistics buffers, tail and ticket are required");
+  if (((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0 && gemm_v2_enabled()) {
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn;
+    return launch_gemm_persistent(p, A, lda, B, ldb, out, ldo, nullptr, nullptr, 0, 1.f, 0.f, 0u, col_sum, col_sumsq, stream, tail);
+  }
+  int rc = rt1_gemm_bf16(A, lda, a_mn, B, ldb, b_mn, out, ldo, 0, M, N, K, nullptr, nullptr, 0, 1.f, 0.f, 0u, 1, 0, col_sum, col_sumsq,
+                         stream);
+  if (rc) return rc;
+  return rt1_bn_finalize(col_sum, col_sumsq, tail->count, tail->gamma, tail->beta, tail->running_mean, tail->running_var,
+                         tail->momentum, tail->eps, 1, tail->a, tail->b, tail->mean, tail->rstd, N, stream);
 }
 
 // column sums of a bf16 [M, N] matrix → bf16 [N] (bias gradients)
 __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, long ld, int M, int N, bf16* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[8][33];
   const int col = blockIdx.x * 32 + (threadIdx.x & 31), r0 = threadIdx.x >> 5;
   float s = 0.f;
@@ -752,16 +785,18 @@ __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x,
   }
 }
 RT1_API int rt1_colsum_bf16(const void* x, long long ld, int M, int N, void* out, cudaStream_t stream) {
-  colsum_kernel<<<rt1_cdiv(N, 32), 256, 0, stream>>>((const bf16*)x, ld, M, N, (bf16*)out);
+  rt1_launch(colsum_kernel, rt1_cdiv(N, 32), 256, 0, stream, (const bf16*)x, ld, M, N, (bf16*)out);
   return rt1_check_launch("rt1_colsum_bf16");
 }
 
 // fp32 → bf16 cast of a small buffer (split-K weight-gradient workspace → gradient slot)
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long n) {
+  pdl_trigger();
+  pdl_wait();
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = __float2bfloat16_rn(in[i]);
 }
 RT1_API int rt1_cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t stream) {
-  cast_f32_bf16_kernel<<<rt1_cdiv(n, 256), 256, 0, stream>>>(in, (bf16*)out, n);
+  rt1_launch(cast_f32_bf16_kernel, rt1_cdiv(n, 256), 256, 0, stream, in, (bf16*)out, n);
   return rt1_check_launch("rt1_cast_f32_bf16");
 }

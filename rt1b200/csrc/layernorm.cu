@@ -14,6 +14,8 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const bf16* __restrict__ x,
                                                      const bf16* __restrict__ b, bf16* __restrict__ y,
                                                      float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
                                                      int D, float eps) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   const int row = blockIdx.x * wpb + warp;
   if (row >= rows) return;
@@ -55,6 +57,8 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x,
                                                      const bf16* __restrict__ dy, const float* __restrict__ mean_in,
                                                      const float* __restrict__ rstd_in, bf16* __restrict__ dx,
                                                      float* __restrict__ partial, int rows, int D) {
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float sm[];  // [2][D] per-CTA dgamma / dbeta partials
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) sm[i] = 0.f;
@@ -111,6 +115,8 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x,
 
 __global__ void ln_param_grad_kernel(const float* __restrict__ partial, int nblk, int D, bf16* __restrict__ dw,
                                      bf16* __restrict__ db) {
+  pdl_trigger();
+  pdl_wait();
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
   if (col >= D) return;
   float a = 0.f, c = 0.f;
@@ -126,7 +132,7 @@ RT1_API int rt1_layernorm_fwd(const void* x, const void* w, const void* b, void*
                               int D, float eps, cudaStream_t stream) {
   RT1_REQUIRE(D % 256 == 0 && D <= 2048, "rt1_layernorm_fwd: D=%d must be a multiple of 256 and <= 2048", D);
   const int wpb = 8, grid = rt1_cdiv(rows, wpb);
-#define LN_F(V) ln_fwd_kernel<V><<<grid, wpb * 32, 0, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)b, (bf16*)y, mean, rstd, rows, D, eps)
+#define LN_F(V) rt1_launch(ln_fwd_kernel<V>, grid, wpb * 32, 0, stream, (const bf16*)x, (const bf16*)w, (const bf16*)b, (bf16*)y, mean, rstd, rows, D, eps)
   switch (D / 256) {
     case 1: LN_F(1); break;
     case 2: LN_F(2); break;
@@ -151,7 +157,7 @@ RT1_API int rt1_layernorm_bwd(const void* x, const void* w, const void* dy, cons
   int grid = rt1_cdiv(rows, 8);
   if (grid > 148) grid = 148;
   const size_t smem = 2 * (size_t)D * sizeof(float);
-#define LN_B(V) ln_bwd_kernel<V><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D)
+#define LN_B(V) rt1_launch(ln_bwd_kernel<V>, grid, 256, smem, stream, (const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D)
   switch (D / 256) {
     case 1: LN_B(1); break;
     case 2: LN_B(2); break;
@@ -162,7 +168,7 @@ RT1_API int rt1_layernorm_bwd(const void* x, const void* w, const void* dy, cons
 #undef LN_B
   int rc = rt1_check_launch("rt1_layernorm_bwd");
   if (rc) return rc;
-  ln_param_grad_kernel<<<rt1_cdiv(D, 128), 128, 0, stream>>>(scratch, grid, D, (bf16*)dw, (bf16*)db);
+  rt1_launch(ln_param_grad_kernel, rt1_cdiv(D, 128), 128, 0, stream, scratch, grid, D, (bf16*)dw, (bf16*)db);
   return rt1_check_launch("rt1_layernorm_param_grad");
 }
 
@@ -241,13 +247,13 @@ RT1_API int rt1_layernorm_bwd_noalloc(const void* x, const void* w, const void* 
   if (rc) return rc;
   const size_t smem = 2 * (size_t)D * sizeof(float);
   switch (D / 256) {
-    case 1: ln_bwd_kernel<1><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
-    case 2: ln_bwd_kernel<2><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
-    case 4: ln_bwd_kernel<4><<<grid, 256, smem, stream>>>((const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
+    case 1: rt1_launch(ln_bwd_kernel<1>, grid, 256, smem, stream, (const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
+    case 2: rt1_launch(ln_bwd_kernel<2>, grid, 256, smem, stream, (const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
+    case 4: rt1_launch(ln_bwd_kernel<4>, grid, 256, smem, stream, (const bf16*)x, (const bf16*)w, (const bf16*)dy, mean, rstd, (bf16*)dx, scratch, rows, D); break;
     default: RT1_REQUIRE(false, "rt1_layernorm_bwd_noalloc: unsupported D=%d (supported: 256, 512, 1024)", D);
   }
   rc = rt1_check_launch("rt1_layernorm_bwd_noalloc");
   if (rc) return rc;
-  ln_param_grad_kernel<<<rt1_cdiv(D, 128), 128, 0, stream>>>(scratch, grid, D, (bf16*)dw, (bf16*)db);
+  rt1_launch(ln_param_grad_kernel, rt1_cdiv(D, 128), 128, 0, stream, scratch, grid, D, (bf16*)dw, (bf16*)db);
   return rt1_check_launch("rt1_layernorm_bwd_noalloc(param_grad)");
 }

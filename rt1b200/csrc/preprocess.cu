@@ -9,6 +9,8 @@
 template <typename T>
 __global__ void __launch_bounds__(256) preprocess_kernel(const T* __restrict__ in, bf16* __restrict__ out, int N, int H, int W,
                                                          int off_y, int off_x, const int* __restrict__ shift_dev, float scale) {
+  pdl_trigger();
+  pdl_wait();
   if (shift_dev != nullptr) {   // offset sampled on the device (graph-captured steps): (dh, dw) added to (-pad_h, -pad_w)
     off_y += __ldg(shift_dev);
     off_x += __ldg(shift_dev + 1);
@@ -36,9 +38,9 @@ static int preprocess_launch(const void* in, int in_is_uint8, void* out, int N, 
   const long total = (long)N * H * W;
   const int grid = rt1_cdiv(total, 256);
   if (in_is_uint8)
-    preprocess_kernel<uint8_t><<<grid, 256, 0, stream>>>((const uint8_t*)in, (bf16*)out, N, H, W, off_y, off_x, shift_dev, 1.f / 255.f);
+    rt1_launch(preprocess_kernel<uint8_t>, grid, 256, 0, stream, (const uint8_t*)in, (bf16*)out, N, H, W, off_y, off_x, shift_dev, 1.f / 255.f);
   else
-    preprocess_kernel<float><<<grid, 256, 0, stream>>>((const float*)in, (bf16*)out, N, H, W, off_y, off_x, shift_dev, 1.f);
+    rt1_launch(preprocess_kernel<float>, grid, 256, 0, stream, (const float*)in, (bf16*)out, N, H, W, off_y, off_x, shift_dev, 1.f);
   return rt1_check_launch("rt1_preprocess_nhwc");
 }
 

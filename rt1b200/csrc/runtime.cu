@@ -57,6 +57,15 @@ int rt1_ensure_dyn_smem(const void* kernel, size_t bytes) {
   return 0;
 }
 
+bool rt1_pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("RT1B200_PDL");
+    on = (e == nullptr || e[0] != '0') ? 1 : 0;
+  }
+  return on == 1;
+}
+
 int rt1_sm_count() {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return 148;

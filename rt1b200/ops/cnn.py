@@ -2,13 +2,14 @@
 
 Entry point: :func:`film_efficientnet_forward` — called by ``EfficientNetEncoder.forward_nhwc`` with bf16
 NHWC frames.  It walks the parameter containers in ``rt1b200.models.film_efficientnet`` and runs each stage
-through the NHWC kernels in ``rt1b200.ops.kernels`` (K2–K8 of SURVEY §2.6):
+through the NHWC kernels of ``rt1b200.ops.kernels_cnn`` (K2–K8 of SURVEY §2.6):
 
-  stem      : 3x3 s2 conv + BN(batch stats) + SiLU
-  MBConv    : [expand 1x1 GEMM + BN-stat epilogue] → [BN+SiLU folded into the depthwise load, BN-stat
-              epilogue] → [BN+SiLU + SE pool] → [SE FCs] → [project GEMM with BN+SiLU+SE-scale prologue]
-              → [BN + stochastic depth + residual + FiLM affine]
+  stem      : im2col + tcgen05 GEMM (BN statistics + their finalisation in the epilogue) → BN + SiLU pass
+  MBConv    : [expand 1x1 GEMM + BN1 statistics/tail] → [depthwise tile kernel: SiLU(BN1(.)) applied to the shared-memory
+              tile, BN2 statistics/tail] → [BN2+SiLU + SE pool] → [SE FCs] → [BN2+SiLU+SE-scale pass] → [project GEMM +
+              BN3 statistics/tail] → [BN3 + stochastic depth + residual + FiLM affine]
   head      : 1x1 384→1536 + BN + SiLU → 1x1 1536→512 → FiLM
+(the schedule itself, forward and backward, is ``rt1b200/ops/kernels_cnn.py``)
 
 ``film_efficientnet_forward_torch`` is the same network on stock channels-last PyTorch ops (cuDNN / cuBLAS bf16).  It is
 NOT a product path: it exists as the library baseline of ``bench.py --cnn cudnn`` and as the bisecting arm of the tests

@@ -55,11 +55,10 @@ def rt1_attention(qkv, mask, p_drop: float = 0.0, seed: Optional[int] = None):
 class _TokenLearner(Function):
     """TokenLearner as LayerNorm kernel → tcgen05 GEMM (C → 64, all frames at once) → per-frame pooling kernel; the
     backward mirrors it (pooling backward → two GEMMs for dLN(x) and dW1 → LayerNorm backward → direct pooling term).
-    ``RT1B200_TL_FUSED=1`` selects the older one-CTA-per-frame kernels instead."""
+    Envelope of the pooling kernels: C a multiple of 64, at most 8 learned tokens, at most 512 positions per frame."""
 
     @staticmethod
     def forward(ctx, feats, ln_w, ln_b, w1, b1, w2, b2, eps, params):
-        import os
         from .kernels import gemm
         n, P, C = feats.shape
         T = w2.shape[0]
@@ -68,14 +67,10 @@ class _TokenLearner(Function):
         w2m = w2.reshape(T, -1)
         assert w1m.shape == (64, C) and w2m.shape == (T, 64), "TokenLearner kernel expects a 64-wide bottleneck"
         tokens = torch.empty(n, T, C, dtype=BF16, device=feats.device)
-        fused = os.environ.get("RT1B200_TL_FUSED", "0") == "1" or C % 64 != 0 or P > 128 or T > 8
-        ctx.fused = fused
+        if C % 64 != 0 or P > 512 or T > 8:
+            raise ValueError(f"TokenLearner kernels support C % 64 == 0, <= 8 tokens and <= 512 positions per frame; got C={C}, "
+                             f"T={T}, P={P}")
         ctx.meta = (eps, params)
-        if fused:
-            call("rt1_token_learner_fwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(tokens),
-                 i64(T * C), i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
-            ctx.save_for_backward(feats, ln_w, ln_b, w1m, b1, w2m, b2)
-            return tokens
         rows = n * P
         x2 = feats.view(rows, C)
         xn = torch.empty_like(x2)
@@ -96,18 +91,6 @@ class _TokenLearner(Function):
         eps, params = ctx.meta
         dtok = dtok if dtok.is_contiguous() else dtok.contiguous()
         g = [_grad_slot(p) for p in params]     # order: ln_w, ln_b, w1, b1, w2, b2
-        if ctx.fused:
-            feats, ln_w, ln_b, w1m, b1, w2m, b2 = ctx.saved_tensors
-            n, P, C = feats.shape
-            T = w2m.shape[0]
-            dfeats = torch.empty_like(feats)
-            ns = 64 * C + 64 + T * 64 + T + 2 * C
-            scratch = torch.empty(ns, dtype=torch.float32, device=feats.device)
-            call("rt1_token_learner_bwd", ptr(feats), ptr(ln_w), ptr(ln_b), ptr(w1m), ptr(b1), ptr(w2m), ptr(b2), ptr(dtok),
-                 i64(T * C), ptr(dfeats), ptr(scratch), ptr(g[0]), ptr(g[1]), ptr(g[2]), ptr(g[3]), ptr(g[4]), ptr(g[5]),
-                 i32(n), i32(P), i32(C), i32(T), f32(eps), stream())
-            _ready(params)
-            return (dfeats,) + (None,) * 8
         from .kernels_cnn import _wgrad_gemm
         feats, ln_w, w1m, w2m, xn, mean, rstd, hpre, wmap = ctx.saved_tensors
         n, P, C = feats.shape

@@ -65,21 +65,55 @@ def _empty(*shape, device, dtype=BF16):
     return torch.empty(*shape, dtype=dtype, device=device)
 
 
+class BnTail(ctypes.Structure):
+    """``Rt1BnTail`` of include/rt1b200.h: what the statistics-producing kernel needs to finalise the BatchNorm itself."""
+    _fields_ = [("gamma", ctypes.c_void_p), ("beta", ctypes.c_void_p), ("running_mean", ctypes.c_void_p),
+                ("running_var", ctypes.c_void_p), ("a", ctypes.c_void_p), ("b", ctypes.c_void_p), ("mean", ctypes.c_void_p),
+                ("rstd", ctypes.c_void_p), ("ticket", ctypes.c_void_p), ("count", ctypes.c_float), ("momentum", ctypes.c_float),
+                ("eps", ctypes.c_float)]
+
+
+# BatchNorm finalisation by the last CTA of the producing kernel (1) or by a launch of its own (0, the A/B baseline)
+_BN_TAIL = os.environ.get("RT1B200_BN_TAIL", "1") != "0"
+
+
 class _BN:
     """Per-layer BatchNorm state of one forward pass: batch statistics → scale/shift, kept for the backward."""
-    __slots__ = ("mod", "a", "b", "mean", "rstd", "sum", "sumsq")
+    __slots__ = ("mod", "a", "b", "mean", "rstd", "sum", "sumsq", "ticket")
 
     def __init__(self, mod, device):
         C = mod.num_features
         self.mod = mod
-        buf = _zeros(6, C, device=device)
-        self.sum, self.sumsq, self.a, self.b, self.mean, self.rstd = buf.unbind(0)
+        buf = _zeros(6 * C + 16, device=device)                  # the arena hands out zeros: sums and ticket start at 0
+        self.sum, self.sumsq, self.a, self.b, self.mean, self.rstd = buf[:6 * C].view(6, C).unbind(0)
+        self.ticket = buf[6 * C:]
+
+    def tail(self, count: int):
+        """By-reference argument for the ``*_bn`` entry points (training mode only), or None when tails are switched off."""
+        if not _BN_TAIL:
+            return None
+        m = self.mod
+        t = BnTail(m.weight.data_ptr(), m.bias.data_ptr(), m.running_mean.data_ptr(), m.running_var.data_ptr(), self.a.data_ptr(),
+                   self.b.data_ptr(), self.mean.data_ptr(), self.rstd.data_ptr(), self.ticket.data_ptr(), float(count),
+                   float(m.momentum if m.momentum is not None else 0.1), float(m.eps))
+        return t
 
     def finalize(self, count: int, training: bool):
         m = self.mod
         call("rt1_bn_finalize", ptr(self.sum), ptr(self.sumsq), f32(count), ptr(m.weight), ptr(m.bias), ptr(m.running_mean),
              ptr(m.running_var), f32(m.momentum if m.momentum is not None else 0.1), f32(m.eps), i32(training), ptr(self.a),
              ptr(self.b), ptr(self.mean), ptr(self.rstd), i32(m.num_features), stream())
+
+
+def _conv_bn(x2d, w2d, out2d, M, N, K, bn: "_BN", training: bool):
+    """1x1 convolution whose epilogue takes the BatchNorm statistics of its output and (training) finalises them."""
+    tail = bn.tail(M) if training else None
+    if tail is not None:
+        call("rt1_gemm_bf16_bn", ptr(x2d), i64(x2d.stride(0)), i32(0), ptr(w2d), i64(w2d.stride(0)), i32(0), ptr(out2d),
+             i64(out2d.stride(0)), i32(M), i32(N), i32(K), ptr(bn.sum), ptr(bn.sumsq), ctypes.byref(tail), stream())
+    else:
+        gemm(x2d, w2d, out2d, M, N, K, col_sum=bn.sum if training else None, col_sumsq=bn.sumsq if training else None)
+        bn.finalize(M, training)
 
 
 def _conv_w2d(conv) -> torch.Tensor:
@@ -153,11 +187,9 @@ class _EncoderFn(Function):
         stem_cols = _empty(N * Ho * Wo, 32, device=dev)
         call("rt1_stem_im2col", ptr(x8), ptr(stem_cols), i32(N), i32(H), i32(W), stream())
         w32 = torch.nn.functional.pad(conv0.weight.detach().view(C0, 27), (0, 5))
-        gemm(stem_cols, w32, stem_raw.view(N * Ho * Wo, C0), N * Ho * Wo, C0, 32,
-             col_sum=bn0.sum if training else None, col_sumsq=bn0.sumsq if training else None)
+        _conv_bn(stem_cols, w32, stem_raw.view(N * Ho * Wo, C0), N * Ho * Wo, C0, 32, bn0, training)
         if not training:
             stem_cols = None
-        bn0.finalize(N * Ho * Wo, training)
         x = _empty(N, Ho, Wo, C0, device=dev)
         call("rt1_bn_act_scale", ptr(stem_raw), ptr(bn0.a), ptr(bn0.b), ptr(None), ptr(x), i32(N), i32(Ho * Wo), i32(C0), i32(1),
              stream())
@@ -175,9 +207,7 @@ class _EncoderFn(Function):
             if blk.expand is not None:
                 e_raw = _empty(N, Hc, Wc, Ce, device=dev)
                 bn1 = _BN(blk.expand[1], dev)
-                gemm(x.view(M, Cin), _conv_w2d(blk.expand[0]), e_raw.view(M, Ce), M, Ce, Cin,
-                     col_sum=bn1.sum if training else None, col_sumsq=bn1.sumsq if training else None)
-                bn1.finalize(M, training)
+                _conv_bn(x.view(M, Cin), _conv_w2d(blk.expand[0]), e_raw.view(M, Ce), M, Ce, Cin, bn1, training)
                 if _DW_ACT_ON_LOAD:
                     # SiLU(BN1(.)) is applied to the depthwise kernel's shared-memory tile (once per element and CTA):
                     # the activated expand tensor never exists in HBM
@@ -196,10 +226,15 @@ class _EncoderFn(Function):
             HWo, Mo = Ho * Wo, N * Ho * Wo
             d_raw = _empty(N, Ho, Wo, Ce, device=dev)
             bn2 = _BN(blk.depthwise[1], dev)
-            call("rt1_dwconv_fwd", ptr(dw_in), ptr(a_in), ptr(b_in), ptr(blk.depthwise[0].weight), ptr(d_raw),
-                 ptr(bn2.sum if training else None), ptr(bn2.sumsq if training else None), i32(N), i32(Hc), i32(Wc), i32(Ce),
-                 i32(k), i32(s), stream())
-            bn2.finalize(Mo, training)
+            tail2 = bn2.tail(Mo) if training else None
+            if tail2 is not None:
+                call("rt1_dwconv_fwd_bn", ptr(dw_in), ptr(a_in), ptr(b_in), ptr(blk.depthwise[0].weight), ptr(d_raw), ptr(bn2.sum),
+                     ptr(bn2.sumsq), ctypes.byref(tail2), i32(N), i32(Hc), i32(Wc), i32(Ce), i32(k), i32(s), stream())
+            else:
+                call("rt1_dwconv_fwd", ptr(dw_in), ptr(a_in), ptr(b_in), ptr(blk.depthwise[0].weight), ptr(d_raw),
+                     ptr(bn2.sum if training else None), ptr(bn2.sumsq if training else None), i32(N), i32(Hc), i32(Wc), i32(Ce),
+                     i32(k), i32(s), stream())
+                bn2.finalize(Mo, training)
             se = blk.se
             if se is not None:
                 Cs = se.fc1.out_channels
@@ -215,9 +250,7 @@ class _EncoderFn(Function):
             call("rt1_bn_act_scale", ptr(d_raw), ptr(bn2.a), ptr(bn2.b), ptr(sc), ptr(a2), i32(N), i32(HWo), i32(Ce), i32(1), stream())
             y_raw = _empty(N, Ho, Wo, Co, device=dev)
             bn3 = _BN(blk.project[1], dev)
-            gemm(a2.view(Mo, Ce), _conv_w2d(blk.project[0]), y_raw.view(Mo, Co), Mo, Co, Ce,
-                 col_sum=bn3.sum if training else None, col_sumsq=bn3.sumsq if training else None)
-            bn3.finalize(Mo, training)
+            _conv_bn(a2.view(Mo, Ce), _conv_w2d(blk.project[0]), y_raw.view(Mo, Co), Mo, Co, Ce, bn3, training)
             sd = sd_scales[bi] if (training and blk.has_skip and blk.drop_rate > 0 and sd_scales is not None) else None
             out = _empty(N, Ho, Wo, Co, device=dev)
             call("rt1_block_finalize", ptr(y_raw), ptr(bn3.a), ptr(bn3.b), ptr(x if blk.has_skip else None), ptr(sd),
@@ -235,9 +268,7 @@ class _EncoderFn(Function):
         M = N * Hc * Wc
         h_raw = _empty(M, Ch, device=dev)
         bnh = _BN(bnhm, dev)
-        gemm(x.view(M, Cl), _conv_w2d(convh), h_raw, M, Ch, Cl, col_sum=bnh.sum if training else None,
-             col_sumsq=bnh.sumsq if training else None)
-        bnh.finalize(M, training)
+        _conv_bn(x.view(M, Cl), _conv_w2d(convh), h_raw, M, Ch, Cl, bnh, training)
         t_act = _empty(M, Ch, device=dev)
         call("rt1_bn_act_scale", ptr(h_raw), ptr(bnh.a), ptr(bnh.b), ptr(None), ptr(t_act), i32(N), i32(Hc * Wc), i32(Ch), i32(1),
              stream())
@@ -286,7 +317,7 @@ class _EncoderFn(Function):
         dh_raw = _empty(M, Ch, device=dev)
         bnm = bnh.mod
         call("rt1_bn_act_bwd", ptr(dt), ptr(h_raw), ptr(bnh.a), ptr(bnh.b), ptr(bnh.mean), ptr(bnh.rstd), ptr(None), ptr(None),
-             ptr(sums), i32(0), ptr(c1), ptr(c2), ptr(_grad_slot(bnm.weight)), ptr(_grad_slot(bnm.bias)), ptr(dh_raw), i32(N), i32(HW),
+             ptr(sums), i32(0), ptr(_grad_slot(bnm.weight)), ptr(_grad_slot(bnm.bias)), ptr(dh_raw), i32(N), i32(HW),
              i32(Ch), i32(1), stream())
         convh = net.convNormAct1[0]
         dx = _empty(M, Cl, device=dev)
@@ -334,28 +365,23 @@ class _EncoderFn(Function):
                 call("rt1_se_bn_bwd_reduce", ptr(da2), ptr(st["d_raw"]), ptr(bn2.a), ptr(bn2.b), ptr(bn2.mean), ptr(bn2.rstd),
                      ptr(parts), i32(N), i32(HWo), i32(Ce), stream())
                 ds = parts[0]
-                dz2, dz1 = _empty(N, Ce, device=dev, dtype=F32), _empty(N, Cs, device=dev, dtype=F32)
                 dpool = _empty(N, Ce, device=dev, dtype=F32)
+                sums = _empty(2, Ce, device=dev, dtype=F32)
                 sc = st["s"]
-                call("rt1_se_fc_bwd", ptr(ds), ptr(sc), ptr(st["z1"]), ptr(st["pooled"]), f32(1.0 / HWo), ptr(se.fc1.weight),
-                     ptr(se.fc2.weight), ptr(dz2), ptr(dz1), ptr(dpool), ptr(None), ptr(None), ptr(None), ptr(None),
-                     i32(N), i32(Ce), i32(Cs), stream())
-                z1_, pooled_ = st["z1"], st["pooled"]
+                # FC-pair backward, its four parameter gradients and BN2's backward sums: two launches, a CTA per 32-channel slice
                 se_slots = [_grad_slot(q) for q in (se.fc1.weight, se.fc1.bias, se.fc2.weight, se.fc2.bias)]
-                lane.run(lambda: call("rt1_se_wgrad", ptr(dz2), ptr(dz1), ptr(z1_), ptr(pooled_), f32(1.0 / HWo), ptr(se_slots[0]),
-                                      ptr(se_slots[1]), ptr(se_slots[2]), ptr(se_slots[3]), i32(N), i32(Ce), i32(Cs), stream()),
-                         dz2, dz1, z1_, pooled_)
+                call("rt1_se_bwd", ptr(ds), ptr(sc), ptr(st["z1"]), ptr(st["pooled"]), f32(1.0 / HWo), ptr(se.fc1.weight),
+                     ptr(se.fc2.weight), ptr(parts), ptr(_zeros(N, (Cs + 3) // 4 * 4, device=dev)), ptr(dpool), ptr(sums),
+                     ptr(se_slots[0]), ptr(se_slots[1]), ptr(se_slots[2]), ptr(se_slots[3]), i32(N), i32(Ce), i32(Cs), stream())
                 ready += [se.fc1.weight, se.fc1.bias, se.fc2.weight, se.fc2.bias]
             # BN2 + SiLU (+ SE scale, + pooled gradient)
             b2 = bn2.mod
-            sums = _empty(2, Ce, device=dev, dtype=F32)
             dd_raw = _empty(Mo, Ce, device=dev)
-            sums_ready = 0
-            if se is not None:
-                call("rt1_bn_sums_from_parts", ptr(parts), ptr(sc), ptr(dpool), ptr(sums), i32(N), i32(Ce), stream())
-                sums_ready = 1
+            sums_ready = 1
+            if se is None:
+                sums, sums_ready = _empty(2, Ce, device=dev, dtype=F32), 0
             call("rt1_bn_act_bwd", ptr(da2), ptr(st["d_raw"]), ptr(bn2.a), ptr(bn2.b), ptr(bn2.mean), ptr(bn2.rstd), ptr(sc), ptr(dpool),
-                 ptr(sums), i32(sums_ready), ptr(c1), ptr(c2), ptr(_grad_slot(b2.weight)), ptr(_grad_slot(b2.bias)), ptr(dd_raw), i32(N),
+                 ptr(sums), i32(sums_ready), ptr(_grad_slot(b2.weight)), ptr(_grad_slot(b2.bias)), ptr(dd_raw), i32(N),
                  i32(HWo), i32(Ce), i32(1), stream())
             ready += [b2.weight, b2.bias]
             del da2
@@ -381,7 +407,7 @@ class _EncoderFn(Function):
                 b1 = bn1.mod
                 de_raw = _empty(Mi, Ce, device=dev)
                 call("rt1_bn_act_bwd", ptr(dhe), ptr(st["e_raw"]), ptr(bn1.a), ptr(bn1.b), ptr(bn1.mean), ptr(bn1.rstd), ptr(None),
-                     ptr(None), ptr(sums1), i32(1), ptr(c1), ptr(c2), ptr(_grad_slot(b1.weight)), ptr(_grad_slot(b1.bias)), ptr(de_raw),
+                     ptr(None), ptr(sums1), i32(1), ptr(_grad_slot(b1.weight)), ptr(_grad_slot(b1.bias)), ptr(de_raw),
                      i32(N), i32(Hin * Win), i32(Ce), i32(0), stream())
                 we = blk.expand[0]
                 dxi = _empty(Mi, Cin, device=dev)
@@ -414,7 +440,7 @@ class _EncoderFn(Function):
         sums = _empty(2, C0, device=dev, dtype=F32)
         dstem = torch.empty_like(stem_raw)
         call("rt1_bn_act_bwd", ptr(dout), ptr(stem_raw), ptr(bn0.a), ptr(bn0.b), ptr(bn0.mean), ptr(bn0.rstd), ptr(None), ptr(None),
-             ptr(sums), i32(0), ptr(c1), ptr(c2), ptr(_grad_slot(b0.weight)), ptr(_grad_slot(b0.bias)), ptr(dstem), i32(N), i32(Hs * Ws),
+             ptr(sums), i32(0), ptr(_grad_slot(b0.weight)), ptr(_grad_slot(b0.bias)), ptr(dstem), i32(N), i32(Hs * Ws),
              i32(C0), i32(1), stream())
         conv0 = net.convNormAct0[0]
         Ms = N * Hs * Ws

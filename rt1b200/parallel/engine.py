@@ -9,7 +9,7 @@ Design (B200-first):
   * backend ``p2p``  — gradients live in NVLink-visible symmetric memory; ONE kernel per bucket pulls the peers'
     slices over NVSwitch (two-shot: each rank reduces 1/W of the bucket, applies 1/W scaling + bf16→fp32 +
     AdamW on that shard, then pushes the updated bf16 parameters to every peer).  No NCCL call and no separate
-    optimizer kernel (``rt1b200/csrc/p2p_allreduce_adamw.cu``);
+    optimizer kernel (``rt1b200/csrc/p2p.cu``);
   * backend ``local`` — world size 1: the same fused AdamW kernel without the exchange;
   * backend ``torchdist`` — ``torch.distributed.all_reduce`` (gloo on CPU, NCCL on GPU) + the fused/reference
     update.  This is the plumbing oracle for CPU tests and the "NCCL baseline" arm of the all-reduce sweep.

@@ -170,11 +170,10 @@ def test_bn_act_bwd_with_se_terms(use_se):
     a, b = (gr * rs).detach(), (br - mu * gr * rs).detach()
     dpool = (w_pool / HW) if use_se else None
     sums = torch.empty(2, C, device=DEV)
-    c1, c2 = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
     dgam, dbet = torch.empty(C, dtype=BF, device=DEV), torch.empty(C, dtype=BF, device=DEV)
     dx = torch.empty_like(x)
     call("rt1_bn_act_bwd", ptr(g), ptr(x), ptr(a), ptr(b), ptr(mu.detach()), ptr(rs.detach()), ptr(s), ptr(dpool), ptr(sums), i32(0),
-         ptr(c1), ptr(c2), ptr(dgam), ptr(dbet), ptr(dx), i32(N), i32(HW), i32(C), i32(1), stream())
+         ptr(dgam), ptr(dbet), ptr(dx), i32(N), i32(HW), i32(C), i32(1), stream())
     assert _rel(dx, xr.grad) < 3e-2 and _rel(dgam, gr.grad) < 3e-2 and _rel(dbet, br.grad) < 3e-2
     # forward pieces used by the SE path
     pooled = torch.zeros(N, C, device=DEV)
@@ -189,8 +188,9 @@ def test_bn_act_bwd_with_se_terms(use_se):
         assert _rel(ds, (g.float() * t).sum(1)) < 2e-2
 
 
-def test_se_fc_fwd_bwd():
-    N, C, Cs, HW = 6, 144, 6, 50
+@pytest.mark.parametrize("N,C,Cs,HW", [(6, 144, 6, 50), (48, 2304, 96, 120), (5, 40, 10, 33), (12, 816, 34, 64)])
+def test_se_fc_fwd_bwd(N, C, Cs, HW):
+    """SE FC pair: forward, and the sliced two-launch backward (data + all four parameter gradients + the BN2 sums)."""
     pooled_sum = torch.randn(N, C, device=DEV) * HW * 0.3
     w1, b1, w2, b2 = _bf(Cs, C, scale=0.2, seed=1), _bf(Cs, seed=2), _bf(C, Cs, scale=0.5, seed=3), _bf(C, seed=4)
     z1, s = torch.empty(N, Cs, device=DEV), torch.empty(N, C, device=DEV)
@@ -202,13 +202,82 @@ def test_se_fc_fwd_bwd():
     assert _rel(s, sr) < 1e-3
     ds = torch.randn(N, C, device=DEV)
     sr.backward(ds)
-    dz2, dz1, dpool = torch.empty(N, C, device=DEV), torch.empty(N, Cs, device=DEV), torch.empty(N, C, device=DEV)
+    parts = torch.randn(5, N, C, device=DEV)
+    dpool, sums = torch.empty(N, C, device=DEV), torch.empty(2, C, device=DEV)
+    dhid = torch.zeros(N, (Cs + 3) // 4 * 4, device=DEV)
     G = [torch.empty_like(t) for t in (w1, b1, w2, b2)]
-    call("rt1_se_fc_bwd", ptr(ds), ptr(s), ptr(z1), ptr(pooled_sum), f32(1.0 / HW), ptr(w1), ptr(w2), ptr(dz2), ptr(dz1), ptr(dpool),
-         ptr(G[0]), ptr(G[1]), ptr(G[2]), ptr(G[3]), i32(N), i32(C), i32(Cs), stream())
+    call("rt1_se_bwd", ptr(ds), ptr(s), ptr(z1), ptr(pooled_sum), f32(1.0 / HW), ptr(w1), ptr(w2), ptr(parts), ptr(dhid), ptr(dpool),
+         ptr(sums), ptr(G[0]), ptr(G[1]), ptr(G[2]), ptr(G[3]), i32(N), i32(C), i32(Cs), stream())
     assert _rel(dpool * HW, pr.grad) < 1e-2
     for gk, p in zip(G, P):
         assert _rel(gk, p.grad) < 2e-2
+    dp = pr.grad / HW
+    want = torch.stack([(s * parts[1] + dp * parts[2]).sum(0), (s * parts[3] + dp * parts[4]).sum(0)])
+    assert _rel(sums, want) < 1e-2
+    # without the BatchNorm parts the sums are left alone
+    call("rt1_se_bwd", ptr(ds), ptr(s), ptr(z1), ptr(pooled_sum), f32(1.0 / HW), ptr(w1), ptr(w2), ptr(None), ptr(dhid.zero_()),
+         ptr(dpool), ptr(None), ptr(G[0]), ptr(G[1]), ptr(G[2]), ptr(G[3]), i32(N), i32(C), i32(Cs), stream())
+    assert _rel(dpool * HW, pr.grad) < 1e-2
+
+
+@pytest.mark.parametrize("M,K,C", [(48 * 32 * 57, 48, 288), (4 * 16 * 29, 96, 576), (1000, 24, 144)])
+def test_gemm_with_batchnorm_tail(M, K, C):
+    """The last CTA of the statistics-taking GEMM finalises the BatchNorm: same a/b/mean/rstd/running stats as rt1_bn_finalize."""
+    from rt1b200.ops.kernels import gemm
+    from rt1b200.ops.kernels_cnn import BnTail
+    import ctypes
+    x, w = _bf(M, K, seed=1), _bf(C, K, scale=0.3, seed=2)
+    gamma, beta = _bf(C, seed=3) * 0.2 + 1, _bf(C, seed=4) * 0.2
+    outs = []
+    for use_tail in (False, True):
+        y = torch.empty(M, C, dtype=BF, device=DEV)
+        st = torch.zeros(6, C, device=DEV)
+        rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+        ticket = torch.zeros(4, dtype=torch.int32, device=DEV)
+        if use_tail:
+            t = BnTail(gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(), rv.data_ptr(), st[2].data_ptr(), st[3].data_ptr(),
+                       st[4].data_ptr(), st[5].data_ptr(), ticket.data_ptr(), float(M), 0.1, 1e-5)
+            call("rt1_gemm_bf16_bn", ptr(x), i64(K), i32(0), ptr(w), i64(K), i32(0), ptr(y), i64(C), i32(M), i32(C), i32(K), ptr(st[0]),
+                 ptr(st[1]), ctypes.byref(t), stream())
+            assert int(ticket[0]) > 0
+        else:
+            gemm(x, w, y, M, C, K, col_sum=st[0], col_sumsq=st[1])
+            call("rt1_bn_finalize", ptr(st[0]), ptr(st[1]), f32(M), ptr(gamma), ptr(beta), ptr(rm), ptr(rv), f32(0.1), f32(1e-5), i32(1),
+                 ptr(st[2]), ptr(st[3]), ptr(st[4]), ptr(st[5]), i32(C), stream())
+        outs.append((y, st, rm, rv))
+    (y0, s0, rm0, rv0), (y1, s1, rm1, rv1) = outs
+    assert torch.equal(y0, y1)
+    assert _rel(s1[2:], s0[2:]) < 1e-4 and _rel(rm1, rm0) < 1e-4 and _rel(rv1, rv0) < 1e-4
+    ref = x.float() @ w.float().t()
+    assert _rel(s1[4], ref.mean(0)) < 2e-2 and _rel(s1[5], torch.rsqrt(ref.var(0, unbiased=False) + 1e-5)) < 2e-2
+
+
+def test_dwconv_with_batchnorm_tail():
+    from rt1b200.ops.kernels_cnn import BnTail
+    import ctypes
+    N, H, W, C, k, s = 4, 32, 57, 288, 5, 1
+    x, w = _bf(N, H, W, C, seed=1), _bf(C, k * k, scale=0.2, seed=2)
+    gamma, beta = _bf(C, seed=3) * 0.2 + 1, _bf(C, seed=4) * 0.2
+    outs = []
+    for use_tail in (False, True):
+        y = torch.empty(N, H, W, C, dtype=BF, device=DEV)
+        st = torch.zeros(6, C, device=DEV)
+        rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+        ticket = torch.zeros(4, dtype=torch.int32, device=DEV)
+        if use_tail:
+            t = BnTail(gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(), rv.data_ptr(), st[2].data_ptr(), st[3].data_ptr(),
+                       st[4].data_ptr(), st[5].data_ptr(), ticket.data_ptr(), float(N * H * W), 0.1, 1e-5)
+            call("rt1_dwconv_fwd_bn", ptr(x), ptr(None), ptr(None), ptr(w), ptr(y), ptr(st[0]), ptr(st[1]), ctypes.byref(t), i32(N), i32(H),
+                 i32(W), i32(C), i32(k), i32(s), stream())
+        else:
+            call("rt1_dwconv_fwd", ptr(x), ptr(None), ptr(None), ptr(w), ptr(y), ptr(st[0]), ptr(st[1]), i32(N), i32(H), i32(W), i32(C),
+                 i32(k), i32(s), stream())
+            call("rt1_bn_finalize", ptr(st[0]), ptr(st[1]), f32(N * H * W), ptr(gamma), ptr(beta), ptr(rm), ptr(rv), f32(0.1), f32(1e-5),
+                 i32(1), ptr(st[2]), ptr(st[3]), ptr(st[4]), ptr(st[5]), i32(C), stream())
+        outs.append((y, st, rm, rv))
+    (y0, s0, rm0, rv0), (y1, s1, rm1, rv1) = outs
+    assert torch.equal(y0, y1)
+    assert _rel(s1[2:], s0[2:]) < 1e-4 and _rel(rm1, rm0) < 1e-4 and _rel(rv1, rv0) < 1e-4
 
 
 @pytest.mark.parametrize("training", [True, False])

@@ -86,16 +86,20 @@ def test_bf16_kernel_training_tracks_fp32_reference(reference, monkeypatch):
     assert theirs[-10:].mean() < 0.7 * theirs[:5].mean(), "the reference itself did not learn these batches"
     # identical start (same weights, same batch): bf16 rounding only
     assert abs(ours[0] - theirs[0]) <= 0.02 * theirs[0], (ours[0], theirs[0])
-    # The curves stay together after the first ten steps.  Tolerance: 5 % on 10-step windowed means, widened to twice the
-    # spread the fp32 reference shows against ITSELF when only its initial weights are rounded to bf16 (a 26-block BatchNorm
-    # network at batch 4 x 3 frames, cycling six batches with Adam at 5e-4, amplifies rounding-sized perturbations: windows
-    # moved by 7-13 % between two boxes, either sign, with the whole-run means within 2 %).
+    # The curves stay together while the loss DESCENDS (10-step windowed means, from step 10, while the reference is above 15 % of
+    # its starting loss).  Tolerance: 5 %, widened to twice the spread the fp32 reference shows against ITSELF when only its
+    # initial weights are rounded to bf16.  Once these six batches are fitted (loss down 10x and more) the fp32 model's own two
+    # runs differ by 25 % (measured) — a 26-block BatchNorm network at batch 4 x 3 frames under Adam at 5e-4 amplifies
+    # rounding-sized perturbations — so there only a factor-of-two sanity bound applies.
     windows = [(a, ours[a:a + 10].mean(), theirs[a:a + 10].mean(), theirs_b[a:a + 10].mean()) for a in range(10, STEPS - 5, 5)]
-    spread = max(abs(rb - r) / r for _, _, r, rb in windows)
+    descent = [w for w in windows if w[2] >= 0.15 * theirs[0]]
+    print(f"[convergence] ours/ref per window {[round(float(o / r), 3) for _, o, r, _ in windows]}; "
+          f"fp32'/fp32 {[round(float(rb / r), 3) for _, _, r, rb in windows]}; descent windows {len(descent)}")
+    assert len(descent) >= 2, "the comparison needs at least two windows in the descent phase"
+    spread = max(abs(rb - r) / r for _, _, r, rb in descent)
     tol = max(0.05, 2.0 * spread)
-    print(f"[convergence] fp32-vs-fp32(bf16-rounded init) spread {spread:.3f}; tolerance {tol:.3f}; "
-          f"ours/ref per window {[round(o / r, 3) for _, o, r, _ in windows]}")
-    assert tol <= 0.30, f"the fp32 reference is chaotic on this problem (spread {spread:.3f}): the comparison says nothing"
-    for a, o, r, _ in windows:
+    assert tol <= 0.20, f"the fp32 reference is chaotic already in the descent phase (spread {spread:.3f})"
+    for a, o, r, _ in descent:
         assert abs(o - r) <= tol * r, (a, o, r, tol)
-    assert abs(ours[10:].mean() - theirs[10:].mean()) <= max(0.05, spread) * theirs[10:].mean(), (ours[10:].mean(), theirs[10:].mean())
+    for a, o, r, _ in windows:
+        assert 0.5 * r <= o <= 2.0 * r, (a, o, r)

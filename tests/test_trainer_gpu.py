@@ -8,12 +8,12 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _trainer(seed=0, hw=(64, 96), graph=False, dropout=0.0):
+def _trainer(seed=0, hw=(64, 96), graph=False, dropout=0.0, lr=1e-3):
     from rt1b200.models.factory import RT1Config
     from rt1b200.train.trainer import RT1Module, Trainer
     torch.manual_seed(seed)
     (H, W), T = hw, 3
-    args = Namespace(height=H, width=W, seq_len=T, lr=1e-3, milestones=[], exp_name="t", log_dir="/tmp/rt1_t/logs",
+    args = Namespace(height=H, width=W, seq_len=T, lr=lr, milestones=[], exp_name="t", log_dir="/tmp/rt1_t/logs",
                      ckpt_dir="/tmp/rt1_t/ckpt", log_every_n_steps=10 ** 9, ckpt_every_n_epochs=1, max_epochs=1)
     cfg = RT1Config.language_table(height=H, width=W, seq_len=T, num_layers=2, dropout_rate=dropout)
     return Trainer(RT1Module(args, cfg), args, device=torch.device("cuda", 0), param_dtype=torch.bfloat16, loggers=[], verbose=False,
@@ -27,7 +27,9 @@ def test_graphed_step_matches_eager_schedule(monkeypatch):
     from rt1b200.ops.kernels_cnn import flush_bn_counters
     monkeypatch.setenv("RT1B200_TRAIN_GRAPH_STRICT", "1")
     src = SyntheticBatchSource(2, 3, 64, 96, pool=2, seed=4, image_dtype=torch.uint8, pin=False)
-    a, b, c = _trainer(seed=5, graph=False), _trainer(seed=5, graph=True), _trainer(seed=5, graph=False)
+    # lr 2e-4: at 1e-3 the loss falls 15x in six steps and the last bits of the atomically accumulated statistics are amplified
+    # into 20 % differences between two runs of the SAME schedule
+    a, b, c = (_trainer(seed=5, graph=g, lr=2e-4) for g in (False, True, False))
     for tr in (a, b, c):
         tr.module.model._crop_shift_override = (3, 5)
         for m in tr.module.modules():
@@ -43,7 +45,8 @@ def test_graphed_step_matches_eager_schedule(monkeypatch):
     # Two EAGER runs of this tiny BatchNorm network already drift apart step by step (batch statistics are accumulated with
     # fp32 atomics and six optimizer steps amplify the last bits): that run-to-run noise is the yardstick.
     la, lb, lc = torch.tensor(la), torch.tensor(lb), torch.tensor(lc)
-    tol = torch.maximum(3e-2 * la.abs() + 2e-4, 3.0 * (lc - la).abs())
+    noise = torch.cummax((lc - la).abs(), 0).values                      # the drift only grows with the step count
+    tol = torch.maximum(3e-2 * la.abs() + 2e-4, 3.0 * noise)
     assert bool(((lb - la).abs() <= tol).all()), (la.tolist(), lb.tolist(), lc.tolist())
     for tr in (a, b):
         flush_bn_counters(tr.module.model)
