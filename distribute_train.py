@@ -56,6 +56,10 @@ def build_parser() -> ArgumentParser:
     p.add_argument("--max_steps", type=int, default=None)
     p.add_argument("--backend", choices=["auto", "p2p", "torchdist", "local"], default="auto")
     p.add_argument("--precision", choices=["bf16", "fp32"], default=None)
+    p.add_argument("--broadcast_buffers", action="store_true",
+                   help="re-broadcast rank 0's BatchNorm statistics after every step, like torch DDP's broadcast_buffers=True; "
+                        "without it they are broadcast before every evaluation pass, which gives the same evaluation and "
+                        "checkpoints (no rank reads another rank's running statistics while training)")
     p.add_argument("--cpu_input", dest="gpu_input", action="store_false",
                    help="crop + resize frames in the loader workers with PIL like the reference (default on a GPU: ship raw uint8 "
                         "frames and crop/resize with a kernel)")

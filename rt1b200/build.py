@@ -49,7 +49,10 @@ def build(verbose: bool = False, force: bool = False) -> str:
     nvcc = _nvcc()
     hdr = b"".join(open(os.path.join(CSRC, f), "rb").read() for f in sorted(os.listdir(CSRC))
                    if f.endswith((".cuh", ".h")))
-    hdr += " ".join(NVCC_FLAGS).encode()
+    flags = list(NVCC_FLAGS)
+    if os.environ.get("RT1B200_PDL_MODE"):      # experiment switch: where kernels wait / trigger (see common.cuh)
+        flags.append("-DRT1_PDL_MODE=" + str(int(os.environ["RT1B200_PDL_MODE"])))
+    hdr += " ".join(flags).encode()
     jobs = []
     objs = []
     for src in sources():
@@ -61,7 +64,7 @@ def build(verbose: bool = False, force: bool = False) -> str:
     def compile_one(job):
         src, obj = job
         log = obj[:-2] + ".log"
-        r = subprocess.run([nvcc, *NVCC_FLAGS, "-I", CSRC, "-c", src, "-o", obj], capture_output=True, text=True)
+        r = subprocess.run([nvcc, *flags, "-I", CSRC, "-c", src, "-o", obj], capture_output=True, text=True)
         with open(log, "w") as f:
             f.write(r.stdout + r.stderr)
         if r.returncode != 0:

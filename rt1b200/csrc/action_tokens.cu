@@ -9,8 +9,7 @@
 __global__ void action_tokenize_kernel(const float* __restrict__ vals, const float* __restrict__ low, const float* __restrict__ high,
                                        const uint8_t* __restrict__ discrete, long long* __restrict__ tokens, long total, int A,
                                        float vmax) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int k = (int)(i % A);
@@ -29,8 +28,7 @@ __global__ void action_tokenize_kernel(const float* __restrict__ vals, const flo
 __global__ void action_detokenize_kernel(const long long* __restrict__ tokens, const float* __restrict__ low,
                                          const float* __restrict__ high, const uint8_t* __restrict__ discrete,
                                          float* __restrict__ vals, long total, int A, float vmax) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int k = (int)(i % A);

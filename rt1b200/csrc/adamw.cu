@@ -12,8 +12,7 @@ template <bool GRAD_BF16>
 __global__ void __launch_bounds__(256) adamw_flat_kernel(bf16* __restrict__ p_lp, float* __restrict__ p, void* __restrict__ g_,
                                                          float* __restrict__ m, float* __restrict__ v, long n, AdamHyper h,
                                                          int zero_grad) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const long n8 = n >> 3;
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long stride = (long)gridDim.x * blockDim.x;

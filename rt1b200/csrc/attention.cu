@@ -73,8 +73,7 @@ __device__ __forceinline__ void scores_softmax(const bf16* q, const bf16* k, flo
 
 __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_kernel(const bf16* __restrict__ qkv, const uint8_t* __restrict__ mask,
                                                                bf16* __restrict__ out, AttnDims d) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   extern __shared__ __align__(16) uint8_t smem[];
   const int S = d.S, DK = d.DK, ld = DK + 8, ldp = S + 1;
   bf16* q = reinterpret_cast<bf16*>(smem);
@@ -120,8 +119,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_fwd_kernel(const bf16* __res
 __global__ void __launch_bounds__(ATT_THREADS) attn_bwd_kernel(const bf16* __restrict__ qkv, const uint8_t* __restrict__ mask,
                                                                const bf16* __restrict__ dout, bf16* __restrict__ dqkv,
                                                                AttnDims d) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   extern __shared__ __align__(16) uint8_t smem[];
   const int S = d.S, DK = d.DK, ld = DK + 8, ldp = S + 1;
   bf16* q = reinterpret_cast<bf16*>(smem);
@@ -235,8 +233,7 @@ RT1_API int rt1_attention_bwd(const void* qkv, const unsigned char* mask, const 
 // dropout mask re-application for the backward of a GEMM-epilogue dropout: out = keep ? in/(1-p) : 0
 __global__ void dropout_apply_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, long n, uint32_t thresh, float ks,
                                      uint32_t seed, const uint32_t* seed_epoch) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   if (seed_epoch != nullptr) seed += __ldg(seed_epoch);
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = rt1_hash_u32((uint32_t)i, seed) >= thresh ? __float2bfloat16_rn(__bfloat162float(in[i]) * ks) : __float2bfloat16_rn(0.f);

@@ -155,8 +155,7 @@ __global__ void __launch_bounds__(TC_THREADS) attn_tc_fwd_kernel(const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *sm.tmem_slot;
-  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
-  pdl_wait();      // the previous kernel's writes are visible from here on
+  pdl_enter();
   const uint32_t t_s = tmem, t_o = tmem + 128;
 
   if (tid == 0) {
@@ -264,8 +263,7 @@ __global__ void __launch_bounds__(TC_THREADS) attn_tc_bwd_kernel(const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *sm.tmem_slot;
-  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
-  pdl_wait();      // the previous kernel's writes are visible from here on
+  pdl_enter();
   const uint32_t t_s = tmem, t_dp = tmem + 128, t_dv = tmem + 256, t_dq = tmem + 384, t_dk = tmem;   // dK reuses the S columns
 
   if (tid == 0) {

@@ -10,8 +10,7 @@ template <int VPL>
 __global__ void __launch_bounds__(256) ce_fwd_kernel(const bf16* __restrict__ logits, const long long* __restrict__ labels,
                                                      float* __restrict__ row_ce, float* __restrict__ row_lse,
                                                      long long* __restrict__ pred, int nrows, int V) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const int lane = threadIdx.x & 31, row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= nrows) return;
   const bf16x8* lr = reinterpret_cast<const bf16x8*>(logits + (size_t)row * V);
@@ -60,8 +59,7 @@ __global__ void __launch_bounds__(256) ce_fwd_kernel(const bf16* __restrict__ lo
 }
 
 __global__ void ce_fold_kernel(const float* __restrict__ row_ce, float* __restrict__ loss, int R, int A, float inv) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= R) return;
   float s = 0.f;
@@ -73,8 +71,7 @@ template <int VPL>
 __global__ void __launch_bounds__(256) ce_bwd_kernel(const bf16* __restrict__ logits, const long long* __restrict__ labels,
                                                      const float* __restrict__ row_lse, const float* __restrict__ dloss,
                                                      bf16* __restrict__ dlogits, int nrows, int A, int V, float inv) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const int lane = threadIdx.x & 31, row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= nrows) return;
   const float scale = dloss[row / A] * inv, lse = row_lse[row];

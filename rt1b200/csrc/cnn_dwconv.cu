@@ -121,8 +121,7 @@ dw_tile_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constan
     if (p.aux_bytes) tma_prefetch_desc(&aux_map);
   }
   __syncthreads();
-  pdl_trigger();
-  pdl_wait();   // barriers are initialised; nothing above touched global memory
+  pdl_enter();
 
   auto issue = [&](int it, int stage) {
     const int tx = it % p.tiles_x;
@@ -350,8 +349,7 @@ dw_tile_kernel(const __grid_constant__ CUtensorMap src_map, const __grid_constan
 
 // scratch [K*K][C] fp32 → weight gradient [C][K*K] bf16
 __global__ void dw_wgrad_cast_kernel(const float* __restrict__ scratch, bf16* __restrict__ dw, int C, int KK) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= C * KK) return;
   const int c = i / KK, t = i % KK;
@@ -483,8 +481,7 @@ RT1_API int rt1_dwconv_wgrad(const void* dout, const void* x, const float* a_in,
 // (round 1) ran at ~7 % of DRAM bandwidth.
 __global__ void __launch_bounds__(256) stem_im2col_kernel(const bf16* __restrict__ x, bf16* __restrict__ cols, int H, int W, int Ho,
                                                           int Wo, long total) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int ox = (int)(i % Wo), oy = (int)((i / Wo) % Ho);

@@ -18,8 +18,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
                                    const bf16* __restrict__ gamma, const bf16* __restrict__ beta, float* __restrict__ running_mean,
                                    float* __restrict__ running_var, float momentum, float eps, int training, float* __restrict__ a,
                                    float* __restrict__ b, float* __restrict__ mean_out, float* __restrict__ rstd_out, int C) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float mean, var;
@@ -55,8 +54,7 @@ RT1_API int rt1_bn_finalize(const float* sum, const float* sumsq, float count, c
 __global__ void __launch_bounds__(CNN_THREADS) bn_act_pool_kernel(const bf16* __restrict__ x, const float* __restrict__ a,
                                                                   const float* __restrict__ b, float* __restrict__ pooled, int HW,
                                                                   int C) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -92,8 +90,7 @@ RT1_API int rt1_bn_act_pool(const void* x, const float* a, const float* b, float
 __global__ void __launch_bounds__(CNN_THREADS) bn_act_scale_kernel(const bf16* __restrict__ x, const float* __restrict__ a,
                                                                    const float* __restrict__ b, const float* __restrict__ s,
                                                                    bf16* __restrict__ y, int HW, int C, int silu) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const ChanMap m = make_chan_map(C / 8);
   if (!m.active) return;
   const int n = blockIdx.y;
@@ -135,8 +132,7 @@ __global__ void __launch_bounds__(CNN_THREADS) block_finalize_kernel(const bf16*
                                                                      const float* __restrict__ b, const bf16* __restrict__ skip,
                                                                      const float* __restrict__ sd, const bf16* __restrict__ gb,
                                                                      long gb_stride, long gb_off, bf16* __restrict__ out, int HW, int C) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const ChanMap m = make_chan_map(C / 8);
   if (!m.active) return;
   const int n = blockIdx.y;
@@ -195,8 +191,7 @@ __global__ void __launch_bounds__(CNN_THREADS) block_finalize_bwd_reduce_kernel(
                                                                                 const bf16* __restrict__ skip, const float* __restrict__ mean,
                                                                                 const float* __restrict__ rstd, float* __restrict__ S, int HW,
                                                                                 int C, int N) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -244,8 +239,7 @@ __global__ void __launch_bounds__(256) block_finalize_bwd_combine_kernel(const f
                                                   const bf16* __restrict__ beta3, bf16* __restrict__ dgb, bf16* __restrict__ dgamma3,
                                                   bf16* __restrict__ dbeta3, float* __restrict__ c1, float* __restrict__ c2, int N, int C,
                                                   float inv_count) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float sdb[8][33], sdg[8][33];
   const int tx = threadIdx.x, ny = threadIdx.y;
   const int c = blockIdx.x * 32 + tx;
@@ -292,8 +286,7 @@ __global__ void __launch_bounds__(CNN_THREADS) block_finalize_bwd_apply_kernel(c
                                                                                const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                                const float* __restrict__ c1, const float* __restrict__ c2,
                                                                                bf16* __restrict__ dy, bf16* __restrict__ dskip, int HW, int C) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const ChanMap m = make_chan_map(C / 8);
   if (!m.active) return;
   const int n = blockIdx.y;
@@ -362,8 +355,7 @@ RT1_API int rt1_block_finalize_bwd(const void* dout, const void* y, const void* 
 __global__ void __launch_bounds__(CNN_THREADS) se_scale_bwd_reduce_kernel(const bf16* __restrict__ g, const bf16* __restrict__ x,
                                                                           const float* __restrict__ a, const float* __restrict__ b,
                                                                           float* __restrict__ ds, int HW, int C) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -407,8 +399,7 @@ __global__ void __launch_bounds__(CNN_THREADS) se_bn_bwd_reduce_kernel(const bf1
                                                                        const float* __restrict__ a, const float* __restrict__ b,
                                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                        float* __restrict__ out, int N, int HW, int C) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float sm[CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;
@@ -489,8 +480,7 @@ __global__ void __launch_bounds__(CNN_THREADS, APPLY ? 3 : 2) bn_act_bwd_kernel(
                                                                  const float* __restrict__ s, const float* __restrict__ dpool,
                                                                  float* __restrict__ sums, float inv_count, bf16* __restrict__ dgamma,
                                                                  bf16* __restrict__ dbeta, bf16* __restrict__ dx, int HW, int C, int silu) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float sm[APPLY ? 1 : CNN_THREADS * 8];
   const ChanMap m = make_chan_map(C / 8);
   const int n = blockIdx.y;

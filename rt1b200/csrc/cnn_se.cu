@@ -16,8 +16,7 @@ __global__ void __launch_bounds__(SE_THREADS) se_fc_fwd_kernel(const float* __re
                                                                const bf16* __restrict__ w1, const bf16* __restrict__ b1,
                                                                const bf16* __restrict__ w2, const bf16* __restrict__ b2,
                                                                float* __restrict__ z1_out, float* __restrict__ s_out, int C, int Cs) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   extern __shared__ float sm[];  // pooled [C] | hid [Cs]
   float* pooled = sm;
   float* hid = sm + C;
@@ -76,8 +75,7 @@ __global__ void __launch_bounds__(SE_BWD_THREADS) se_bwd_a_kernel(const float* _
                                                                   const float* __restrict__ z1, const bf16* __restrict__ w2,
                                                                   float* __restrict__ dhid, bf16* __restrict__ dw2, bf16* __restrict__ db2,
                                                                   int N, int C, int Cs) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   extern __shared__ __align__(16) float se_sm[];
   const int Cs4 = (Cs + 3) & ~3, U4 = Cs4 >> 2;
   float* hid = se_sm;                       // [N][Cs4]
@@ -152,8 +150,7 @@ __global__ void __launch_bounds__(SE_BWD_THREADS) se_bwd_b_kernel(const float* _
                                                                   const float* __restrict__ s, float* __restrict__ dpooled,
                                                                   float* __restrict__ sums, bf16* __restrict__ dw1, bf16* __restrict__ db1,
                                                                   int N, int C, int Cs) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   extern __shared__ __align__(16) float se_sm[];
   const int Cs4 = (Cs + 3) & ~3, U4 = Cs4 >> 2, Np = (N + 3) & ~3, N4 = Np >> 2;
   float* dz1t = se_sm;                      // [Cs4][Np]  (transposed: 16-byte broadcasts along the frames)

@@ -38,18 +38,36 @@ typedef __nv_bfloat162 bf162;
 
 static inline int rt1_cdiv(long a, long b) { return (int)((a + b - 1) / b); }
 
-// ---- programmatic dependent launch -------------------------------------------------------------------------
-// A training step is ~900 kernels of 5-50 us in ONE dependency chain: between two of them the GPU drains, the next grid is
-// launched, its CTAs are placed and run their prologue (barrier init, TMEM allocation, index math) before the first byte
-// moves — a few microseconds each time, a tenth of the step in total.  Every kernel of this library is therefore launched
-// with programmatic stream serialization: its CTAs may be placed while the previous kernel of the stream is still finishing,
-// run whatever does not touch global memory, and block in pdl_wait() until the previous grid has completed and its writes
-// are visible.  pdl_wait() precedes EVERY global access of a kernel (reads, and writes too: the allocator may hand a buffer
-// the predecessor still reads to its successor as output).  pdl_trigger() lets the NEXT kernel's CTAs be placed as soon as
-// all CTAs of this one are running.  Both are no-ops for a kernel launched without the attribute; stream capture records the
-// launches as programmatic graph edges.  RT1B200_PDL=0 launches everything fully serialised (A/B baseline).
+// ---- programmatic dependent launch (opt-in: RT1B200_PDL=1) -------------------------------------------------
+// A training step is ~900 kernels of 5-50 us in ONE dependency chain.  With programmatic stream serialization a kernel's
+// CTAs may be placed while the previous kernel of the stream is still draining; they run whatever does not touch global
+// memory and block in pdl_wait() until the previous grid has completed and its writes are visible.  pdl_enter() therefore
+// precedes EVERY global access of every kernel launched through rt1_launch (reads, and writes too: the allocator may hand
+// a buffer the predecessor still reads to its successor as output); in the tcgen05 kernels it comes after the TMEM
+// allocation, so that a placed-and-waiting CTA can never hold columns a running kernel still has to allocate.
+// Measured on B200 (profiles/r2_pdl_modes.jsonl): 18.67-18.69 ms per captured step with it against 18.81 without, and
+// 9.0 vs 9.2 us per kernel on a chain of 400 small dependent kernels — within noise, so it is OFF by default; triggering
+// before waiting (mode 3: arbitrarily deep chains of placed-and-waiting grids) doubled the chain's time.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// What a kernel does where its prologue ends (build-time choice RT1B200_PDL_MODE, see rt1b200/build.py):
+//   1  wait, then trigger: the next kernel's CTAs are placed while this one runs its main loop (one kernel deep)
+//   2  wait only: the trigger is the implicit one at CTA exit — the next kernel's CTAs fill in as this one's drain
+//   3  trigger, then wait
+#ifndef RT1_PDL_MODE
+#define RT1_PDL_MODE 2
+#endif
+__device__ __forceinline__ void pdl_enter() {
+#if RT1_PDL_MODE == 1
+  pdl_wait();
+  pdl_trigger();
+#elif RT1_PDL_MODE == 2
+  pdl_wait();
+#elif RT1_PDL_MODE == 3
+  pdl_trigger();
+  pdl_wait();
+#endif
+}
 bool rt1_pdl_enabled();
 
 template <typename... KArgs, typename... Args>

@@ -100,8 +100,7 @@ __global__ void __launch_bounds__(128, 8) gemm_tcgen05_kernel(const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
-  pdl_wait();      // the previous kernel's writes are visible from here on
+  pdl_enter();
 
   if (num_kb > 0) {
     if (warp == 0 && lane == 0) {
@@ -380,8 +379,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  pdl_trigger();   // every CTA holds its TMEM columns: CTAs of the next kernel may be placed now
-  pdl_wait();      // the previous kernel's writes are visible from here on
+  pdl_enter();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -768,8 +766,7 @@ RT1_API int rt1_gemm_bf16_bn(const void* A, long long lda, int a_mn, const void*
 
 // column sums of a bf16 [M, N] matrix → bf16 [N] (bias gradients)
 __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ x, long ld, int M, int N, bf16* __restrict__ out) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float sm[8][33];
   const int col = blockIdx.x * 32 + (threadIdx.x & 31), r0 = threadIdx.x >> 5;
   float s = 0.f;
@@ -791,8 +788,7 @@ RT1_API int rt1_colsum_bf16(const void* x, long long ld, int M, int N, void* out
 
 // fp32 → bf16 cast of a small buffer (split-K weight-gradient workspace → gradient slot)
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long n) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = __float2bfloat16_rn(in[i]);
 }

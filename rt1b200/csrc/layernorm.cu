@@ -14,8 +14,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const bf16* __restrict__ x,
                                                      const bf16* __restrict__ b, bf16* __restrict__ y,
                                                      float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows,
                                                      int D, float eps) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   const int row = blockIdx.x * wpb + warp;
   if (row >= rows) return;
@@ -57,8 +56,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x,
                                                      const bf16* __restrict__ dy, const float* __restrict__ mean_in,
                                                      const float* __restrict__ rstd_in, bf16* __restrict__ dx,
                                                      float* __restrict__ partial, int rows, int D) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   extern __shared__ float sm[];  // [2][D] per-CTA dgamma / dbeta partials
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) sm[i] = 0.f;
@@ -115,8 +113,7 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const bf16* __restrict__ x,
 
 __global__ void ln_param_grad_kernel(const float* __restrict__ partial, int nblk, int D, bf16* __restrict__ dw,
                                      bf16* __restrict__ db) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
   if (col >= D) return;
   float a = 0.f, c = 0.f;

@@ -9,8 +9,7 @@
 template <typename T>
 __global__ void __launch_bounds__(256) preprocess_kernel(const T* __restrict__ in, bf16* __restrict__ out, int N, int H, int W,
                                                          int off_y, int off_x, const int* __restrict__ shift_dev, float scale) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   if (shift_dev != nullptr) {   // offset sampled on the device (graph-captured steps): (dh, dw) added to (-pad_h, -pad_w)
     off_y += __ldg(shift_dev);
     off_x += __ldg(shift_dev + 1);

@@ -61,7 +61,7 @@ bool rt1_pdl_enabled() {
   static int on = -1;
   if (on < 0) {
     const char* e = getenv("RT1B200_PDL");
-    on = (e == nullptr || e[0] != '0') ? 1 : 0;
+    on = (e != nullptr && e[0] == '1') ? 1 : 0;     // opt-in: measured neutral on the captured step (profiles/ncu_notes.md §12)
   }
   return on == 1;
 }

@@ -64,8 +64,7 @@ __global__ void __launch_bounds__(TLP_THREADS) tl_pool_fwd_kernel(const bf16* __
                                                                   const bf16* __restrict__ w2, const bf16* __restrict__ b2,
                                                                   bf16* __restrict__ tokens, long out_stride, float* __restrict__ wmap,
                                                                   int P, int C, int T) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float wm[TLP_MAXP * TLP_MAXT];
   __shared__ float w2s[TLP_MAXT * TL_HID];
   __shared__ float part[4][TLP_MAXT * 8][8];
@@ -101,8 +100,7 @@ __global__ void __launch_bounds__(512) tl_pool_bwd_kernel(const bf16* __restrict
                                                           const float* __restrict__ wmap, const bf16* __restrict__ w2,
                                                           const bf16* __restrict__ dtokens, long dtok_stride, bf16* __restrict__ dhpre,
                                                           float* __restrict__ scratch, int P, int C, int T) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   extern __shared__ __align__(16) uint8_t tl_dyn[];
   bf16* dts = reinterpret_cast<bf16*>(tl_dyn);                       // [T][C] bf16
   float* dl = reinterpret_cast<float*>(dts + (size_t)T * C);          // [P][T] dwmap → dlogit
@@ -184,8 +182,7 @@ __global__ void __launch_bounds__(512) tl_pool_bwd_kernel(const bf16* __restrict
 // grid (n, C / 64): dfeats[p][c] += sum_k wmap[p][k] * dtok[k][c]
 __global__ void __launch_bounds__(TLP_THREADS) tl_direct_bwd_kernel(const float* __restrict__ wmap, const bf16* __restrict__ dtokens,
                                                                     long dtok_stride, bf16* __restrict__ dfeats, int P, int C, int T) {
-  pdl_trigger();
-  pdl_wait();
+  pdl_enter();
   __shared__ float dts[TLP_MAXT][64];
   __shared__ float wm[TLP_MAXP * TLP_MAXT];
   const int n = blockIdx.x, c0 = blockIdx.y * 64;

@@ -53,6 +53,7 @@ class _ZeroArena:
 
 
 _ARENA = None       # set for the duration of _EncoderFn.forward / backward
+_STATS_EPOCH = 0    # training passes of the encoder being run (set by _EncoderFn.forward; keys the evaluation-mode BN cache)
 
 
 def _zeros(*shape, device):
@@ -98,8 +99,26 @@ class _BN:
                    float(m.momentum if m.momentum is not None else 0.1), float(m.eps))
         return t
 
-    def finalize(self, count: int, training: bool):
+    def finalize(self, count: int, training: bool, stats_epoch: int = 0):
         m = self.mod
+        if not training:
+            # Evaluation reads the running statistics: scale / shift only change when the statistics or the affine
+            # parameters do, so they are computed once and kept on the module (78 tiny launches per policy step otherwise).
+            # `stats_epoch` counts the training passes of the owning encoder — the kernels update the running statistics
+            # through raw pointers, which tensor version counters do not see.
+            key = (stats_epoch, m.running_mean._version, m.running_var._version, m.weight._version, m.bias._version,
+                   m.weight.data_ptr(), m.running_mean.data_ptr())
+            cached = getattr(m, "_rt1_eval_affine", None)
+            if cached is None or cached[0] != key:
+                buf = torch.empty(4, m.num_features, dtype=F32, device=m.running_mean.device)
+                call("rt1_bn_finalize", ptr(None), ptr(None), f32(count), ptr(m.weight), ptr(m.bias), ptr(m.running_mean),
+                     ptr(m.running_var), f32(0.0), f32(m.eps), i32(0), ptr(buf[0]), ptr(buf[1]), ptr(buf[2]), ptr(buf[3]),
+                     i32(m.num_features), stream())
+                cached = (key, buf)
+                if not torch.cuda.is_current_stream_capturing():     # memory allocated under capture belongs to that graph
+                    m._rt1_eval_affine = cached
+            self.a, self.b, self.mean, self.rstd = cached[1].unbind(0)
+            return
         call("rt1_bn_finalize", ptr(self.sum), ptr(self.sumsq), f32(count), ptr(m.weight), ptr(m.bias), ptr(m.running_mean),
              ptr(m.running_var), f32(m.momentum if m.momentum is not None else 0.1), f32(m.eps), i32(training), ptr(self.a),
              ptr(self.b), ptr(self.mean), ptr(self.rstd), i32(m.num_features), stream())
@@ -113,7 +132,7 @@ def _conv_bn(x2d, w2d, out2d, M, N, K, bn: "_BN", training: bool):
              i64(out2d.stride(0)), i32(M), i32(N), i32(K), ptr(bn.sum), ptr(bn.sumsq), ctypes.byref(tail), stream())
     else:
         gemm(x2d, w2d, out2d, M, N, K, col_sum=bn.sum if training else None, col_sumsq=bn.sumsq if training else None)
-        bn.finalize(M, training)
+        bn.finalize(M, training, _STATS_EPOCH)
 
 
 def _conv_w2d(conv) -> torch.Tensor:
@@ -155,11 +174,12 @@ def _film_operands(enc):
 class _EncoderFn(Function):
     @staticmethod
     def forward(ctx, enc, x8, context, sd_scales, *anchors):
-        global _ARENA
+        global _ARENA, _STATS_EPOCH
         net = enc.net
         dev = x8.device
         _ARENA = _ZeroArena(dev)
         training = enc.training
+        _STATS_EPOCH = getattr(enc, "_bn_stats_epoch", 0)
         N, H, W, _ = x8.shape
         S = []                                    # saved per-layer state for backward
         ctx.enc, ctx.training = enc, training
@@ -234,7 +254,7 @@ class _EncoderFn(Function):
                 call("rt1_dwconv_fwd", ptr(dw_in), ptr(a_in), ptr(b_in), ptr(blk.depthwise[0].weight), ptr(d_raw),
                      ptr(bn2.sum if training else None), ptr(bn2.sumsq if training else None), i32(N), i32(Hc), i32(Wc), i32(Ce),
                      i32(k), i32(s), stream())
-                bn2.finalize(Mo, training)
+                bn2.finalize(Mo, training, _STATS_EPOCH)
             se = blk.se
             if se is not None:
                 Cs = se.fc1.out_channels
@@ -282,6 +302,7 @@ class _EncoderFn(Function):
         ctx.S, ctx.gb, ctx.film_off, ctx.GB, ctx.use_early, ctx.context = S, gb, film_off, GB, use_early, context
         if training:
             enc._nbt_pending = getattr(enc, "_nbt_pending", 0) + 1
+            enc._bn_stats_epoch = getattr(enc, "_bn_stats_epoch", 0) + 1
         _ARENA = None
         return feats
 

@@ -51,8 +51,10 @@ def keep_bn_stats_fp32(model: nn.Module):
 class DataParallelEngine:
     def __init__(self, model: nn.Module, lr: float = 5e-4, betas: Tuple[float, float] = (0.9, 0.999),
                  eps: float = 1e-8, weight_decay: float = 0.0, param_dtype: Optional[torch.dtype] = None,
-                 backend: str = "auto", bucket_mb: Optional[float] = None, process_group=None, overlap: bool = True):
+                 backend: str = "auto", bucket_mb: Optional[float] = None, process_group=None, overlap: bool = True,
+                 broadcast_buffers: bool = False):
         self.model = model
+        self.broadcast_buffers = broadcast_buffers   # re-broadcast rank 0's buffers after every step (see sync_buffers)
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
         self.step_count = 0
         self.group = process_group
@@ -113,12 +115,24 @@ class DataParallelEngine:
         self.sync_buffers(src)
 
     def sync_buffers(self, src: int = 0):
+        """Rank ``src``'s module buffers (BatchNorm running statistics and step counters) become everyone's — C3 of
+        SURVEY §2.5.  torch DDP does this before EVERY forward (``broadcast_buffers=True``, the Lightning default the
+        reference runs with, ``distribute_train.py:231-238``); since no rank ever reads another rank's running statistics
+        during training, the observable effect is that evaluation and checkpoints use rank ``src``'s.  Here the ~160 buffers
+        travel as ONE coalesced broadcast per dtype, (a) at construction, (b) before every evaluation pass and checkpoint
+        (``Trainer`` calls this), and (c) after every optimisation step when ``broadcast_buffers=True`` is asked for."""
         if self.world == 1:
             return
         dist = _dist()
+        by_dtype: Dict[torch.dtype, List[torch.Tensor]] = {}
         for b in self.model.buffers():
             if b.is_floating_point() or b.dtype in (torch.int64, torch.int32):
-                dist.broadcast(b, src, group=self.group)
+                by_dtype.setdefault(b.dtype, []).append(b)
+        for bufs in by_dtype.values():
+            flat = torch.cat([b.reshape(-1) for b in bufs])
+            dist.broadcast(flat, src, group=self.group)
+            if self.rank != src:
+                torch._foreach_copy_(bufs, [c.view_as(b) for c, b in zip(flat.split([b.numel() for b in bufs]), bufs)])
 
     def _install_ready_hooks(self):
         """Count gradients as autograd finishes them; when a bucket is complete, reduce+update it right away."""
@@ -240,6 +254,8 @@ class DataParallelEngine:
             for b in reversed(range(len(self.buckets))):
                 self._reduce_and_update(b, hyper)
         self.step_count += 1
+        if self.broadcast_buffers:
+            self.sync_buffers(0)
 
     def _reduce_and_update(self, b: int, h: dict):
         lo, hi = self.buckets[b]

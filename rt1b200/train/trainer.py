@@ -257,6 +257,7 @@ class GraphedTrainStep:
         _lib.add_launches(self.native_launches)
         for m in self._bn_encoders():                             # the Python-side step counter of the BatchNorm buffers
             m._nbt_pending = getattr(m, "_nbt_pending", 0) + 1
+            m._bn_stats_epoch = getattr(m, "_bn_stats_epoch", 0) + 1     # running statistics moved: evaluation caches are stale
         return self.loss
 
 
@@ -269,7 +270,8 @@ class Trainer:
         module.to(self.device)
         if param_dtype is None:
             param_dtype = torch.bfloat16 if self.device.type == "cuda" else torch.float32
-        self.engine = DataParallelEngine(module.model, lr=args.lr, param_dtype=param_dtype, backend=backend)
+        self.engine = DataParallelEngine(module.model, lr=args.lr, param_dtype=param_dtype, backend=backend,
+                                         broadcast_buffers=bool(getattr(args, "broadcast_buffers", False)))
         self.sched = MultiStepLR(args.lr, getattr(args, "milestones", []), 0.1)
         self.rank, self.world = self.engine.rank, self.engine.world
         self.epoch = 0
@@ -412,6 +414,8 @@ class Trainer:
         return float(self._loss_host[0])
 
     def _run_eval(self, loader, step_fn) -> float:
+        # every rank evaluates with rank 0's BatchNorm running statistics, as under torch DDP's per-forward buffer broadcast
+        self.engine.sync_buffers(0)
         self.module.eval()
         total = torch.zeros((), device=self.device)
         n = 0

@@ -79,6 +79,17 @@ def main():
     ls = [torch.empty_like(m) for _ in range(world)]
     dist.all_gather(ls, l.reshape(1).float())
     torch.testing.assert_close(m, torch.stack(ls).mean(0))
+    # 4. BatchNorm running statistics are per-rank while training (different data per rank) and rank 0's after sync_buffers()
+    def bn_stats():
+        return torch.cat([b.detach().float().reshape(-1) for n_, b in module.model.named_buffers() if "running_" in n_])
+    mine = bn_stats()
+    both = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(both, mine)
+    assert not torch.equal(both[0], both[1]), "ranks saw different batches: their running statistics should differ"
+    eng.sync_buffers(0)
+    after = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(after, bn_stats())
+    assert all(torch.equal(both[0], a) for a in after), "sync_buffers must make rank 0's statistics everyone's"
     if rank == 0:
         print("DP_WORKER_OK", flush=True)
     dist.barrier()

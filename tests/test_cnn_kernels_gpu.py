@@ -349,3 +349,46 @@ def test_full_encoder_matches_fp32_module(training):
             # bf16 activations 20+ blocks deep: a few per cent of drift against the fp32 module is rounding, not a bug
             # (the statistics are accumulated with fp32 atomics, so the last digits also vary from run to run)
             assert _rel(bf_, br) < 1.2e-1 or float(br.norm()) < 1e-3, n
+
+
+def test_eval_batchnorm_affine_is_cached_and_invalidated_by_training():
+    """Evaluation keeps BatchNorm scale/shift on the module; a training pass (which moves the running statistics through raw
+    pointers) must invalidate them."""
+    from rt1b200 import ops
+    from rt1b200.models.tokenizers import RT1ImageTokenizer
+    from rt1b200.parallel.engine import keep_bn_stats_fp32
+    torch.manual_seed(0)
+    net = RT1ImageTokenizer(512, use_token_learner=True, num_tokens=8).to(DEV).to(BF)
+    keep_bn_stats_fp32(net)
+    b, t, H, W = 2, 2, 64, 96
+    img = torch.rand(b * t, 3, H, W, device=DEV)
+    x8 = ops.reference.preprocess_nhwc(img, (4, 6)).to(DEV)
+    ctx = _bf(b, t, 512, seed=5)
+    bns = [m for m in net.modules() if isinstance(m, torch.nn.BatchNorm2d)]
+
+    def drop_caches():
+        for m in bns:
+            if hasattr(m, "_rt1_eval_affine"):
+                del m._rt1_eval_affine
+
+    net.eval()
+    with torch.no_grad():
+        e0 = net.forward_nhwc(x8, ctx, b, t).clone()
+        n0 = _lib.launch_count()
+        e1 = net.forward_nhwc(x8, ctx, b, t).clone()
+        cached_calls = _lib.launch_count() - n0
+        drop_caches()
+        n0 = _lib.launch_count()
+        net.forward_nhwc(x8, ctx, b, t)
+        uncached_calls = _lib.launch_count() - n0
+    assert torch.equal(e0, e1)
+    assert uncached_calls - cached_calls == len(bns), (uncached_calls, cached_calls, len(bns))
+    net.train()
+    net.forward_nhwc(x8 * 0.5, ctx, b, t)                      # moves every running mean / variance
+    net.eval()
+    with torch.no_grad():
+        e2 = net.forward_nhwc(x8, ctx, b, t).clone()
+        drop_caches()
+        e3 = net.forward_nhwc(x8, ctx, b, t).clone()
+    assert not torch.equal(e2, e0), "the running statistics changed: the evaluation output must change too"
+    assert torch.equal(e2, e3), "stale cached scale/shift after a training pass"
