@@ -27,6 +27,9 @@ int rt1_device_info(int* sm_count, int* cc_major, int* cc_minor, long long* smem
  * clears it).  A captured CUDA graph bakes the seeds passed by value; advancing this word from a node of the graph gives
  * every replay fresh dropout masks (forward and backward of one replay read the same value). */
 int rt1_set_seed_epoch(const void* dev_u32);
+/* Publish a device float to pinned host memory from inside a captured graph: *dst_host = *src_dev, then ++*counter_dev is
+ * written to *flag_host (both host pointers must be pinned, device-accessible memory).  The host polls *flag_host. */
+int rt1_publish_scalar(const float* src_dev, float* dst_host, unsigned* counter_dev, unsigned* flag_host, cudaStream_t stream);
 /* Benchmark helper: stream `bytes` of writes through `buf` (use a buffer larger than the 126 MB L2). */
 int rt1_l2_flush(void* buf, long long bytes, unsigned tag, cudaStream_t stream);
 

@@ -121,3 +121,21 @@ RT1_API int rt1_l2_flush(void* buf, long long bytes, unsigned tag, cudaStream_t 
   l2_flush_kernel<<<148 * 8, 256, 0, stream>>>((uint4*)buf, n16, tag);
   return rt1_check_launch("rt1_l2_flush");
 }
+
+// Publish a device scalar to the host from INSIDE a captured graph: the value goes to pinned (device-mapped) host memory,
+// then a step counter is bumped and written next to it.  The host polls the counter: it learns the step's loss as soon as
+// the forward pass has produced it, while the rest of the graph (backward, optimizer) is still running — an event cannot be
+// waited on in the middle of a graph launch.
+__global__ void publish_scalar_kernel(const float* __restrict__ src, float* dst_host, unsigned* counter, volatile unsigned* flag_host) {
+  pdl_enter();
+  *dst_host = *src;
+  __threadfence_system();
+  const unsigned c = *counter + 1u;
+  *counter = c;
+  *flag_host = c;
+}
+RT1_API int rt1_publish_scalar(const float* src_dev, float* dst_host, unsigned* counter_dev, unsigned* flag_host, cudaStream_t stream) {
+  RT1_REQUIRE(src_dev != nullptr && dst_host != nullptr && counter_dev != nullptr && flag_host != nullptr, "rt1_publish_scalar: null pointer");
+  publish_scalar_kernel<<<1, 1, 0, stream>>>(src_dev, dst_host, counter_dev, flag_host);
+  return rt1_check_launch("rt1_publish_scalar");
+}

@@ -178,6 +178,11 @@ class GraphedTrainStep:
         dev = trainer.device
         self.static = _tree_map(lambda t: torch.empty_like(t), template_batch)
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        # the step's loss reaches the host from INSIDE the graph (right after the forward): pinned scalar + pinned step counter
+        self.loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self.flag_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self.step_ctr = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.replays = 0                                          # value flag_host takes when the latest replay's loss is out
         self.seed_epoch = kernels.seed_epoch_tensor(dev)
         self.stream = torch.cuda.Stream(device=dev)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
@@ -188,6 +193,9 @@ class GraphedTrainStep:
         tr = self.tr
         self.seed_epoch.add_(0x61C88647)                         # fresh dropout masks on every replay
         loss = tr.module.training_step(self.static, 0)
+        self.loss.copy_(loss.detach().float())
+        from ..ops._lib import call, ptr, stream
+        call("rt1_publish_scalar", ptr(self.loss), ptr(self.loss_host), ptr(self.step_ctr), ptr(self.flag_host), stream())
         # torch.autograd.grad, not loss.backward(): AccumulateGrad nodes (kept alive by the engine's hooks) remember the
         # stream they were created on — the default stream — and synchronising with it would invalidate the capture.
         # The kernel wrappers write most parameter gradients straight into the flat buffer and hand autograd `None`;
@@ -197,7 +205,6 @@ class GraphedTrainStep:
         dst = [p.grad for p, g in zip(params, grads) if g is not None]
         if dst:
             torch._foreach_add_(dst, [g for g in grads if g is not None])
-        self.loss.copy_(loss.detach().float())
 
     def _fill(self, batch):
         for d, s in zip(_tree_leaves(self.static), _tree_leaves(batch)):
@@ -239,6 +246,21 @@ class GraphedTrainStep:
         self.native_launches = _lib.launch_count() - n0          # native calls recorded into the graph (not executed yet)
         _lib.add_launches(-self.native_launches)
         self._undo_counters()
+        torch.cuda.synchronize(dev)
+        self.replays = int(self.step_ctr.item())                  # the warm-up pass counted once; replays continue from here
+
+    def wait_loss(self, timeout_s: float = 60.0) -> float:
+        """Block until the latest replay has published its loss (i.e. its forward pass is done) and return it."""
+        import time
+        want = self.replays & 0x7FFFFFFF
+        t0 = None
+        while (int(self.flag_host[0]) & 0x7FFFFFFF) != want:
+            if t0 is None:
+                t0 = time.monotonic()
+            elif time.monotonic() - t0 > timeout_s:
+                torch.cuda.synchronize(self.tr.device)
+                raise RuntimeError("the captured step did not publish its loss")
+        return float(self.loss_host[0])
 
     def _bn_encoders(self):
         if self._encoders is None:
@@ -254,6 +276,7 @@ class GraphedTrainStep:
         from ..ops import _lib
         self._fill(batch)
         self.graph.replay()
+        self.replays += 1
         _lib.add_launches(self.native_launches)
         for m in self._bn_encoders():                             # the Python-side step counter of the BatchNorm buffers
             m._nbt_pending = getattr(m, "_nbt_pending", 0) + 1
@@ -339,13 +362,14 @@ class Trainer:
         if g is not None:
             with trace.range_("train_step/graph replay (forward + backward)"):
                 loss = g.run(batch)                   # forward + backward: one graph replay
-            self._stage_loss(loss)
+            self._loss_graph = g                      # the graph itself publishes the loss to pinned memory after its forward
             with trace.range_("train_step/fused exchange + AdamW"):
                 self.engine.step(lr)                  # fused gradient exchange + AdamW (clears the gradients)
             self.global_step += 1
             return loss
         with trace.range_("train_step/forward"):
             loss = self.module.training_step(batch, self.global_step)
+        self._loss_graph = None
         self._stage_loss(loss)
         self.engine.begin_step(lr)
         with trace.range_("train_step/backward (+ overlapped exchange)"):
@@ -409,6 +433,8 @@ class Trainer:
 
     def read_loss(self) -> float:
         """The last step's (rank-local) loss as a Python float: device→host read that waits for that step's forward only."""
+        if getattr(self, "_loss_graph", None) is not None:
+            return self._loss_graph.wait_loss()
         if self.device.type == "cuda":
             self._loss_ev.synchronize()
         return float(self._loss_host[0])
