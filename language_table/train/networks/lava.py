@@ -5,9 +5,10 @@ Pipeline per frame: image encoder (conv/max-pool tower, or a frozen ResNet pyram
 → ``num_layers`` pre-norm cross-attention blocks in which ONE language token queries the visual sentence (residual on the
 language path only) → LayerNorm; then over the ``sequence_length`` frames a pre-norm temporal transformer (1-D sinusoidal
 positions, mean over time, LayerNorm) → dense ResNet → action.  The language token is a sentence embedding found in the
-observation (``clip_embedding``); the reference's in-graph frozen CLIP text tower (``lang_encoder="clip"``) needs a
-checkpoint that is not available offline — any module mapping token ids to a 512-d embedding can be passed as
-``text_encoder`` instead.
+observation (``clip_embedding``, the default) or comes from the in-graph frozen CLIP text tower
+(``lang_encoder="clip"``: :mod:`.clip_text` restates the architecture; its pretrained checkpoint is not available offline —
+load one with ``clip_text.load_clip_text_weights`` or pass any module mapping token ids to a 512-d embedding as
+``text_encoder``).
 """
 import math
 from typing import Optional, Sequence
@@ -178,8 +179,11 @@ class SequenceLAVAEncoder(nn.Module):
         if lang_encoder not in ("clip_in_obs", "clip"):
             raise NotImplementedError(lang_encoder)
         if lang_encoder == "clip" and text_encoder is None:
-            raise ValueError("lang_encoder='clip' needs a text_encoder module (token ids -> [b, 512]); the reference's frozen "
-                             "CLIP text tower checkpoint is not available offline — use 'clip_in_obs' with precomputed embeddings")
+            # the reference's in-graph frozen CLIP text tower (lava.py:423-432): same architecture, restated in clip_text.py.
+            # Its pretrained checkpoint is not reachable offline: load one with clip_text.load_clip_text_weights(), or pass a
+            # ready module as `text_encoder`; without either the tower is randomly initialised (and frozen).
+            from language_table.train.networks.clip_text import ClipTextEncoder
+            text_encoder = ClipTextEncoder(out_features=lang_dim).freeze()
         self.lang_encoder, self.text_encoder, self.d_model = lang_encoder, text_encoder, d_model
         self.descriptors = VisualDescriptorsNet(self.image_encoder.pyramid_channels, pyramid_fuse_layers, d_model)
         self.vis_drop, self.lang_drop = nn.Dropout(0.1), nn.Dropout(0.1)

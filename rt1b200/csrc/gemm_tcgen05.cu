@@ -752,7 +752,8 @@ RT1_API int rt1_gemm_bf16_bn(const void* A, long long lda, int a_mn, const void*
   RT1_REQUIRE(M > 0 && N > 0 && K > 0, "rt1_gemm_bf16_bn: empty problem %dx%dx%d", M, N, K);
   RT1_REQUIRE(col_sum != nullptr && col_sumsq != nullptr && tail != nullptr && tail->ticket != nullptr,
               "rt1_gemm_bf16_bn: statistics buffers, tail and ticket are required");
-  if (((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0 && gemm_v2_enabled()) {
+  const long tiles128 = (long)((M + 127) / 128) * ((N + 127) / 128);
+  if (((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0 && tiles128 >= v2_min_tiles() && gemm_v2_enabled()) {
     GemmParams p;
     p.M = M; p.N = N; p.K = K; p.a_mn = a_mn; p.b_mn = b_mn;
     return launch_gemm_persistent(p, A, lda, B, ldb, out, ldo, nullptr, nullptr, 0, 1.f, 0.f, 0u, col_sum, col_sumsq, stream, tail);

@@ -136,3 +136,49 @@ def test_lava_closed_loop_eval_entry(tmp_path):
                                         num_evals_per_reward=1, max_episode_steps=2, device="cpu")
     assert list(res) == ["blocktoblock", "blocktoabsolutelocation", "blocktoblockrelativelocation", "blocktorelativelocation", "separate"]
     assert all(v["episodes"] == 1 for v in res.values()) and (tmp_path / "eval" / "results.json").exists()
+
+
+def test_clip_text_tower_architecture_pooling_and_checkpoint_names():
+    """The CLIP text tower behind ``lang_encoder="clip"`` (reference lava.py:423-432): ViT-B/32's text transformer."""
+    from language_table.train.networks.clip_text import ClipTextEncoder, load_clip_text_weights
+    torch.manual_seed(0)
+    full = ClipTextEncoder()
+    assert sum(p.numel() for p in full.parameters()) == 63_428_096          # CLIP ViT-B/32 text tower
+    enc = ClipTextEncoder(vocab_size=300, features=64, num_heads=4, num_layers=2, out_features=32, context_length=16).eval()
+    sot, eot = 298, 299
+    toks = torch.zeros(3, 16, dtype=torch.long)
+    toks[0, :5] = torch.tensor([sot, 5, 6, 7, eot])
+    toks[1, :5] = torch.tensor([sot, 5, 6, 7, eot])
+    toks[1, 5:9] = torch.tensor([1, 2, 3, 4])            # padding garbage AFTER the end-of-text token
+    toks[2, :4] = torch.tensor([sot, 5, 9, eot])
+    with torch.no_grad():
+        out = enc(toks)
+    assert out.shape == (3, 32)
+    # causal attention + pooling at the end-of-text position: what follows it cannot change the embedding
+    torch.testing.assert_close(out[0], out[1])
+    assert not torch.allclose(out[0], out[2])
+    # public CLIP checkpoints name the blocks transformer.resblocks.<i>.* and carry a visual half
+    other = ClipTextEncoder(vocab_size=300, features=64, num_heads=4, num_layers=2, out_features=32, context_length=16)
+    ck = {("transformer." + k if k.startswith("resblocks.") else k): v.clone() for k, v in other.state_dict().items()}
+    ck["visual.conv1.weight"] = torch.zeros(1)
+    ck["logit_scale"] = torch.zeros(())
+    load_clip_text_weights(enc, ck)
+    with torch.no_grad():
+        torch.testing.assert_close(enc(toks), other.eval()(toks))
+    with pytest.raises(KeyError):
+        load_clip_text_weights(enc, {k: v for k, v in ck.items() if not k.startswith("ln_final")})
+    frozen = ClipTextEncoder(vocab_size=300, features=64, num_heads=4, num_layers=1, out_features=32, context_length=16).freeze()
+    assert not any(p.requires_grad for p in frozen.parameters()) and not frozen.training
+
+
+def test_sequence_lava_with_in_graph_clip_tower():
+    from language_table.train.networks import lava
+    from language_table.train.networks.clip_text import ClipTextEncoder
+    tower = ClipTextEncoder(vocab_size=300, features=64, num_heads=4, num_layers=1, out_features=512, context_length=16).freeze()
+    enc = lava.SequenceLAVAEncoder(lang_encoder="clip", sequence_length=4, text_encoder=tower)
+    toks = torch.zeros(2, 4, 16, dtype=torch.long)
+    toks[:, :, 0], toks[:, :, 1], toks[:, :, 2] = 298, 7, 299
+    out = enc({"rgb": torch.rand(2, 4, 64, 96, 3), "instruction_tokenized_clip": toks})
+    assert out.shape[0] == 2
+    out.sum().backward()
+    assert all(p.grad is None for p in tower.parameters())               # frozen, like the reference's
