@@ -34,6 +34,7 @@ def ours(a):
     keep_bn_stats_fp32(model)
     model.eval()
     res = run_closed_loop(model, num_envs=a.envs, episodes=1, max_episode_steps=a.steps, device=dev, seed=0)
+    res_g = run_closed_loop(model, num_envs=a.envs, episodes=1, max_episode_steps=a.steps, device=dev, seed=0, graphed=True)
     # policy call alone (no board / rasteriser), same batch
     state = model.initial_state(a.envs, device=dev, dtype=torch.bfloat16)
     obs = {"image": torch.rand(a.envs, 3, 256, 456, device=dev), "natural_language_embedding": torch.randn(a.envs, 512, device=dev)}
@@ -48,8 +49,11 @@ def ours(a):
     lat = np.asarray(lat[3:])
     return {"impl": "ours", "num_envs": a.envs, "control_steps": a.steps, "dtype": "bf16",
             "control_step_ms_p50": res["step_latency_ms_p50"], "control_step_ms_p99": res["step_latency_ms_p99"],
+            "control_step_graphed_policy_ms_p50": res_g["step_latency_ms_p50"],
+            "control_step_graphed_policy_ms_p99": res_g["step_latency_ms_p99"],
             "policy_call_ms_p50": float(np.percentile(lat, 50)), "policy_call_ms_p99": float(np.percentile(lat, 99)),
             "env_steps_per_s": a.envs / (res["step_latency_ms_p50"] / 1e3),
+            "env_steps_per_s_graphed_policy": a.envs / (res_g["step_latency_ms_p50"] / 1e3),
             "what": "render + crop/resize + batched policy_step + board step for all envs, per control step"}
 
 
