@@ -44,29 +44,41 @@ def main():
     ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--out", default="gpurun_out/input_pipeline.json")
+    ap.add_argument("--train-only", action="store_true", help="skip the loader-only measurements (implied under torchrun)")
     a = ap.parse_args()
+    world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:                                        # one process per GPU: every rank reads its own shuffled stream
+        torch.cuda.set_device(local)
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+        a.train_only = True
     from argparse import Namespace
     from torch.utils.data import DataLoader
     from rt1b200.data.dataset import DecodeAndRandomResizedCrop, EmbodiedIntelligenceDataset, collate_fn
     from rt1b200.data.episodes import write_synthetic_dataset
     from rt1b200.data.gpu_transforms import GpuCropResize, RawFramesWithBoxes
     root = "/tmp/rt1_input_bench"
-    if not os.path.isdir(os.path.join(root, "train")):
+    if rank == 0 and not os.path.isdir(os.path.join(root, "train")):
         write_synthetic_dataset(root, a.episodes, 0, 0, min_len=30, max_len=40, height=180, width=320)
+    if world > 1:
+        torch.distributed.barrier()
     ids = list(range(a.episodes))
-    res = {"batch": a.batch, "seq_len": 6, "workers": a.workers, "episodes": a.episodes, "frame": "180x320 uint8 -> 256x456"}
+    res = {"batch": a.batch, "seq_len": 6, "workers": a.workers, "episodes": a.episodes, "frame": "180x320 uint8 -> 256x456",
+           "n_gpus": world}
 
     def mk(ds):
         return DataLoader(ds, batch_size=a.batch, shuffle=True, collate_fn=collate_fn, num_workers=a.workers, pin_memory=True,
                           drop_last=True, persistent_workers=a.workers > 0)
 
     n_b = 60
-    res["loader_pil_samples_per_s"] = loader_rate(mk(EmbodiedIntelligenceDataset(
-        os.path.join(root, "train"), ids, 6, DecodeAndRandomResizedCrop(0.95, (456, 256)))), n_b, a.batch)
     raw_ds = EmbodiedIntelligenceDataset(os.path.join(root, "train"), ids, 6, RawFramesWithBoxes(0.95))
-    res["loader_raw_samples_per_s"] = loader_rate(mk(raw_ds), n_b, a.batch)
+    if not a.train_only:
+        res["loader_pil_samples_per_s"] = loader_rate(mk(EmbodiedIntelligenceDataset(
+            os.path.join(root, "train"), ids, 6, DecodeAndRandomResizedCrop(0.95, (456, 256)))), n_b, a.batch)
+        res["loader_raw_samples_per_s"] = loader_rate(mk(raw_ds), n_b, a.batch)
     # the unmodified reference dataset + transform (needs the reference installation and its import shims)
     try:
+        if a.train_only:
+            raise RuntimeError("skipped (--train-only)")
         sys.path.insert(0, os.path.join(REPO, "baseline"))
         import refenv
         if refenv.available() or refenv.try_install():
@@ -90,7 +102,7 @@ def main():
 
     if torch.cuda.is_available():
         from rt1b200.train.trainer import RT1Module, Trainer
-        dev = torch.device("cuda", 0)
+        dev = torch.device("cuda", local)
         torch.cuda.set_device(dev)
         args = Namespace(height=256, width=456, seq_len=6, lr=5e-4, milestones=[], exp_name="inp", log_dir="/tmp/rt1_inp/logs",
                          ckpt_dir="/tmp/rt1_inp/ckpt", log_every_n_steps=10 ** 9, ckpt_every_n_epochs=1, max_epochs=1)
@@ -104,8 +116,11 @@ def main():
             tr.train_step(batch)
             tr.prefetch(nxt)
         torch.cuda.synchronize()
-        sampler = ClockSampler(0)
+        sampler = ClockSampler(local)
         sampler.start()
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.time()
         e0.record()
@@ -122,15 +137,23 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         wall = time.time() - t0
-        res["train_e2e_samples_per_s"] = a.steps * a.batch / (e0.elapsed_time(e1) / 1e3)
-        res["train_e2e_wall_samples_per_s"] = a.steps * a.batch / wall
-        res["train_e2e_ms_per_step"] = e0.elapsed_time(e1) / a.steps
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:                                    # the job's rate is set by its slowest rank
+            torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+        ms = float(ms.item())
+        res["train_e2e_samples_per_s"] = world * a.steps * a.batch / (ms / 1e3)
+        res["train_e2e_wall_samples_per_s"] = world * a.steps * a.batch / wall
+        res["train_e2e_ms_per_step"] = ms / a.steps
         res["h2d_bytes_per_step"] = sum(t.numel() * t.element_size() for v in batch.values() for t in v.values())
         res["last_loss"] = losses[-1]
         res["clocks"] = sampler.stop()
-    os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
-    json.dump(res, open(a.out, "w"), indent=1)
-    print(json.dumps(res))
+    if rank == 0:
+        os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
+        json.dump(res, open(a.out, "w"), indent=1)
+        print(json.dumps(res))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":
