@@ -1,4 +1,5 @@
-# N-GPU evidence run of the end-of-round tree: multi-GPU tests, exchange sweep, both bench arms, disk-backed training
+# N-GPU evidence run (usage: gpurun --gpus N -- bash tools/gpu_run_multi.sh N [sweep]): multi-GPU tests, both bench arms,
+# the scaled variant, training on disk-backed episodes, optionally the fused-exchange sweep
 set -x
 mkdir -p gpurun_out
 N=${1:-8}
