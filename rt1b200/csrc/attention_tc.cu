@@ -95,14 +95,14 @@ struct Smem {
   uint32_t* tmem_slot;
 };
 __device__ __forceinline__ Smem carve(uint8_t* raw, int DK, int SP, bool bwd) {
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* base = raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space
   const int nch = DK / 64;
   Smem s;
   s.q = base;
   s.k = s.q + nch * CHUNK_BYTES;
   s.v = s.k + nch * SP * 128;
   uint8_t* nxt = s.v + nch * SP * 128;
-  nxt = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(nxt) + 1023) & ~(uintptr_t)1023);
+  nxt += (1024u - (smem_u32(nxt) & 1023u)) & 1023u;
   s.go = nxt;
   if (bwd) nxt += nch * CHUNK_BYTES;
   s.p = nxt;

@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(128, 8) gemm_tcgen05_kernel(const __grid_const
                                                            const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // dynamic smem base is only guaranteed 16B-aligned by the ABI: align up to 1024 (swizzle-128B atom)
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS/STS, not generic LD/ST)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // 1-D grid over (m-tile, n-tile) with the n-tile index fastest: the CTAs that share an A tile run back to back,
   // so A is fetched from HBM once and re-read from L2
@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
                                                                               const __grid_constant__ CUtensorMap tma_o,
                                                                               const GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (LDS/STS, not generic LD/ST)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tiles = (p.N + p.block_n - 1) / p.block_n;
   const int m_tiles = (p.M + BLOCK_M - 1) / BLOCK_M;
