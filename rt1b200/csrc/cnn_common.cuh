@@ -55,6 +55,53 @@ static inline int cnn_ctas_per_frame(int N, int HW, int C) {
   return want;
 }
 
+// ---- packed fp32 pairs (fma.rn.f32x2 and friends): two channels per instruction -----------------------------------------
+// The elementwise BatchNorm / SiLU passes are issue-bound on scalar FFMA / FMUL / FADD (ncu: 55 % of the executed instructions
+// of se_bn_bwd_reduce); Blackwell executes the x2 forms at the same rate per instruction.
+typedef unsigned long long p2;
+__device__ __forceinline__ p2 p2_pack(float lo, float hi) {
+  p2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void p2_unpack(p2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ p2 p2_fma(p2 a, p2 b, p2 c) {
+  p2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ p2 p2_mul(p2 a, p2 b) {
+  p2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ p2 p2_add(p2 a, p2 b) {
+  p2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// sigmoid of a pair given u: tanh(u/2)/2 + 1/2 (two MUFU.TANH, two packed ops)
+__device__ __forceinline__ p2 p2_sigmoid(p2 u) {
+  const p2 half = p2_pack(0.5f, 0.5f);
+  float h0, h1;
+  p2_unpack(p2_mul(u, half), h0, h1);
+  return p2_fma(p2_pack(tanh_approx_f(h0), tanh_approx_f(h1)), half, half);
+}
+// eight consecutive floats / one 16-byte bf16 vector as four pairs
+__device__ __forceinline__ void load8p(const float* p, p2* f) {
+  const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+  f[0] = p2_pack(a.x, a.y); f[1] = p2_pack(a.z, a.w); f[2] = p2_pack(b.x, b.y); f[3] = p2_pack(b.z, b.w);
+}
+__device__ __forceinline__ void unpack8p(const bf16x8& v, p2* f) {
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) f[j] = p2_pack(__uint_as_float(w[j] << 16), __uint_as_float(w[j] & 0xffff0000u));
+}
+__device__ __forceinline__ void p2_to8(const p2* v, float* f) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) p2_unpack(v[j], f[2 * j], f[2 * j + 1]);
+}
+
 __device__ __forceinline__ void load8f(const float* p, float* f) {
   const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
   f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;

@@ -381,7 +381,7 @@ def test_eval_batchnorm_affine_is_cached_and_invalidated_by_training():
         n0 = _lib.launch_count()
         net.forward_nhwc(x8, ctx, b, t)
         uncached_calls = _lib.launch_count() - n0
-    assert torch.equal(e0, e1)
+    assert _rel(e1, e0) < 2e-2                                   # (the SE pooling sums with fp32 atomics: not bitwise repeatable)
     assert uncached_calls - cached_calls == len(bns), (uncached_calls, cached_calls, len(bns))
     net.train()
     net.forward_nhwc(x8 * 0.5, ctx, b, t)                      # moves every running mean / variance
@@ -390,5 +390,5 @@ def test_eval_batchnorm_affine_is_cached_and_invalidated_by_training():
         e2 = net.forward_nhwc(x8, ctx, b, t).clone()
         drop_caches()
         e3 = net.forward_nhwc(x8, ctx, b, t).clone()
-    assert not torch.equal(e2, e0), "the running statistics changed: the evaluation output must change too"
-    assert torch.equal(e2, e3), "stale cached scale/shift after a training pass"
+    assert _rel(e2, e0) > 10 * max(_rel(e1, e0), 1e-3), "the running statistics changed: the evaluation output must change too"
+    assert _rel(e2, e3) < 2e-2, "stale cached scale/shift after a training pass"
