@@ -60,34 +60,19 @@ __global__ void __launch_bounds__(CNN_THREADS) bn_act_pool_kernel(const bf16* __
   const int n = blockIdx.y;
   int rb, re;
   cta_rows(HW, rb, re);
-  p2 pacc[4] = {0, 0, 0, 0};
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (m.active) {
-    p2 fa[4], fb[4];
-    load8p(a + m.cv * 8, fa);
-    load8p(b + m.cv * 8, fb);
+    float fa[8], fb[8];
+    load8f(a + m.cv * 8, fa);
+    load8f(b + m.cv * 8, fb);
     const bf16* base = x + ((size_t)n * HW) * C + (size_t)m.cv * 8;
-    // two rows in flight per thread, channel pairs in packed fp32 (one fma / mul per pair, two MUFU.TANH)
-    for (int r = rb + m.r0; r < re; r += 2 * m.rows_per_pass) {
-      const int r2 = r + m.rows_per_pass;
-      const bool has2 = r2 < re;
-      bf16x8 raw[2];
-      raw[0] = *reinterpret_cast<const bf16x8*>(base + (size_t)r * C);
-      if (has2) raw[1] = *reinterpret_cast<const bf16x8*>(base + (size_t)r2 * C);
+    for (int r = rb + m.r0; r < re; r += m.rows_per_pass) {
+      float f[8];
+      load8bf(base + (size_t)r * C, f);
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        if (h == 1 && !has2) break;
-        p2 f[4];
-        unpack8p(raw[h], f);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const p2 u = p2_fma(fa[j], f[j], fb[j]);
-          pacc[j] = p2_fma(u, p2_sigmoid(u), pacc[j]);
-        }
-      }
+      for (int k = 0; k < 8; ++k) acc[k] += silu_f(fmaf(fa[k], f[k], fb[k]));
     }
   }
-  float acc[8];
-  p2_to8(pacc, acc);
   cta_channel_reduce_atomic(m, acc, sm, pooled + (size_t)n * C);
 }
 
@@ -527,53 +512,35 @@ __global__ void __launch_bounds__(CNN_THREADS, APPLY ? 3 : 2) bn_act_bwd_kernel(
   const int n = blockIdx.y;
   int rb, re;
   cta_rows(HW, rb, re);
-  p2 pacc1[4] = {0, 0, 0, 0}, pacc2[4] = {0, 0, 0, 0};
+  float acc1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, acc2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (m.active) {
-    // per channel pair: fa, fb (BN scale / shift), fs, dp (SE scale and pooled-gradient term), and
-    //   reduce: rs, nmr with xhat = x rs + nmr            apply: P, Q with dX = a dh + P x + Q
-    p2 fa[4], fb[4], fs[4], dp[4], k1[4], k2[4];
-    load8p(a + m.cv * 8, fa);
-    load8p(b + m.cv * 8, fb);
+    float fa[8], fb[8], mu[8], rs[8], fs[8], dp[8], k1[8], k2[8];
+    load8f(a + m.cv * 8, fa);
+    load8f(b + m.cv * 8, fb);
+    load8f(mean + m.cv * 8, mu);
+    load8f(rstd + m.cv * 8, rs);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      fs[j] = p2_pack(1.f, 1.f);
-      dp[j] = 0;
+    for (int k = 0; k < 8; ++k) {
+      fs[k] = 1.f; dp[k] = 0.f; k1[k] = 0.f; k2[k] = 0.f;
     }
-    if (s != nullptr) load8p(s + (size_t)n * C + m.cv * 8, fs);
-    if (dpool != nullptr) load8p(dpool + (size_t)n * C + m.cv * 8, dp);
-    {
-      float mu[8], rs[8], af[8], c1[8], c2[8], o1[8], o2[8];
-      load8f(mean + m.cv * 8, mu);
-      load8f(rstd + m.cv * 8, rs);
-      if (APPLY) {
-        load8f(a + m.cv * 8, af);
-        load8f(sums + m.cv * 8, c1);
-        load8f(sums + C + m.cv * 8, c2);
-        if (blockIdx.x == 0 && n == 0 && m.r0 == 0) {
-          store8bf(dbeta + m.cv * 8, c1);
-          store8bf(dgamma + m.cv * 8, c2);
-        }
-        // dX = a (dh - c1 - xhat c2) = a dh + P x + Q with P = -a rstd c2, Q = -a c1 - P mean: two constants per channel
-        // instead of four (mean, rstd, c1, c2) keeps the thread under 100 registers
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          o1[k] = -af[k] * rs[k] * c2[k] * inv_count;               // P
-          o2[k] = -af[k] * c1[k] * inv_count - o1[k] * mu[k];       // Q
-        }
-      } else {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          o1[k] = rs[k];
-          o2[k] = -mu[k] * rs[k];
-        }
+    if (s != nullptr) load8f(s + (size_t)n * C + m.cv * 8, fs);
+    if (dpool != nullptr) load8f(dpool + (size_t)n * C + m.cv * 8, dp);
+    if (APPLY) {
+      load8f(sums + m.cv * 8, k1);
+      load8f(sums + C + m.cv * 8, k2);
+      if (blockIdx.x == 0 && n == 0 && m.r0 == 0) {
+        store8bf(dbeta + m.cv * 8, k1);
+        store8bf(dgamma + m.cv * 8, k2);
       }
+      // dX = a (dh - c1 - xhat c2) = a dh + P x + Q with P = -a rstd c2, Q = -a c1 - P mean: two constants per channel
+      // instead of four (mean, rstd, c1, c2) keeps the thread under 100 registers
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        k1[j] = p2_pack(o1[2 * j], o1[2 * j + 1]);
-        k2[j] = p2_pack(o2[2 * j], o2[2 * j + 1]);
+      for (int k = 0; k < 8; ++k) {
+        const float pk = -fa[k] * rs[k] * k2[k] * inv_count;
+        k2[k] = -fa[k] * k1[k] * inv_count - pk * mu[k];     // Q
+        k1[k] = pk;                                          // P
       }
     }
-    const p2 one = p2_pack(1.f, 1.f), neg1 = p2_pack(-1.f, -1.f);
     const size_t off = ((size_t)n * HW) * C + (size_t)m.cv * 8;
     // two rows per trip: four 16-byte loads are in flight before the first one is consumed
     for (int r = rb + m.r0; r < re; r += 2 * m.rows_per_pass) {
@@ -589,32 +556,23 @@ __global__ void __launch_bounds__(CNN_THREADS, APPLY ? 3 : 2) bn_act_bwd_kernel(
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         if (h == 1 && !has2) break;
-        p2 gg[4], f[4];
-        float o[8];
-        unpack8p(raw[2 * h], gg);
-        unpack8p(raw[2 * h + 1], f);
+        float gg[8], f[8], o[8];
+        unpack8(raw[2 * h], gg);
+        unpack8(raw[2 * h + 1], f);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          p2 dh = p2_fma(gg[j], fs[j], dp[j]);                           // dT
-          if (silu) {
-            const p2 u = p2_fma(fa[j], f[j], fb[j]);
-            const p2 sg = p2_sigmoid(u);
-            dh = p2_mul(dh, p2_fma(p2_mul(u, sg), p2_fma(sg, neg1, one), sg));   // * SiLU'(u) = s + u s (1 - s)
-          }
-          if (APPLY) {
-            p2_unpack(p2_fma(fa[j], dh, p2_fma(k1[j], f[j], k2[j])), o[2 * j], o[2 * j + 1]);
-          } else {
-            pacc1[j] = p2_add(pacc1[j], dh);
-            pacc2[j] = p2_fma(dh, p2_fma(f[j], k1[j], k2[j]), pacc2[j]);
+        for (int k = 0; k < 8; ++k) {
+          const float dT = fmaf(gg[k], fs[k], dp[k]);
+          const float dh = silu ? dT * silu_grad_f(fmaf(fa[k], f[k], fb[k])) : dT;
+          if (APPLY) o[k] = fmaf(fa[k], dh, fmaf(k1[k], f[k], k2[k]));
+          else {
+            acc1[k] += dh;
+            acc2[k] += dh * (f[k] - mu[k]) * rs[k];
           }
         }
         if (APPLY) store8bf(dx + off + (size_t)(h ? r2 : r) * C, o);
       }
     }
   }
-  float acc1[8], acc2[8];
-  p2_to8(pacc1, acc1);
-  p2_to8(pacc2, acc2);
   if (!APPLY) {
     cta_channel_reduce_atomic(m, acc1, sm, sums);
     cta_channel_reduce_atomic(m, acc2, sm, sums + C);
