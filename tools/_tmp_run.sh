@@ -1,7 +1,6 @@
 set -x
 mkdir -p gpurun_out
-RT1B200_TRAIN_GRAPH_STRICT=1 timeout -s KILL 1200 python -m pytest tests -m gpu -q > gpurun_out/test_gpu.log 2>&1; tail -3 gpurun_out/test_gpu.log | cut -c1-300
-timeout -s KILL 600 python bench.py --reps 3 > gpurun_out/bench_ours_1gpu.json 2>/dev/null; tail -1 gpurun_out/bench_ours_1gpu.json | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(json.dumps({'ms_per_step': d['ms_per_step'], 'value': d['value'], 'e2e': d['e2e']['value']}))"
-export RT1B200_TRAIN_GRAPH=0
-timeout -s KILL 300 python tools/profile_step.py > gpurun_out/plain.log 2>&1 && timeout -s KILL 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches.csv python tools/profile_step.py > gpurun_out/ncu_list.log 2>&1
-python tools/agg_launches.py gpurun_out/launches.csv 70 > gpurun_out/step_launches.txt; head -12 gpurun_out/step_launches.txt
+N=${1:-8}
+run() { tag=$1; shift; timeout -s KILL 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node=$N --master-addr 127.0.0.1 --master-port 29632 bench.py --gpus $N "$@" > gpurun_out/bench_${tag}_$N.json 2> gpurun_out/bench_${tag}_$N.err; echo "$tag exit $?"; grep -a "^{" gpurun_out/bench_${tag}_$N.json | tail -1 | cut -c1-300; }
+RT1B200_TRAIN_GRAPH_STRICT=1 run ours --steps 20 --warmup 4
+RT1B200_TRAIN_GRAPH_STRICT=1 run ours_scaled --model scaled --steps 20 --warmup 4
