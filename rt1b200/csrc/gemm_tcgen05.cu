@@ -49,6 +49,24 @@ struct GemmParams {
   int dbg;               // bench-only switches (RT1B200_GEMM_DBG): 1 no copy-out, 2 no statistics, 4 no TMEM drain/staging, 8 no A loads, 16 no B loads
 };
 
+typedef unsigned long long p2s;   // two fp32 values in one 64-bit register pair (fma/add.rn.f32x2)
+__device__ __forceinline__ p2s p2s_pack(float lo, float hi) {
+  p2s r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void p2s_unpack(p2s v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ p2s p2s_add(p2s a, p2s b) {
+  p2s d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ p2s p2s_fma(p2s a, p2s b, p2s c) {
+  p2s d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;
 constexpr int A_TILE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KiB
@@ -475,21 +493,25 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
     float* s_bias = reinterpret_cast<float*>(smem + L.bias) + grp * 128;
     const uint32_t thresh = rt1_drop_threshold(p.dropout_p);
     const float keep_scale = p.dropout_p > 0.f ? 1.f / (1.f - p.dropout_p) : 1.f;
-    uint32_t li = 0;
+    // Tile cursor (m-tile, position in the serpentine n walk) and accumulator ring position advance by increments: the
+    // divisions they replace (t / n_tiles, li % n_acc, li / n_acc) were ~15 % of the epilogue's executed instructions.
+    uint32_t li = 0, acc_i = 0, use = 0;
+    int mt = t_begin / n_tiles, jn = t_begin - mt * n_tiles;
     for (int t = t_begin; t < t_end; ++t, ++li) {
+      const uint32_t acc_cur = acc_i, use_cur = use;
+      const int m0 = mt * BLOCK_M, n0 = ((mt & 1) ? n_tiles - 1 - jn : jn) * p.block_n;
+      if (++acc_i == n_acc) { acc_i = 0; ++use; }
+      if (++jn == n_tiles) { jn = 0; ++mt; }
       if ((int)(li & 1u) != grp) continue;                 // group g owns accumulators g, g + 2: it sees every phase of their barriers
-      const uint32_t acc_i = li % n_acc, use = li / n_acc;
-      int m0, n0;
-      v2_tile_coords(t, n_tiles, p.block_n, m0, n0);
       const int nv = min(p.block_n, p.N - n0);              // valid columns of this tile
       const int row = m0 + row_l;
       const bool row_ok = row < p.M;
       if (tid == 0) tma_store_wait_read();                   // staging tile free again (previous store has read it)
       if (p.bias != nullptr && tid < p.block_n) s_bias[tid] = (n0 + tid < p.N) ? __bfloat162float(p.bias[n0 + tid]) : 0.f;
       named_bar_sync(1 + grp, V2_EPI_THREADS);
-      mbar_wait(tfull0 + 8 * acc_i, use & 1u);
+      mbar_wait(tfull0 + 8 * acc_cur, use_cur & 1u);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc_i * (uint32_t)acc_stride;
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc_cur * (uint32_t)acc_stride;
       const bool full_tile = m0 + BLOCK_M <= p.M;
       // the accumulator goes back to the MMA warp as soon as its last chunk sits in registers
       const int cbeg = half * 64, cend = (p.dbg & 4) ? 0 : min(nv, half * 64 + 64);
@@ -504,7 +526,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) gemm_tcgen05_persistent_kernel(
         if (h2 == 1) {                                     // last read of this accumulator: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty0 + 8 * acc_i);
+          if (lane == 0) mbar_arrive(tempty0 + 8 * acc_cur);
         }
         if (c0 >= cend) continue;
         const bool edge = !full_tile || c0 + 32 > nv;

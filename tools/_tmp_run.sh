@@ -1,6 +1,4 @@
 set -x
-mkdir -p gpurun_out
-N=${1:-8}
-run() { tag=$1; shift; timeout -s KILL 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node=$N --master-addr 127.0.0.1 --master-port 29632 bench.py --gpus $N "$@" > gpurun_out/bench_${tag}_$N.json 2> gpurun_out/bench_${tag}_$N.err; echo "$tag exit $?"; grep -a "^{" gpurun_out/bench_${tag}_$N.json | tail -1 | cut -c1-300; }
-RT1B200_TRAIN_GRAPH_STRICT=1 run ours --steps 20 --warmup 4
-RT1B200_TRAIN_GRAPH_STRICT=1 run ours_scaled --model scaled --steps 20 --warmup 4
+cp rt1b200/lib/librt1b200.so /tmp/keep.so
+for rep in 1 2; do for v in old new; do cp rt1b200/lib/variants/$v.so rt1b200/lib/librt1b200.so; timeout -s KILL 600 python bench.py --reps 3 --no-e2e 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('$v', d['ms_per_step'])"; done; done
+cp /tmp/keep.so rt1b200/lib/librt1b200.so
