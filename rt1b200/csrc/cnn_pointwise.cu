@@ -260,6 +260,7 @@ __global__ void __launch_bounds__(256) block_finalize_bwd_combine_kernel(const f
   float db = 0.f, dg = 0.f;
   if (c < C) {
     const float g3 = has_bn ? __bfloat162float(gamma3[c]) : 1.f, b3 = has_bn ? __bfloat162float(beta3[c]) : 0.f;
+#pragma unroll 4
     for (int n = ny; n < N; n += 8) {
       const float s1 = S[(size_t)n * C + c], s2 = S[plane + (size_t)n * C + c], s3 = S[2 * plane + (size_t)n * C + c];
       const float sdn = sd != nullptr ? sd[n] : 1.f;

@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(SE_THREADS) se_fc_fwd_kernel(const float* __re
   for (int u = warp; u < Cs; u += nw) {
     float acc = 0.f;
     const bf16* wr = w1 + (size_t)u * C;
+#pragma unroll 4
     for (int c = lane * 8; c < C; c += 256) {
       float fw[8];
       unpack8(*reinterpret_cast<const bf16x8*>(wr + c), fw);
@@ -43,6 +44,7 @@ __global__ void __launch_bounds__(SE_THREADS) se_fc_fwd_kernel(const float* __re
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float acc = __bfloat162float(b2[c]);
     const bf162* wr = reinterpret_cast<const bf162*>(w2 + (size_t)c * Cs);   // Cs is even: rows are 4-byte aligned
+#pragma unroll 8
     for (int u = 0; u < Cs; u += 2) {
       const float2 w = __bfloat1622float2(wr[u >> 1]);
       acc = fmaf(w.x, hid[u], acc);
@@ -227,6 +229,7 @@ __global__ void __launch_bounds__(SE_BWD_THREADS) se_bwd_b_kernel(const float* _
     const size_t plane = (size_t)N * C;
     float s1 = 0.f, s2 = 0.f;
     if (c < C)
+#pragma unroll 3
       for (int n = grp; n < N; n += SE_BWD_THREADS / SE_SL) {
         const size_t i = (size_t)n * C + c;
         const float sv = s[i], dp = dps[n * (SE_SL + 1) + cl];
