@@ -88,16 +88,53 @@ def load_episodes(dataset_path: Optional[str], split: str = "train", synthetic: 
     return [load_episode(f) for f in files]
 
 
-def create_datasets(config, seed: int = 0):
+def _save_norm_info(path: str, info) -> None:
+    os.makedirs(path, exist_ok=True)
+    tmp = os.path.join(path, "norm_info.tmp.npy")
+    np.save(tmp, np.array(info, dtype=object), allow_pickle=True)
+    os.replace(tmp, os.path.join(path, "norm_info.npy"))                 # atomic: a waiting process never sees half a file
+
+
+def _load_norm_info(path: str):
+    f = os.path.join(path, "norm_info.npy")
+    return np.load(f, allow_pickle=True).item() if os.path.exists(f) else None
+
+
+def _wait_for_norm_info(path: str, timeout_s: float = 3600.0, poll_s: float = 0.2):
+    import time
+    t0 = time.time()
+    while True:
+        info = _load_norm_info(path)
+        if info is not None:
+            return info
+        if time.time() - t0 > timeout_s:
+            raise TimeoutError(f"process 0 did not write {path}/norm_info.npy within {timeout_s:.0f} s")
+        time.sleep(poll_s)
+
+
+def create_datasets(config, seed: int = 0, normalization_path: str = None, process_index: int = 0):
     """Returns ``(train WindowDataset, norm_info)`` like the reference's ``create_datasets`` (``:47-323``): statistics come from
-    ``data_normalization_num_samples`` batches and actions are normalised with them."""
+    ``data_normalization_num_samples`` batches and actions are normalised with them.
+
+    With ``normalization_path`` the statistics are handed off between processes the way the reference does it (``:191-233``,
+    ``:517-529``): process 0 loads them from ``<normalization_path>/norm_info.npy`` or computes and writes them; every other
+    process waits for the file and loads it, so all ranks (and a resumed run) normalise with the SAME numbers.  The data order
+    of a process is seeded with ``seed + process_index`` (the reference folds ``jax.process_index()`` into its data rng,
+    ``train.py:81``)."""
     from . import normalization
     eps = load_episodes(getattr(config, "dataset_path", None), "train", synthetic=getattr(config, "synthetic_data", False), seed=seed)
     ds = WindowDataset(eps, config.sequence_length, (config.data_target_height, config.data_target_width),
                        config.random_crop_factor if config.image_augment_crop else None, config.image_photometric_distortions,
-                       train=True, seed=seed)
-    stat_batches = ((b["observation"], b["action"]) for b in ds.batches(min(8, len(ds)), shuffle=False, drop_last=False))
-    obs_stats, act_stats, amin, amax = normalization.compute_dataset_statistics(
-        (({k: v.numpy() for k, v in o.items()}, a.numpy()) for o, a in stat_batches), config.data_normalization_num_samples,
-        skip_keys=tuple(config.data_skip_normalize_keys) + ("clip_embedding",))
-    return ds, {"observation_statistics": obs_stats, "action_statistics": act_stats, "action_min": amin, "action_max": amax}
+                       train=True, seed=seed + process_index)
+    if normalization_path is not None and process_index != 0:
+        return ds, _wait_for_norm_info(normalization_path)
+    info = _load_norm_info(normalization_path) if normalization_path is not None else None
+    if info is None:
+        stat_batches = ((b["observation"], b["action"]) for b in ds.batches(min(8, len(ds)), shuffle=False, drop_last=False))
+        obs_stats, act_stats, amin, amax = normalization.compute_dataset_statistics(
+            (({k: v.numpy() for k, v in o.items()}, a.numpy()) for o, a in stat_batches), config.data_normalization_num_samples,
+            skip_keys=tuple(config.data_skip_normalize_keys) + ("clip_embedding",))
+        info = {"observation_statistics": obs_stats, "action_statistics": act_stats, "action_min": amin, "action_max": amax}
+        if normalization_path is not None:
+            _save_norm_info(normalization_path, info)
+    return ds, info

@@ -39,7 +39,12 @@ def latest_checkpoint(workdir: str):
 def train(config, workdir: str, device=None, verbose: bool = True) -> Dict:
     torch.manual_seed(config.seed)
     device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
-    ds, norm_info = input_pipeline_rlds.create_datasets(config, seed=config.seed)
+    import torch.distributed as dist
+    rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+    # normalisation statistics: computed (or re-loaded) by process 0, read from <workdir>/norm_info by everyone else
+    ds, norm_info = input_pipeline_rlds.create_datasets(config, seed=config.seed, normalization_path=os.path.join(workdir, "norm_info"),
+                                                        process_index=rank)
+    verbose = verbose and rank == 0
     model = create_model(config).to(device)
     agent = create_agent(config, model, norm_info)
     os.makedirs(os.path.join(workdir, "checkpoints"), exist_ok=True)
@@ -57,7 +62,7 @@ def train(config, workdir: str, device=None, verbose: bool = True) -> Dict:
             if verbose and agent.step % config.log_loss_every_steps == 0:
                 print(f"[lava] step {agent.step} loss {sum(losses[-config.log_loss_every_steps:]) / min(len(losses), config.log_loss_every_steps):.5f} "
                       f"({(time.time() - t0) / max(1, len(losses)):.3f} s/step)", flush=True)
-            if agent.step % config.checkpoint_every_steps == 0 or agent.step >= config.num_train_steps:
+            if rank == 0 and (agent.step % config.checkpoint_every_steps == 0 or agent.step >= config.num_train_steps):
                 torch.save(agent.state_dict(), os.path.join(workdir, "checkpoints", f"ckpt_{agent.step}.pt"))
             if agent.step >= config.num_train_steps:
                 break

@@ -182,3 +182,26 @@ def test_sequence_lava_with_in_graph_clip_tower():
     assert out.shape[0] == 2
     out.sum().backward()
     assert all(p.grad is None for p in tower.parameters())               # frozen, like the reference's
+
+
+def test_normalization_handoff_between_processes(tmp_path):
+    """Process 0 computes and writes the normalisation statistics, the others wait for the file (reference
+    input_pipeline_rlds.py:191-233): same numbers everywhere, also after a restart."""
+    import threading
+    from language_table.train import input_pipeline_rlds as ip
+    cfg = _small(language_table_sim_local.get_config())
+    cfg.synthetic_data = True
+    path = str(tmp_path / "norm_info")
+    got = {}
+    waiter = threading.Thread(target=lambda: got.update(r1=ip.create_datasets(cfg, seed=0, normalization_path=path, process_index=1)[1]))
+    waiter.start()                                      # rank 1 starts first and has to wait
+    _, info0 = ip.create_datasets(cfg, seed=0, normalization_path=path, process_index=0)
+    waiter.join(timeout=60)
+    assert not waiter.is_alive() and "r1" in got
+    a0, a1 = info0["action_statistics"], got["r1"]["action_statistics"]
+    assert np.allclose(a0["mean"], a1["mean"]) and np.allclose(a0["std"], a1["std"])
+    # a restarted process 0 re-loads the file instead of recomputing: poison the file and see the poison come back
+    info0["action_min"] = np.asarray(info0["action_min"]) - 123.0
+    ip._save_norm_info(path, info0)
+    _, again = ip.create_datasets(cfg, seed=0, normalization_path=path, process_index=0)
+    assert np.allclose(again["action_min"], info0["action_min"])
