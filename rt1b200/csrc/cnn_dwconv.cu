@@ -6,7 +6,8 @@
 //   * A CTA walks a contiguous run of work items (channel chunk of <= 64 channels, frame, 16-wide spatial tile).  The
 //     item's source tile INCLUDING its halo is fetched by one 4-D TMA box load (cp.async.bulk.tensor.4d) into shared
 //     memory; coordinates outside the image arrive as zeros, which is the convolution's padding — no bounds tests in the
-//     inner loop.  Two stages: the load of item i+1 is in flight while item i is computed.
+//     inner loop.  A ring of 2-4 stages: the loads of the next items are in flight while item i is computed; items are
+//     walked with incremental cursors (no division per item), tile pointers keep their shared-memory provenance (LDS/STS).
 //   * lane = channel pair, warp = position inside the tile.  A thread owns a PX x PY block of destination pixels for two
 //     channels; it reads every source row of its footprint ONCE (one conflict-free 4-byte LDS per pixel: the 32 lanes of a
 //     warp read 32 consecutive words) and uses it for all PY x K row/tap combinations, so a source element costs one
@@ -15,8 +16,8 @@
 //   * the two channels of a thread are the two halves of a packed fp32 pair: every multiply-add is one FFMA2
 //     (fma.rn.f32x2), the only way to reach the full fp32 rate on sm_100 (a 3-register FFMA issues every other cycle).
 //   * fusions: BatchNorm+SiLU of the producer can be applied to the tile in shared memory (each source element once per
-//     CTA, zero padding re-imposed afterwards); the forward emits the per-channel sum / sum of squares the next
-//     BatchNorm needs; the data gradient multiplies by SiLU'(BN(x)) and emits the BatchNorm-backward sums; the weight
+//     CTA, packed pairs, zero padding re-imposed afterwards); the forward emits the per-channel sum / sum of squares the next
+//     BatchNorm needs and, through its last CTA, that BatchNorm's scale / shift (bn_tail.cuh); the data gradient multiplies by SiLU'(BN(x)) and emits the BatchNorm-backward sums; the weight
 //     gradient keeps its K*K accumulators in registers across all items of a chunk.
 #include "cnn_common.cuh"
 #include "sm100.cuh"

@@ -3,11 +3,15 @@
 Forward and backward are explicit kernel schedules over the kernels in ``csrc/cnn_*.cu`` and the tcgen05 GEMM
 (``csrc/gemm_tcgen05.cu``); nothing here is a PyTorch op except allocation.  Per MBConv block:
 
-  forward   expand GEMM (+BN1 statistics from the epilogue) → bn_finalize → depthwise (BN1+SiLU applied on load,
-            BN2 statistics from the epilogue) → bn_finalize → SE squeeze → SE FCs → SE excite (writes the GEMM
-            operand) → project GEMM (+BN3 statistics) → bn_finalize → BN3 + stochastic depth + residual + FiLM
-  backward  the mirror image; BatchNorm backward constants come from fused reduction passes, weight gradients
-            are written straight into the parameters' ``.grad`` slots (split-K GEMMs for the 1x1 convolutions).
+  forward   expand GEMM (+BN1 statistics and their finalisation from the epilogue / last CTA) → depthwise (BN1+SiLU applied
+            to the shared-memory tile, BN2 statistics + finalisation) → SE squeeze → SE FCs → SE excite (writes the GEMM
+            operand) → project GEMM (+BN3 statistics + finalisation) → BN3 + stochastic depth + residual + FiLM
+            (7 launches per block; evaluation mode reads cached scale / shift instead of statistics)
+  backward  FiLM/BN3 backward (reduce, combine, apply) → project data gradient → one pass for the SE-scale gradient and the
+            separable parts of BN2's backward sums → SE FC backward (two launches: data + four parameter gradients + BN2's
+            sums) → BN2 apply → depthwise data gradient (× SiLU', BN1 sums) → BN1 apply → expand data gradient; the weight
+            gradients (split-K GEMMs, depthwise wgrad) are leaves on a second stream and are written straight into the
+            parameters' ``.grad`` slots.
 
 Raw (pre-BatchNorm) tensors are what is stored for the backward pass; activated tensors are recomputed on load.
 """
