@@ -12,9 +12,12 @@ What it covers of the reference (``distribute_train.py``):
                           ``{epoch}-{eval_loss:.6f}-{train_loss_epoch:.6f}.ckpt`` + ``last.ckpt`` (``:214-220``),
                           and — unlike the reference, where resume is a commented hint (``:240``) — ``resume``.
 
-The step itself is the B200 design: bf16 model, flat fp32 master/optimizer state, one fused reduce+AdamW per
-bucket overlapped with backward (:class:`rt1b200.parallel.engine.DataParallelEngine`); the loss scalar for
-logging is averaged over ranks without leaving the device until a log interval is reached.
+The step itself is the B200 design: bf16 model, flat fp32 master/optimizer state, forward + backward captured as ONE CUDA
+graph after two eager warm-up steps (:class:`GraphedTrainStep`), then one fused gradient exchange + AdamW
+(:class:`rt1b200.parallel.engine.DataParallelEngine`; on the eager schedule it runs per bucket, overlapped with backward).
+The captured step publishes its loss to pinned host memory right after its forward pass, so ``read_loss()`` returns while
+the backward is still running and the host has the next step queued before the GPU runs dry; the loss scalar for logging is
+averaged over ranks without leaving the device until a log interval is reached.
 """
 from __future__ import annotations
 
@@ -432,7 +435,9 @@ class Trainer:
             self._loss_ev.record(self._d2h_stream)
 
     def read_loss(self) -> float:
-        """The last step's (rank-local) loss as a Python float: device→host read that waits for that step's forward only."""
+        """The last step's (rank-local) loss as a Python float: device→host read that waits for that step's forward only
+        (captured step: the graph writes it to pinned memory itself and the host polls a step counter; eager step: a D2H
+        copy on a side stream + event)."""
         if getattr(self, "_loss_graph", None) is not None:
             return self._loss_graph.wait_loss()
         if self.device.type == "cuda":
