@@ -27,6 +27,30 @@ from rt1b200 import spaces
 from rt1b200.envs.board import BatchedLanguageTable
 
 
+def add_debug_info_to_image(image: np.ndarray, info_dict: Dict[str, Any], pos=(0, 0), text_color=(0, 0, 0)) -> np.ndarray:
+    """The frame scaled to 640x360 under a white band that carries ``instruction: <text>``, wrapped at 35 characters
+    (reference ``language_table.py:1000-1030``, which draws with OpenCV's Hershey font; OpenCV is not available offline, so
+    the text is set with Pillow's built-in font — same layout, different glyphs).  Returns uint8 ``[444, 640, 3]``."""
+    import textwrap
+    from PIL import Image, ImageDraw, ImageFont
+    img = Image.fromarray(np.ascontiguousarray(image, dtype=np.uint8)).resize((640, 360), Image.BILINEAR)
+    band = int(3 * int(360 * 0.08))
+    canvas = Image.new("RGB", (640, 360 + band), (255, 255, 255))
+    canvas.paste(img, (0, band))
+    text = "instruction: %s" % info_dict["instruction"] if "instruction" in info_dict else ""
+    try:
+        font = ImageFont.load_default(size=24)           # Pillow >= 10.1 with FreeType
+    except Exception:                                     # noqa: BLE001 - older Pillow / no FreeType: the small bitmap font
+        font = ImageFont.load_default()
+    draw = ImageDraw.Draw(canvas)
+    x, y = pos
+    for line in textwrap.wrap(text, width=35):
+        box = draw.textbbox((x, y), line, font=font)
+        draw.text((x, y), line, fill=tuple(text_color), font=font)
+        y += int((box[3] - box[1]) * 1.2) + 2
+    return np.asarray(canvas, dtype=np.uint8)
+
+
 class LanguageTable:
     metadata = {"render.modes": ["rgb_array"]}
 
@@ -125,14 +149,9 @@ class LanguageTable:
 
     def render(self, mode="rgb_array"):
         frame = self._render_camera()
-        if self._render_text_in_image and self._instruction_str:
-            try:
-                import cv2
-                frame = np.ascontiguousarray(frame)
-                cv2.putText(frame, self._instruction_str[:60], (4, 12), cv2.FONT_HERSHEY_SIMPLEX, 0.35, (0, 0, 0), 1, cv2.LINE_AA)
-            except Exception:
-                pass
-        return frame
+        if not self._render_text_in_image:
+            return frame
+        return add_debug_info_to_image(frame, {"instruction": self._instruction_str} if self._instruction_str else {})
 
     # -------------------------------------------------------------------------------------- reset / step
     def reset(self, reset_poses=True):

@@ -270,3 +270,23 @@ def test_compat_import_paths():
             "assert distribute_train.RT1_Lightning is distribute_train.RT1Module; print('ok')")
     r = subprocess.run([sys.executable, "-c", code], cwd=repo, capture_output=True, text=True)
     assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
+
+
+def test_render_writes_the_instruction_above_the_frame():
+    """``render()`` = frame at 640x360 under a white band with the wrapped instruction (reference language_table.py:192-199,
+    1000-1030); ``render_text_in_image=False`` returns the bare camera frame."""
+    from language_table.environments import blocks, language_table
+    from language_table.environments.rewards import block2block
+    env = language_table.LanguageTable(block_mode=blocks.LanguageTableBlockVariants.BLOCK_8,
+                                       reward_factory=block2block.BlockToBlockReward, seed=0)
+    obs = env.reset()
+    frame = env.render()
+    assert frame.shape == (444, 640, 3) and frame.dtype == np.uint8
+    band = frame[:84]
+    assert (band == 255).mean() > 0.7 and (band < 128).any()           # white band with dark glyphs
+    bare = language_table.LanguageTable(block_mode=blocks.LanguageTableBlockVariants.BLOCK_8,
+                                        reward_factory=block2block.BlockToBlockReward, seed=0, render_text_in_image=False)
+    bare.reset()
+    assert bare.render().shape == obs["rgb"].shape
+    empty = language_table.add_debug_info_to_image(obs["rgb"], {})
+    assert empty.shape == (444, 640, 3) and (empty[:84] == 255).all()

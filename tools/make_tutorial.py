@@ -98,11 +98,12 @@ obs = env.reset()
 print({k: (v.shape, v.dtype) for k, v in obs.items()})
 print(decode_inst(obs["instruction"]))
 show(obs["rgb"], "first_observation")
+show(env.render(), "first_observation_with_text")
 """)
 
 md("""
-`env.render()` returns the camera image as well (the upstream class also draws the instruction into it; there is no font
-rasteriser here, so the text stays in `obs["instruction"]`).  An action is a 2-D effector displacement in metres, clipped
+`env.render()` returns the camera image scaled to 640x360 under a white band with the instruction written into it, like the
+upstream class (pass `render_text_in_image=False` for the bare frame).  An action is a 2-D effector displacement in metres, clipped
 by the policy wrappers to ±0.03 per 10 Hz control step.  The arm model behind it (xArm6 forward / inverse kinematics and
 a joint servo) makes the effector lag its target within a step, as in the upstream simulation.
 """)
