@@ -55,7 +55,8 @@ class LanguageTable:
     metadata = {"render.modes": ["rgb_array"]}
 
     def __init__(self, block_mode, reward_factory=None, control_frequency=10.0, shared_memory=False, seed=None,
-                 delay_reward_steps=0, render_text_in_image=True, training=True, device="cpu", arm_kinematics=True):
+                 delay_reward_steps=0, render_text_in_image=True, training=True, device="cpu", arm_kinematics=True,
+                 debug_visuals=False, add_invisible_walls=False):
         if shared_memory:
             raise NotImplementedError("the PyBullet GUI / shared-memory visualiser is unavailable on this box")
         self._block_mode = blocks_module.LanguageTableBlockVariants(block_mode) if isinstance(block_mode, str) else block_mode
@@ -72,7 +73,9 @@ class LanguageTable:
         self._board = BatchedLanguageTable(1, self._block_mode if self._block_mode in (
             blocks_module.LanguageTableBlockVariants.BLOCK_1, blocks_module.LanguageTableBlockVariants.BLOCK_4,
             blocks_module.LanguageTableBlockVariants.BLOCK_8, blocks_module.LanguageTableBlockVariants.N_CHOOSE_K)
-            else blocks_module.LanguageTableBlockVariants.BLOCK_8, device=device, seed=seed or 0, max_episode_steps=10 ** 9)
+            else blocks_module.LanguageTableBlockVariants.BLOCK_8, device=device, seed=seed or 0, max_episode_steps=10 ** 9,
+            add_invisible_walls=add_invisible_walls)
+        self._debug_visuals = debug_visuals        # GUI-only in the reference (debug lines in the PyBullet visualiser): accepted, no effect
         self._all_blocks = self._board.block_names
         self._blocks_on_table = list(self._all_blocks)
         self._reward_calculator = None

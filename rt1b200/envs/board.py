@@ -47,8 +47,12 @@ def resolve_contacts(eff: torch.Tensor, blocks: torch.Tensor, mask: torch.Tensor
 
 class BatchedLanguageTable:
     def __init__(self, num_envs: int, block_mode=blocks_module.LanguageTableBlockVariants.BLOCK_8, device="cpu", seed: int = 0,
-                 max_episode_steps: int = 80, image_hw=(256, 456), crop: float = 0.95):
+                 max_episode_steps: int = 80, image_hw=(256, 456), crop: float = 0.95, add_invisible_walls: bool = False):
         self.E = num_envs
+        # The reference's experimental "invisible walls" (language_table.py:933-990): four static boxes of half-width 0.04 m
+        # just outside the workspace that keep blocks from sliding off the board.  Here: block centres are clamped to the
+        # rectangle the walls' inner faces leave, shrunk by the block radius.
+        self.add_invisible_walls = bool(add_invisible_walls)
         self.device = torch.device(device)
         self.block_names = list(blocks_module.get_block_set(block_mode))
         self.B = len(self.block_names)
@@ -120,6 +124,11 @@ class BatchedLanguageTable:
         for k in range(effector_path.shape[1]):
             self.effector = effector_path[:, k].to(self.device, torch.float32)
             self.block_xy = resolve_contacts(self.effector, self.block_xy, self.block_mask, iters=2)
+            if self.add_invisible_walls:
+                r = C.BLOCK_RADIUS
+                wlo = torch.tensor([C.X_MIN + 0.02 + r, C.Y_MIN + 0.03 + r], device=self.device)
+                whi = torch.tensor([C.X_MAX - 0.05 - r, C.Y_MAX - 0.03 - r], device=self.device)
+                self.block_xy = torch.minimum(torch.maximum(self.block_xy, wlo), whi)
         self.steps += 1
         success = self.task_distance() < TARGET_BLOCK_DISTANCE
         self.succeeded |= success

@@ -290,3 +290,22 @@ def test_render_writes_the_instruction_above_the_frame():
     assert bare.render().shape == obs["rgb"].shape
     empty = language_table.add_debug_info_to_image(obs["rgb"], {})
     assert empty.shape == (444, 640, 3) and (empty[:84] == 255).all()
+
+
+def test_invisible_walls_keep_blocks_on_the_board():
+    """``add_invisible_walls=True`` (reference language_table.py:933-990): a block pushed towards the edge stops at the wall."""
+    import torch
+    from language_table.environments import constants as C
+    from rt1b200.envs.board import BatchedLanguageTable
+    res = {}
+    for walls in (False, True):
+        b = BatchedLanguageTable(1, device="cpu", seed=0, add_invisible_walls=walls)
+        b.reset()
+        b.block_xy[0, 0] = torch.tensor([C.X_MAX - 0.08, 0.0])
+        b.block_xy[0, 1:] = torch.tensor([C.X_MIN + 0.05, C.Y_MIN + 0.05])        # out of the way
+        b.effector[0] = b.effector_target[0] = torch.tensor([C.X_MAX - 0.14, 0.0])
+        for _ in range(12):
+            b.step(torch.tensor([[0.02, 0.0]]))
+        res[walls] = float(b.block_xy[0, 0, 0])
+    assert res[True] <= C.X_MAX - 0.05 - C.BLOCK_RADIUS + 1e-6
+    assert res[False] > res[True]
