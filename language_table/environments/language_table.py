@@ -51,6 +51,16 @@ def add_debug_info_to_image(image: np.ndarray, info_dict: Dict[str, Any], pos=(0
     return np.asarray(canvas, dtype=np.uint8)
 
 
+def sleep_spin(sleep_time_sec: float) -> None:
+    """Busy-wait sleep (reference ``:1032-1038``; used when pacing a viewer to the control rate)."""
+    import time
+    if sleep_time_sec <= 0:
+        return
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < sleep_time_sec:
+        pass
+
+
 class LanguageTable:
     metadata = {"render.modes": ["rgb_array"]}
 
@@ -119,6 +129,17 @@ class LanguageTable:
     @property
     def instruction_str(self):
         return self._instruction_str
+
+    @property
+    def pybullet_client(self):
+        """The reference hands out its Bullet client here (``:362``); there is no physics engine behind this environment."""
+        return None
+
+    def calc_camera_params(self, image_size):
+        """``(view matrix, projection matrix, position, look-at, up)`` of the table camera for ``image_size`` = (H, W), in
+        the reference's column-major OpenGL convention (``:365-397``) — the math of :mod:`rt1b200.envs.camera`."""
+        from rt1b200.envs import camera
+        return camera.calc_camera_params(image_size, constants.CAMERA_POSE, constants.CAMERA_ORIENTATION, constants.CAMERA_INTRINSICS)
 
     def get_control_frequency(self):
         return self._control_frequency
