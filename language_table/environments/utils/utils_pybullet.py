@@ -118,3 +118,71 @@ def write_state_file(path: str, states: List[Dict[str, Any]]) -> None:
 def read_state_file(path: str) -> List[Dict[str, Any]]:
     with gzip.open(path, "rt") as f:
         return json.load(f)
+
+
+# ------------------------------------------------------------------------------ reference-format state files (version 2)
+PYBULLET_STATE_VERSION = 2
+
+
+def rotation_to_matrix(rotation):
+    return rotation.as_matrix()
+
+
+def matrix_to_rotation(matrix):
+    from scipy.spatial import transform
+    return transform.Rotation.from_matrix(matrix)
+
+
+def _serialize_pybullet_state(state):
+    """Plain-old-data form of a state dict whose leaves are ints or ObjState / XarmState records (reference ``:376-393``)."""
+    if isinstance(state, list):
+        return [_serialize_pybullet_state(e) for e in state]
+    if isinstance(state, dict):
+        assert "_serialized_obj_name" not in state
+        return {k: _serialize_pybullet_state(v) for k, v in state.items()}
+    if isinstance(state, (XarmState, ObjState)):
+        return {"_serialized_obj_name": type(state).__name__, "_serialized_data": state.serialize()}
+    if isinstance(state, (int, float, str)) or state is None:
+        return state
+    raise ValueError("Unhandled type for object %s, type %s" % (str(state), type(state)))
+
+
+def _deserialize_pybullet_state(state):
+    if isinstance(state, list):
+        return [_deserialize_pybullet_state(e) for e in state]
+    if isinstance(state, dict):
+        if "_serialized_obj_name" in state:
+            name, data = state["_serialized_obj_name"], state["_serialized_data"]
+            if name == XarmState.__name__:
+                from language_table.environments.utils.pose3d import Pose3d
+                tep = data.get("target_effector_pose")
+                return XarmState(data["obj_id"], data["base_pose"], data.get("base_vel"), data.get("joint_info", ()),
+                                 data.get("joint_state", ()), None if tep is None else Pose3d.deserialize(tep),
+                                 data.get("goal_translation"))
+            if name == ObjState.__name__:
+                return ObjState.deserialize(data)
+            raise ValueError("Unsupported: %s" % name)
+        return {k: _deserialize_pybullet_state(v) for k, v in state.items()}
+    return state
+
+
+def write_pybullet_state(filename: str, pybullet_state, task, actions=None) -> None:
+    """gz-compressed JSON in the reference's layout (``:417-430``): ``pybullet_state`` (dict of ObjState / XarmState lists),
+    ``state_version``, ``ts_ms``, ``user``, ``task``, ``actions``."""
+    import getpass
+    import time
+    data = {"pybullet_state": _serialize_pybullet_state(pybullet_state), "state_version": PYBULLET_STATE_VERSION,
+            "ts_ms": int(time.time()) * 1000, "user": getpass.getuser(), "task": task,
+            "actions": [] if actions is None else _tolist(actions)}
+    with gzip.open(filename, "wb") as f:
+        f.write(json.dumps(data).encode("utf-8"))
+
+
+def read_pybullet_state(filename: str):
+    with gzip.open(filename, "rb") as f:
+        data = json.loads(f.read().decode("utf-8"))
+    assert isinstance(data, dict)
+    if data["state_version"] != PYBULLET_STATE_VERSION:
+        raise ValueError("incompatible state data (version %d, expected %d)" % (data["state_version"], PYBULLET_STATE_VERSION))
+    data["pybullet_state"] = _deserialize_pybullet_state(data["pybullet_state"])
+    return data

@@ -309,3 +309,34 @@ def test_invisible_walls_keep_blocks_on_the_board():
         res[walls] = float(b.block_xy[0, 0, 0])
     assert res[True] <= C.X_MAX - 0.05 - C.BLOCK_RADIUS + 1e-6
     assert res[False] > res[True]
+
+
+def test_reference_format_state_file_round_trip(tmp_path):
+    """Scene → the reference's state layout (robots / objects as XarmState / ObjState) → gz-JSON file (version 2) → scene."""
+    from language_table.environments import blocks, language_table
+    from language_table.environments.rewards import block2block
+    from language_table.environments.utils import utils_pybullet as up
+    env = language_table.LanguageTable(block_mode=blocks.LanguageTableBlockVariants.BLOCK_4,
+                                       reward_factory=block2block.BlockToBlockReward, seed=3)
+    env.reset()
+    for _ in range(3):
+        env.step(np.array([0.01, -0.01], np.float32))
+    st = env.export_pybullet_state()
+    assert set(st) >= {"robots", "robot_end_effectors", "targets", "objects"} and isinstance(st["robots"][0], up.XarmState)
+    f = str(tmp_path / "state.json.gz")
+    up.write_pybullet_state(f, st, task="block2block", actions=[[0.01, -0.01]] * 3)
+    data = up.read_pybullet_state(f)
+    assert data["state_version"] == 2 and data["task"] == "block2block" and len(data["actions"]) == 3
+    other = language_table.LanguageTable(block_mode=blocks.LanguageTableBlockVariants.BLOCK_4,
+                                         reward_factory=block2block.BlockToBlockReward, seed=99)
+    other.reset()
+    other.import_pybullet_state(data["pybullet_state"])
+    a, b = env._board, other._board
+    assert np.allclose(a.block_xy.numpy(), b.block_xy.numpy(), atol=1e-6)
+    assert np.allclose(np.cos(a.block_yaw.numpy() - b.block_yaw.numpy()), 1.0, atol=1e-6)      # same angle modulo 2 pi
+    assert np.allclose(a.effector_target.numpy(), b.effector_target.numpy(), atol=1e-6)
+    assert other.instruction_str == env.instruction_str
+    assert np.allclose(other.robot.get_joint_positions(), env.robot.get_joint_positions())
+    import gzip, json
+    raw = json.loads(gzip.open(f, "rb").read().decode())
+    assert raw["pybullet_state"]["objects"][0]["_serialized_obj_name"] == "ObjState"     # the reference's tagging
