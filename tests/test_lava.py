@@ -205,3 +205,15 @@ def test_normalization_handoff_between_processes(tmp_path):
     ip._save_norm_info(path, info0)
     _, again = ip.create_datasets(cfg, seed=0, normalization_path=path, process_index=0)
     assert np.allclose(again["action_min"], info0["action_min"])
+
+
+def test_clip_checkpoint_conversion_script(tmp_path):
+    from language_table.train import download_clip_flax_ckpt as conv
+    from language_table.train.networks.clip_text import ClipTextEncoder
+    src = ClipTextEncoder(vocab_size=300, features=64, num_heads=1, num_layers=2, out_features=32, context_length=16)
+    ck = {("transformer." + k if k.startswith("resblocks.") else k): v for k, v in src.state_dict().items()}
+    ck["visual.proj"] = torch.zeros(2)
+    torch.save(ck, tmp_path / "clip.pt")
+    out = conv.convert(str(tmp_path / "clip.pt"), str(tmp_path / "ckpt"))
+    back = torch.load(out)
+    assert set(back) == set(src.state_dict()) and all(torch.equal(back[k], v) for k, v in src.state_dict().items())
