@@ -40,7 +40,14 @@ NAME_TO_OBSERVATIONS = dict(zip(space_names_list(), observations_list()))
 NAME_TO_INF_OBSERVATIONS = dict(zip(space_names_list(), observations_list(False)))
 
 
-class TransformerNetworkTestUtils(unittest.TestCase):
+try:                                    # the reference's tests decorate their cases with absl's parameterized
+    from absl.testing import parameterized as _parameterized
+    _Base = (_parameterized.TestCase, unittest.TestCase)
+except ImportError:                     # pragma: no cover - absl is optional here
+    _Base = (unittest.TestCase,)
+
+
+class TransformerNetworkTestUtils(*_Base):
     """``setUp`` defines what the reference's fixture defines: ``_state_space`` (observation space), ``_action_space`` (ordered:
     terminate_episode, world_vector, rotation_delta, gripper_closedness_action), ``_policy_info_space``, constant
     ``_train_observation`` / ``_train_action`` of shape [b, t, ...] and ``_inference_observation`` / ``_inference_action`` of

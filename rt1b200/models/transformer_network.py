@@ -209,6 +209,23 @@ class TransformerNetwork(nn.Module):
         seq = torch.cat((context_image_tokens, zeros), dim=2)
         return seq.view(batch_size, -1, self._token_embedding_size)
 
+    def _transformer_call(self, context_image_tokens: torch.Tensor, action_tokens: torch.Tensor, batch_size: int,
+                          attention_mask: torch.Tensor) -> torch.Tensor:
+        """Logits ``[b, t * tokens_per_step, vocab]`` for explicit image / action tokens and an explicit mask — the reference's
+        entry point of this name (``transformer_network.py:364-375``; its causality test drives it directly).  The action
+        tokens enter as zeros, as in the reference, so only their positions matter."""
+        if not context_image_tokens.is_floating_point():           # the reference's test feeds one-hot int64 tokens
+            context_image_tokens = context_image_tokens.to(self._action_token_emb.weight.dtype)
+        seq = self._assemble_input_token_sequence(context_image_tokens, action_tokens, batch_size)
+        out, self._attention_scores = self._transformer(seq, attention_mask.to(seq.device) if attention_mask is not None else None)
+        return out
+
+    def _transformer_call_and_slice(self, *args, slice_start: int = 0, slice_length: int = 1, **kwargs):
+        """``(argmax token [b, slice_length], logits [b, slice_length, vocab])`` of a slice of :meth:`_transformer_call`'s output
+        (reference ``:393-409``: one action token of one time step during autoregressive inference)."""
+        logits = self._transformer_call(*args, **kwargs)[:, slice_start:slice_start + slice_length]
+        return torch.argmax(logits, dim=-1), logits
+
     def _decode(self, context_image_tokens, positions: Optional[torch.Tensor] = None):
         """Run the decoder; return logits at ``positions`` (``[P]`` shared or ``[b, P]`` per sample) or all."""
         b = context_image_tokens.shape[0]
