@@ -27,6 +27,15 @@ from rt1b200.train.trainer import RT1Module, Trainer  # noqa: F401  (RT1Module r
 RT1_Lightning = RT1Module   # name used by code written against the reference (language_table/eval/main_rt1.py:24)
 
 
+def print_keys(obj, prefix: str = "") -> None:
+    """Print the dotted paths of the leaves of a nested dict (the reference's checkpoint-inspection helper, ``:184-189``)."""
+    if isinstance(obj, dict):
+        for key, value in obj.items():
+            print_keys(value, prefix + str(key) + ".")
+    else:
+        print(prefix[:-1])
+
+
 def build_parser() -> ArgumentParser:
     p = ArgumentParser()
     p.add_argument("--device", type=str, default="gpu")

@@ -2,6 +2,7 @@
 four shapes, the fixed 1/4/8-block boards, the pole variants and the seeded train/test split of all 4..10-block
 combinations."""
 import enum
+import collections
 import itertools
 
 import numpy as np
@@ -22,6 +23,13 @@ SHAPES = ["moon", "cube", "star", "pentagon"]
 ALL_BLOCKS = ["_".join(cs) for cs in itertools.product(COLORS, SHAPES)]
 POLE = "purple_pole"
 DUMMY_START_BLOCK = "red_moon"
+# URDF of every block in the reference's path convention (its ``blocks.py:85-112``; resolved against the local asset directory
+# by ``utils_pybullet.resolve_asset_path`` / ``rt1b200.envs.assets``), red / blue / yellow / green x moon / cube / star / pentagon
+_ASSET_PREFIX = "third_party/py/language_table/environments/assets/"
+BLOCK_URDF_PATHS = collections.OrderedDict(
+    (f"{c}_{sh}", f"{_ASSET_PREFIX}blocks/{c}_{sh}.urdf") for c in ("red", "blue", "yellow", "green")
+    for sh in ("moon", "cube", "star", "pentagon"))
+POLE_URDF_PATHS = collections.OrderedDict(purple_pole=f"{_ASSET_PREFIX}blocks/purple_pole.urdf")
 
 FIXED_1_COMBINATION = ["green_star"]
 FIXED_4_COMBINATION = ("red_moon", "blue_cube", "green_star", "yellow_pentagon")

@@ -32,3 +32,7 @@ EFFECTOR_RADIUS = 0.0125
 BLOCK_RADIUS = 0.02
 BLOCK_HEIGHT = 0.02
 CONTROL_HZ = 10.0
+
+# asset paths in the reference's convention (``constants.py:22,42``): Bullet's ground plane and the board
+PLANE_URDF_PATH = "third_party/bullet/examples/pybullet/gym/pybullet_data/plane.urdf"
+WORKSPACE_URDF_PATH = "third_party/py/language_table/environments/assets/workspace_real.urdf"

@@ -5,8 +5,15 @@ import numpy as np
 from scipy.spatial import transform
 
 
+class NoCopyAsDict:
+    """Mixin for dataclasses: ``asdict()`` without the deep copy ``dataclasses.asdict`` performs (reference ``pose3d.py:24-37``)."""
+
+    def asdict(self):
+        return {f.name: getattr(self, f.name) for f in dataclasses.fields(self)}
+
+
 @dataclasses.dataclass
-class Pose3d:
+class Pose3d(NoCopyAsDict):
     rotation: transform.Rotation
     translation: np.ndarray
 

@@ -186,3 +186,54 @@ def read_pybullet_state(filename: str):
         raise ValueError("incompatible state data (version %d, expected %d)" % (data["state_version"], PYBULLET_STATE_VERSION))
     data["pybullet_state"] = _deserialize_pybullet_state(data["pybullet_state"])
     return data
+
+
+# ------------------------------------------------------------------------------------------------ assets without Bullet
+def resolve_asset_path(file_path: str) -> str:
+    """A URDF / OBJ path in the reference's convention → a file on this machine.  The reference's ``load_urdf`` (``:61-91``)
+    tries the path as given, then strips ``third_party/py/`` and resolves ``language_table/environments/...`` against the
+    package root (Bullet's own data under ``third_party/bullet/...`` comes from ``pybullet_data``, which does not exist
+    here).  The same rules, against the asset directory ``rt1b200.envs.assets.find_asset_dir()`` found."""
+    import os
+    from rt1b200.envs import assets
+    if os.path.exists(file_path):
+        return file_path
+    rel = file_path[len("third_party/py/"):] if file_path.startswith("third_party/py/language_table/") else file_path
+    marker = "language_table/environments/assets/"
+    root = assets.find_asset_dir()
+    if marker in rel and root is not None:
+        cand = os.path.join(root, rel.split(marker, 1)[1])
+        if os.path.exists(cand):
+            return cand
+    raise FileNotFoundError("Cannot load the URDF file {}".format(file_path))
+
+
+def load_urdf(pybullet_client, file_path, *args, **kwargs):
+    """Without a physics engine "loading" a URDF means parsing its visuals: returns the list of
+    ``{"tris": [T,3,3], "rgb": (r,g,b)}`` records of :func:`rt1b200.envs.assets.load_urdf_visuals` (``pybullet_client`` and
+    Bullet's placement arguments are accepted and ignored)."""
+    from rt1b200.envs import assets
+    return assets.load_urdf_visuals(resolve_asset_path(file_path))
+
+
+def add_visual_sphere(client=None, center=(0, 0, 0), radius=0.1, rgba=(0.5, 0.5, 0.5, 0.5)):
+    """GUI debugging aid of the reference (a non-colliding sphere in the Bullet visualiser): there is no visualiser on this
+    box, so this only returns the description of what would have been drawn."""
+    return {"center": tuple(center), "radius": float(radius), "rgba": tuple(rgba)}
+
+
+def reset_camera_pose(env, view_type):
+    """The reference re-aims the Bullet debug visualiser's camera (``:208-241``).  No visualiser here; returns the
+    ``(distance, yaw_deg, pitch_deg, target)`` it would have set, computed with the same rules."""
+    if view_type == "POLICY":
+        viewm, _, position, lookat, _ = env.calc_camera_params((180, 320))
+        euler = matrix_to_rotation(pybullet_mat_to_numpy_4x4(viewm)[0:3, 0:3]).as_euler("xyz", degrees=False)
+        pitch, yaw = euler[1], -euler[2]
+        distance = float(np.linalg.norm(np.asarray(position) - np.asarray(lookat)) * 0.6)
+        target = np.asarray(lookat)
+    elif view_type == "TOP_DOWN":
+        target, _ = get_workspace(env)
+        distance, yaw, pitch = 0.5, np.pi / 2, -(np.pi / 2 - 1e-5)
+    else:
+        raise ValueError("unsupported view_type %s" % view_type)
+    return distance, 360 * yaw / (2.0 * np.pi), 360 * pitch / (2.0 * np.pi), target

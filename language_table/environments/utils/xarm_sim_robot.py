@@ -24,6 +24,12 @@ from scipy.spatial import transform
 
 from language_table.environments.utils.pose3d import Pose3d
 
+# URDFs the reference loads into Bullet (``:24-36``); kept as names for callers, the kinematics below restate the xArm6 chain
+XARM_URDF_PATH = "third_party/bullet/examples/pybullet/gym/pybullet_data/xarm/xarm6_robot.urdf"
+XARM_WHITE_URDF_PATH = "third_party/bullet/examples/pybullet/gym/pybullet_data/xarm/xarm6_robot_white.urdf"
+SUCTION_URDF_PATH = "third_party/py/language_table/environments/assets/suction/suction-head-long.urdf"
+CYLINDER_URDF_PATH = "third_party/py/language_table/environments/assets/suction/cylinder.urdf"
+CYLINDER_REAL_URDF_PATH = "third_party/py/language_table/environments/assets/suction/cylinder_real.urdf"
 HOME_JOINT_POSITIONS = np.deg2rad([0, -20, -80, 0, 100, -30])
 
 # (xyz, roll) of each joint's origin in its parent link; every joint turns about its own z axis

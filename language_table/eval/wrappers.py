@@ -44,6 +44,28 @@ class UseTokenWrapper(_Wrapper):
         return obs
 
 
+def crop_test_image(images, random_crop_factor):
+    """The centre crop that is the mean of the training-time random crop (reference ``wrappers.py:99-123``): a window of
+    ``int(H * f) x int(W * f)`` at offset ``((H - H f) // 2, (W - W f) // 2)``.  ``images``: ``[H, W, C]`` or ``[N, H, W, C]``
+    (numpy or torch)."""
+    h, w = images.shape[-3], images.shape[-2]
+    sh, sw = h * random_crop_factor, w * random_crop_factor
+    oy, ox = int((h - sh) // 2), int((w - sw) // 2)
+    return images[..., oy:oy + int(sh), ox:ox + int(sw), :]
+
+
+def resize_images(images, target_height=None, target_width=None):
+    """Bilinear resize (half-pixel centres, no antialiasing — ``tf.image.resize``'s default, reference ``:126-137``) of
+    ``[H, W, C]`` or ``[N, H, W, C]`` images to float32 ``[..., target_height, target_width, C]``."""
+    assert target_height and target_width
+    x = torch.as_tensor(np.asarray(images)).float()
+    single = x.dim() == 3
+    x = (x[None] if single else x).permute(0, 3, 1, 2)
+    y = torch.nn.functional.interpolate(x, size=(target_height, target_width), mode="bilinear", align_corners=False, antialias=False)
+    y = y.permute(0, 2, 3, 1)
+    return (y[0] if single else y).numpy()
+
+
 class CentralCropImageWrapper(_Wrapper):
     def __init__(self, env, target_height=256, target_width=456, random_crop_factor=0.95):
         super().__init__(env)

@@ -15,6 +15,40 @@ import argparse
 from rt1b200.data.episodes import convert_rlds, iter_exported_episodes, write_synthetic_dataset  # noqa: F401
 
 
+NUM_TRAIN, NUM_VAL, NUM_TEST = 7800, 100, 100          # the reference's split of the first 8 000 episodes (``:35-37``)
+
+
+def decode_inst(inst) -> str:
+    """Zero-padded utf-8 byte array → instruction string."""
+    from rt1b200.data.episodes import decode_instruction
+    return decode_instruction(inst)
+
+
+def create_episode(path, raw_episode, embed=False, embed_model=None, path_embed=None):
+    """One RLDS episode → ``path`` (``.npy`` of flat step dicts); with ``embed`` also ``path_embed`` with every instruction
+    replaced by ``embed_model([text])[0]`` (reference ``:13-33``; ``embed_model`` is any callable on a list of strings — the
+    Universal Sentence Encoder upstream).  Embeddings are cached per distinct instruction."""
+    import copy
+    import os
+
+    import numpy as np
+    from rt1b200.data.episodes import flatten_rlds_episode, save_episode
+    steps = flatten_rlds_episode(raw_episode)
+    save_episode(path, steps)
+    if embed:
+        cache, out = {}, []
+        for st in steps:
+            st = copy.deepcopy(st)
+            text = decode_inst(st["instruction"])
+            if text not in cache:
+                e = embed_model([text])[0]
+                cache[text] = np.asarray(e.numpy() if hasattr(e, "numpy") else e, np.float32)
+            st["instruction"] = cache[text]
+            out.append(st)
+        os.makedirs(os.path.dirname(os.path.abspath(path_embed)), exist_ok=True)
+        save_episode(path_embed, out)
+
+
 def _encoder(kind: str, use_path=None):
     if kind == "use":
         import tensorflow_hub as hub           # not installed offline: raises a clear ImportError

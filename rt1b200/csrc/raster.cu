@@ -90,18 +90,19 @@ RT1_API int rt1_raster(const float* tris, const int* ntris, int max_tris, unsign
   return rt1_check_launch("rt1_raster");
 }
 
-// Centre crop of `crop` (fraction of each side, e.g. 0.95) + bilinear resize (half-pixel centres, no antialias) of
+// Centre crop of `crop` (fraction of each side, e.g. 0.95; whole pixels, see rt1_crop_resize) + bilinear resize (half-pixel centres, no antialias) of
 // uint8 HWC frames to float32 CHW in [0, 1]: the policy's `image` observation.
 __global__ void crop_resize_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, int E, int H, int W, int OH, int OW,
-                                   float y0, float x0, float sy, float sx) {
+                                   float y0, float x0, float sy, float sx, int ylo, int yhi, int xlo, int xhi) {
   const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long total = (long)E * OH * OW;
   if (i >= total) return;
   const int ox = (int)(i % OW), oy = (int)((i / OW) % OH);
   const long e = i / ((long)OW * OH);
   const float fy = y0 + (oy + 0.5f) * sy - 0.5f, fx = x0 + (ox + 0.5f) * sx - 0.5f;
-  const int iy0 = max(0, min(H - 1, (int)floorf(fy))), ix0 = max(0, min(W - 1, (int)floorf(fx)));
-  const int iy1 = min(H - 1, iy0 + 1), ix1 = min(W - 1, ix0 + 1);
+  // the crop window is its own image: samples are clamped to it, like a resize of the cropped frame
+  const int iy0 = max(ylo, min(yhi, (int)floorf(fy))), ix0 = max(xlo, min(xhi, (int)floorf(fx)));
+  const int iy1 = min(yhi, iy0 + 1), ix1 = min(xhi, ix0 + 1);
   const float ty = fminf(fmaxf(fy - iy0, 0.f), 1.f), tx = fminf(fmaxf(fx - ix0, 0.f), 1.f);
   const uint8_t* img = in + (size_t)e * H * W * 3;
 #pragma unroll
@@ -114,10 +115,14 @@ __global__ void crop_resize_kernel(const uint8_t* __restrict__ in, float* __rest
 }
 
 RT1_API int rt1_crop_resize(const unsigned char* in, float* out, int E, int H, int W, int OH, int OW, float crop, cudaStream_t stream) {
-  const float ch = H * crop, cw = W * crop;
-  const float y0 = (H - ch) * 0.5f, x0 = (W - cw) * 0.5f;
+  // the reference's evaluation crop (language_table/eval/wrappers.py:99-118): a window of int(H f) x int(W f) pixels at the
+  // integer offset ((H - H f) // 2, (W - W f) // 2), then a resize of that window
+  const float ch = floorf(H * crop), cw = floorf(W * crop);
+  const float y0 = floorf((H - H * crop) * 0.5f), x0 = floorf((W - W * crop) * 0.5f);
   const long total = (long)E * OH * OW;
-  crop_resize_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>(in, out, E, H, W, OH, OW, y0, x0, ch / OH, cw / OW);
+  const int ylo = (int)y0, xlo = (int)x0, yhi = ylo + (int)ch - 1, xhi = xlo + (int)cw - 1;
+  crop_resize_kernel<<<rt1_cdiv(total, 256), 256, 0, stream>>>(in, out, E, H, W, OH, OW, y0, x0, ch / OH, cw / OW, ylo, yhi < H ? yhi : H - 1,
+                                                               xlo, xhi < W ? xhi : W - 1);
   return rt1_check_launch("rt1_crop_resize");
 }
 

@@ -63,12 +63,15 @@ def render(tris: torch.Tensor, ntris: torch.Tensor, H: int = C.IMAGE_HEIGHT, W: 
 def crop_resize_reference(frames: torch.Tensor, out_h: int, out_w: int, crop: float = 0.95) -> torch.Tensor:
     """uint8 [E,H,W,3] → float32 [E,3,out_h,out_w] in [0,1]; same sampling rule as the kernel (half-pixel centres)."""
     E, H, W, _ = frames.shape
-    ch, cw = H * crop, W * crop
-    y0, x0 = (H - ch) / 2, (W - cw) / 2
+    import math
+    ch, cw = float(math.floor(H * crop)), float(math.floor(W * crop))           # whole-pixel window, like the reference's
+    y0, x0 = float(math.floor((H - H * crop) / 2)), float(math.floor((W - W * crop) / 2))   # crop_test_image
     fy = y0 + (torch.arange(out_h, dtype=torch.float32) + 0.5) * (ch / out_h) - 0.5
     fx = x0 + (torch.arange(out_w, dtype=torch.float32) + 0.5) * (cw / out_w) - 0.5
-    iy0 = fy.floor().clamp(0, H - 1).long(); ix0 = fx.floor().clamp(0, W - 1).long()
-    iy1 = (iy0 + 1).clamp(max=H - 1); ix1 = (ix0 + 1).clamp(max=W - 1)
+    ylo, xlo = int(y0), int(x0)
+    yhi, xhi = min(H - 1, ylo + int(ch) - 1), min(W - 1, xlo + int(cw) - 1)      # samples stay inside the crop window
+    iy0 = fy.floor().clamp(ylo, yhi).long(); ix0 = fx.floor().clamp(xlo, xhi).long()
+    iy1 = (iy0 + 1).clamp(max=yhi); ix1 = (ix0 + 1).clamp(max=xhi)
     ty = (fy - iy0).clamp(0, 1)[None, :, None, None]; tx = (fx - ix0).clamp(0, 1)[None, None, :, None]
     f = frames.float().cpu()
     v = (f[:, iy0][:, :, ix0] * (1 - tx) + f[:, iy0][:, :, ix1] * tx) * (1 - ty) + \

@@ -43,6 +43,11 @@ _B0_STAGES = (
     (5, 4, 112, 192, 6, 2),
     (3, 1, 192, 320, 6, 1),
 )
+# Initialiser descriptions the reference keeps from the Keras original (``film_efficientnet_encoder.py:101-117``); the PyTorch
+# modules below realise them as kaiming-style fan-out normal (convolutions) and fan-out uniform (the classifier head).
+CONV_KERNEL_INITIALIZER = {"class_name": "VarianceScaling", "config": {"scale": 2.0, "mode": "fan_out", "distribution": "truncated_normal"}}
+DENSE_KERNEL_INITIALIZER = {"class_name": "VarianceScaling", "config": {"scale": 1.0 / 3.0, "mode": "fan_out", "distribution": "uniform"}}
+
 DEFAULT_BLOCKS_ARGS = [
     dict(kernel_size=k, repeats=r, in_size=i, out_size=o, expand_ratio=e, id_skip=True, strides=s, se_ratio=0.25)
     for (k, r, i, o, e, s) in _B0_STAGES

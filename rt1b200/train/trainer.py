@@ -51,6 +51,16 @@ class RT1Module(nn.Module):
         self.state_space = self.model._input_tensor_space
         self.action_space = self.model._output_tensor_space
 
+    def configure_optimizers(self):
+        """The reference's Lightning hook (``distribute_train.py:99-110``): plain ``torch.optim.Adam`` + ``MultiStepLR`` over this
+        module's parameters, in Lightning's dict layout.  :class:`Trainer` does not call it — its optimizer is the fused
+        reduce + AdamW over flat buffers — but code that drives the module with its own loop (or with Lightning) gets the
+        reference's recipe."""
+        optimizer = torch.optim.Adam(self.parameters(), lr=self.args.lr)
+        scheduler = torch.optim.lr_scheduler.MultiStepLR(optimizer, list(getattr(self.args, "milestones", [])), gamma=0.1)
+        return {"optimizer": optimizer, "interval": "epoch",
+                "lr_scheduler": {"scheduler": scheduler, "monitor": "val_loss", "frequency": 1}}
+
     def loss_fn(self, x: torch.Tensor) -> torch.Tensor:
         return torch.mean(x.float())
 
