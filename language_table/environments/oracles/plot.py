@@ -40,3 +40,62 @@ def plot_plan(path: Optional[Sequence[Sequence[float]]], obstacles: Iterable[Tup
         with open(filename, "wb") as f:
             f.write(f"P6 {size} {size} 255\n".encode() + img.tobytes())
     return img
+
+
+DEBUG_IMAGE_PATH = "/tmp/rrt_debug_img.png"
+
+
+class PlotRRT:
+    """The reference's debug plotter (``plot.py:28-114``) on the numpy rasteriser above: same constructor and the same
+    ``animation`` → ``save_debug_image`` sequence, a PNG at ``image_path`` as the product.
+
+    ``obs_boundary``: wall rectangles ``(x, y, w, h)`` — their hull is the drawn region; ``obs_circle``: discs
+    ``(x, y, r)``.  ``nodelist`` is either a list of tree edges ``((x0, y0), (x1, y1))`` or a planner exposing
+    ``nodes`` / ``parent`` (``rrt_star.RRTStar``)."""
+
+    def __init__(self, x_start, x_goal, obs_boundary, obs_circle, image_path=DEBUG_IMAGE_PATH, size: int = 400):
+        self._x_start, self._x_goal = x_start, x_goal
+        self._obs_bound, self._obs_circle = list(obs_boundary), list(obs_circle)
+        self._image_path, self._size = image_path, size
+        self.fig = None
+        self._edges, self._path, self.name = [], None, ""
+
+    def _bounds(self):
+        if not self._obs_bound:
+            pts = np.asarray([self._x_start, self._x_goal] + [c[:2] for c in self._obs_circle], float)
+            return pts.min(0) - 0.1, pts.max(0) + 0.1
+        r = np.asarray(self._obs_bound, float)
+        return np.array([r[:, 0].min(), r[:, 1].min()]), np.array([(r[:, 0] + r[:, 2]).max(), (r[:, 1] + r[:, 3]).max()])
+
+    def plot_grid(self, name):
+        self.name = name
+        self._render()
+
+    def plot_visited(self, nodelist, animation=False):
+        if hasattr(nodelist, "nodes") and hasattr(nodelist, "parent"):
+            self._edges = [(nodelist.nodes[p], n) for n, p in zip(nodelist.nodes, nodelist.parent) if p >= 0]
+        else:
+            self._edges = list(nodelist or [])
+        self._render()
+
+    def plot_path(self, path):
+        self._path = None if path is None or len(path) == 0 else [np.asarray(p, float) for p in path]
+        self._render()
+
+    def animation(self, nodelist, path, name, animation=False):
+        self.name = name
+        self.plot_visited(nodelist, animation)
+        self.plot_path(path)
+
+    def _render(self):
+        lo, hi = self._bounds()
+        self.fig = plot_plan(self._path, self._obs_circle, self._x_start, self._x_goal, bounds=(lo, hi), edges=self._edges,
+                             size=self._size)
+        return self.fig
+
+    def fig_to_array(self, figure=None):
+        return self._render() if figure is None else np.asarray(figure)
+
+    def save_debug_image(self):
+        from rt1b200.utils.video import write_apng
+        return write_apng(self._image_path, self.fig_to_array()[None])

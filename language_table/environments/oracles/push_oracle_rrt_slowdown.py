@@ -34,7 +34,10 @@ PREBLOCK_OFFSET = 0.05
 EE_BACKOFF_OFFSETS = (0.06, 0.07, 0.08)
 RRT_STEP_LENGTH = 0.05
 RRT_GOAL_SAMPLE_RATE = 0.1
+RRT_SEARCH_RADIUS = 0.5                     # neighbourhood scale of the choose-parent / rewire steps
 RRT_MAX_ITERS = 1024
+REPLAN_IF_FAILURE = True                    # a failed search is retried every RETRY_FOR_NEW_PLAN_EVERY steps
+EPS = 1e-5
 RETRY_FOR_NEW_PLAN_EVERY = 10
 ADVANCE_TO_NEXT_EE_SUBGOAL_THRESHOLD = 0.01
 EE_RRT_STEP_LENGTH = 0.025
@@ -45,8 +48,9 @@ RETRY_FOR_NEW_EE_PLAN_EVERY = 1
 EXTRA_BOUNDARY_BUFFER = 0.04
 BEYOND_TABLE_THRESHOLD = 2.0
 # planning may leave the official workspace on the three sides that are not next to the robot
-PLAN_BOUNDS = ((constants.X_MIN, constants.Y_MIN - EXTRA_BOUNDARY_BUFFER),
-               (constants.X_MAX + EXTRA_BOUNDARY_BUFFER, constants.Y_MAX + EXTRA_BOUNDARY_BUFFER))
+X_RANGE_RRT = (constants.X_MIN, constants.X_MAX + EXTRA_BOUNDARY_BUFFER)
+Y_RANGE_RRT = (constants.Y_MIN - EXTRA_BOUNDARY_BUFFER, constants.Y_MAX + EXTRA_BOUNDARY_BUFFER)
+PLAN_BOUNDS = ((X_RANGE_RRT[0], Y_RANGE_RRT[0]), (X_RANGE_RRT[1], Y_RANGE_RRT[1]))
 SLOWDOWN_TABLE = ((0.02, 0.2), (0.04, 0.3), (0.06, 0.4), (0.08, 0.5), (0.1, 0.6))      # (distance below, step factor)
 
 
@@ -245,7 +249,7 @@ class ObstacleOrientedPushOracleBoard2dRRT(oriented_push_oracle.OrientedPushOrac
         if self._plan is None:
             self.get_plan(state)
         self._replan_counter += 1
-        if self._need_replan and self._replan_counter % RETRY_FOR_NEW_PLAN_EVERY == 0:
+        if REPLAN_IF_FAILURE and self._need_replan and self._replan_counter % RETRY_FOR_NEW_PLAN_EVERY == 0:
             self.get_plan(state)
         block, goal = self._goal_and_block(state)
         while len(self._plan) > 1 and np.linalg.norm(self._plan[0] - block) <= ADVANCE_TO_NEXT_SUBGOAL_THRESHOLD:

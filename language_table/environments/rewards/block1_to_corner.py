@@ -9,6 +9,8 @@ from language_table.environments.rewards import block2absolutelocation as b2a, t
 
 BUFFER = 0.08
 X_MIN, X_MAX, Y_MIN, Y_MAX = 0.15, 0.6, -0.3048, 0.3048
+CENTER_X = (X_MAX - X_MIN) / 2.0 + X_MIN
+CENTER_Y = (Y_MAX - Y_MIN) / 2.0 + Y_MIN
 BLOCK2ABSOLUTELOCATION_TARGET_DISTANCE = 0.08
 
 

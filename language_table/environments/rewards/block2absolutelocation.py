@@ -8,8 +8,10 @@ from language_table.environments import blocks as blocks_module
 from language_table.environments.rewards import reward as base_reward, synonyms, task_info
 
 X_BUFFER = 0.025
-X_MIN, X_MAX = 0.15 - X_BUFFER, 0.6 - X_BUFFER
-Y_MIN, Y_MAX = -0.3048, 0.3048
+X_MIN_REAL, X_MAX_REAL = 0.15, 0.6                # the reachable board; the named locations sit X_BUFFER closer to the arm
+Y_MIN_REAL, Y_MAX_REAL = -0.3048, 0.3048
+X_MIN, X_MAX = X_MIN_REAL - X_BUFFER, X_MAX_REAL - X_BUFFER
+Y_MIN, Y_MAX = Y_MIN_REAL, Y_MAX_REAL
 CENTER_X = (X_MAX - X_MIN) / 2.0 + X_MIN
 CENTER_Y = (Y_MAX - Y_MIN) / 2.0 + Y_MIN
 BLOCK2ABSOLUTELOCATION_TARGET_DISTANCE = 0.115

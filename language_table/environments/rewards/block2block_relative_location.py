@@ -32,8 +32,15 @@ DIRECTIONS = {"up": [UP, 0.0], "down": [DOWN, 0.0], "left": [0.0, LEFT], "right"
               "diagonal_up_left": [UP, LEFT], "diagonal_up_right": [UP, RIGHT],
               "diagonal_down_left": [DOWN, LEFT], "diagonal_down_right": [DOWN, RIGHT]}
 DIRECTION_IDS = list(DIRECTIONS.keys())
-UNIQUE_TASK_STRINGS = {s: i for i, s in enumerate(sorted(
-    f"{a}-{b}-{d}" for a in blocks_module.ALL_BLOCKS for b in blocks_module.ALL_BLOCKS for d in DIRECTIONS))}
+
+
+def get_unique_task_strings():
+    """``"<block>-<target block>-<direction>"`` → task id, ids in sorted-string order (reference ``:84-98``)."""
+    return {s: i for i, s in enumerate(sorted(
+        f"{a}-{b}-{d}" for a in blocks_module.ALL_BLOCKS for b in blocks_module.ALL_BLOCKS for d in DIRECTIONS))}
+
+
+UNIQUE_TASK_STRINGS = get_unique_task_strings()
 NUM_UNIQUE_TASKS = len(UNIQUE_TASK_STRINGS)
 
 BLOCK2BLOCKRELATIVELOCATION_VERBS = ["move the", "push the", "put the", "bring the", "slide the"]

@@ -27,6 +27,22 @@ class Block2LocationTaskInfo:
 
 
 @dataclass
+class Block2LineTaskInfo:
+    """Push a block onto a line of the board (declared by the reference, ``task_info.py:42``; no reward uses it there either)."""
+    instruction: str
+    block: str
+    target_translation: Any
+
+
+@dataclass
+class Block2PoleTaskInfo:
+    """Push a block to one of the coloured poles (``task_info.py:50``; the poles are listed in ``blocks.POLE_URDF_PATHS``)."""
+    instruction: str
+    block1: str
+    goal: str
+
+
+@dataclass
 class Block2RelativeLocationTaskInfo:
     instruction: str
     block: str

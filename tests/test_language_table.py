@@ -140,8 +140,34 @@ def test_point_separate_and_play_rewards():
     rew = separate_blocks.SeparateBlocksReward(100.0, np.random.RandomState(0), 0, blocks.LanguageTableBlockVariants.BLOCK_4)
     info = rew.reset(env._compute_state(), list(blocks.FIXED_4_COMBINATION))
     assert info == task_info.FAILURE or "from the" in info.instruction
-    pr = play.PlayReward(100.0, np.random.RandomState(0), 0, None)
-    assert isinstance(pr.reset({}, list(blocks.FIXED_8_COMBINATION)).instruction, str) and pr.reward({}) == (0.0, False)
+    env8 = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8, None, seed=0)
+    env8.reset()
+    pr = play.PlayReward(100.0, np.random.RandomState(0), 0, blocks.LanguageTableBlockVariants.BLOCK_8)
+    info = pr.reset(env8._compute_state(), list(blocks.FIXED_8_COMBINATION))
+    assert isinstance(info.instruction, str) and info.block1 != info.block2 and pr.reward({}) == (0.0, False)
+
+
+def test_play_instruction_families():
+    """Family sizes of the reference's long-horizon vocabulary (rewards/play.py): 100 training + 25 held-out 4-block
+    instructions, eleven 8-block families sampled family-first."""
+    train, test = play.get_100_4block_instructions(), play.get_100_4block_instructions(return_train=False)
+    assert len(train) == 100 and len(test) == 25 and not set(train) & set(test)
+    assert train == play.get_100_4block_instructions()                       # seeded split, no global random state touched
+    assert [len(f) for f in play.four_block_families()] == [29, 288, 216, 72, 48]
+    sizes = {f.__name__: len(f()) for f in play.EIGHT_BLOCK_FAMILIES if f is not play.blocks_in_order_outer_edge}
+    assert sizes == {"get_sort_tasks": 1, "colors_in_locations": 72576, "group_color_pairs": 24, "get_colors_in_lines": 24,
+                     "group_color_pairs_in_locations": 432, "get_line_tasks": 11, "get_surround_tasks": 8,
+                     "all_blocks_in_location": 9, "k_blocks_in_location_i_rest_in_location_j": 504,
+                     "get_shape_instructions": 22}
+    rng = np.random.RandomState(0)
+    draws = [play.get_random_8block_instruction(rng) for _ in range(400)]
+    assert all(len(d) <= play.MAX_INSTRUCTION_LENGTH for d in draws)
+    # family-first sampling: the single-instruction family shows up about 1 time in 11, not 1 in 114 000
+    assert 15 <= draws.count("group the blocks by color") <= 70
+    edge = play.sample_outer_edge(rng)
+    assert edge.startswith("put the ") and all(b in edge for b in play.BLOCKS8)
+    pr4 = play.PlayReward(100.0, np.random.RandomState(0), 0, blocks.LanguageTableBlockVariants.BLOCK_4)
+    assert pr4._sample_instruction() in train
 
 
 def test_rrt_star_routes_around_an_obstacle():
@@ -340,3 +366,51 @@ def test_reference_format_state_file_round_trip(tmp_path):
     import gzip, json
     raw = json.loads(gzip.open(f, "rb").read().decode())
     assert raw["pybullet_state"]["objects"][0]["_serialized_obj_name"] == "ObjState"     # the reference's tagging
+
+
+def test_rrt_entry_point_predicates_and_debug_plot(tmp_path):
+    """The planner's public entry point and helpers (reference oracles/rrt_star.py:25-85, :275-332; plot.py:28)."""
+    from language_table.environments.oracles import plot
+    path, ok = rrt_star.get_shortest_path_no_collisions(
+        [0.2, 0.0], [0.5, 0.0], (0.15, 0.6), (-0.3, 0.3), [(0.35, 0.0)], [0.05], delta=0.015, step_length=0.05,
+        goal_sample_rate=0.1, search_radius=0.5, iter_max=1024, rng=np.random.RandomState(0))
+    assert ok and np.allclose(path[0], [0.5, 0.0]) and np.allclose(path[-1], [0.2, 0.0])       # goal first
+    for a, b in zip(path[:-1], path[1:]):
+        assert not rrt_star.is_collision(a, b, 0.0, [(0.35, 0.0, 0.064)], [])
+    # boxed in: no route, the straight line is handed back (or an error on request)
+    ring = [(0.2 + 0.05 * np.cos(t), 0.05 * np.sin(t)) for t in np.linspace(0, 2 * np.pi, 12, endpoint=False)]
+    args = dict(x_range=(0.15, 0.6), y_range=(-0.3, 0.3), obstacle_xy=ring, obstacle_widths=[0.02] * 12, delta=0.005,
+                step_length=0.05, goal_sample_rate=0.1, search_radius=0.5, iter_max=64)
+    path, ok = rrt_star.get_shortest_path_no_collisions([0.2, 0.0], [0.5, 0.0], **args)
+    assert not ok and len(path) == 2 and np.allclose(path[0], [0.5, 0.0])
+    with pytest.raises(ValueError):
+        rrt_star.get_shortest_path_no_collisions([0.2, 0.0], [0.5, 0.0], raise_error_on_plan_failure=True, **args)
+    assert rrt_star.is_collision([0.2, 0.0], [0.5, 0.0], 0.015, [(0.35, 0.0, 0.05)], [])
+    assert not rrt_star.is_collision([0.2, 0.2], [0.5, 0.2], 0.015, [(0.35, 0.0, 0.05)], [])
+    assert rrt_star.inside_boundary([0.15, 0.0], 0.01, [(0.15, -0.3, 0.01, 0.6)])
+    assert rrt_star.is_intersect_circle([0, 0], [1, 0], [0.5, 0.05], 0.04, 0.02)
+    assert not rrt_star.is_intersect_circle([0, 0], [1, 0], [1.5, 0.0], 0.04, 0.02)            # foot point beyond the end
+    assert np.allclose(rrt_star.segment_distances([0, 0], [1, 0], [[0.5, 0.3], [2.0, 0.0]]), [0.3, 1.0])
+    planner = rrt_star.RRTStar([0.2, 0.0], [0.5, 0.0], [(0.35, 0.0, 0.06)], ((0.15, -0.3), (0.6, 0.3)),
+                               rng=np.random.RandomState(0))
+    route = planner.plan()
+    p = plot.PlotRRT([0.2, 0.0], [0.5, 0.0], [(0.15, -0.3, 0.45, 0.6)], [(0.35, 0.0, 0.06)], image_path=str(tmp_path / "rrt.png"))
+    p.animation(planner, route, "rrt*")
+    out = p.save_debug_image()
+    assert open(out, "rb").read(8) == b"\x89PNG\r\n\x1a\n" and p.fig.shape == (400, 400, 3)
+    assert (p.fig == np.array([220, 30, 30], np.uint8)).all(-1).any()                           # the path is drawn
+
+
+def test_oriented_oracle_pushing_info():
+    from language_table.environments.oracles.oriented_push_oracle import OrientedPushOracle, PushingInfo
+    env = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8, block2block.BlockToBlockReward, seed=0)
+    env.reset()
+    oracle = OrientedPushOracle(env)
+    info = oracle.get_pushing_info()
+    assert isinstance(info, PushingInfo) and len(info.obstacle_poses) == 7
+    assert abs(np.linalg.norm(info.xy_dir_block_to_target) - 1) < 1e-6 and -np.pi <= info.theta_error <= np.pi
+    # behind the block, on the line to the target: no orientation error
+    state = dict(env._compute_state())
+    state["effector_target_translation"] = info.xy_pre_block
+    assert abs(oracle.get_pushing_info(state).theta_error) < 1e-6
+    assert np.allclose(oracle.rotate(np.pi / 2, [1.0, 0.0]), [0.0, 1.0]) and abs(oracle.get_theta_from_vector([0, 2]) - np.pi / 2) < 1e-9
