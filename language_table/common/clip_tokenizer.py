@@ -68,13 +68,32 @@ class ClipTokenizer:
         self.cache[token] = " ".join(word)
         return self.cache[token]
 
+    @staticmethod
+    def clean(text: str) -> str:
+        """Strip, collapse white space, lower-case (``clip_tokenizer.py:72-84``; like there, no HTML un-escaping)."""
+        return re.sub(r"\s+", " ", text.strip()).lower()
+
     def tokenize(self, text: str) -> List[int]:
-        text = re.sub(r"\s+", " ", text.strip()).lower()
-        ids = []
-        for tok in _PAT.findall(text):
-            tok = "".join(self.byte_encoder[b] for b in tok.encode("utf-8"))
-            ids.extend(self.encoder.get(t, self.unk) for t in self.bpe(tok).split(" "))
-        return ids
+        return self.tokenize_with_offsets(text)[0]
+
+    def tokenize_with_offsets(self, text: str):
+        """``(ids, begin, end)``: one entry per BPE piece; ``begin`` / ``end`` are byte offsets (end exclusive) into the
+        UTF-8 encoding of the cleaned text (``clean``), so ``clean(text).encode()[b:e]`` is the piece's surface form.
+        The reference's method of the same name (``clip_tokenizer.py:71-110``) returns ragged tensors with the same three
+        parts; its end offsets also count the four characters of the ``</w>`` marker, which are not text."""
+        text = self.clean(text)
+        ids, begin, end = [], [], []
+        char_to_byte = np.cumsum([0] + [len(c.encode("utf-8")) for c in text])
+        for m in _PAT.finditer(text):
+            at = int(char_to_byte[m.start()])
+            tok = "".join(self.byte_encoder[b] for b in m.group().encode("utf-8"))      # one symbol per byte
+            for piece in self.bpe(tok).split(" "):
+                n = len(piece[:-4] if piece.endswith("</w>") else piece)
+                ids.append(self.encoder.get(piece, self.unk))
+                begin.append(at)
+                end.append(at + n)
+                at += n
+        return ids, begin, end
 
 
 def tokenize_text(text, tokenizer: ClipTokenizer, vocab_size: int = 49408, context_length: int = 77) -> np.ndarray:

@@ -40,7 +40,8 @@ FIXED_8_COMBINATION_WPOLE = FIXED_8_COMBINATION + (POLE,)
 
 MIN_K, MAX_K = 4, 10
 _all = [c for k in range(MIN_K, MAX_K + 1) for c in itertools.combinations(ALL_BLOCKS, k)]
-np.random.RandomState(seed=0).shuffle(_all)
+combo_rng = np.random.RandomState(seed=0)      # the seeded shuffle behind the train / test split of the combinations
+combo_rng.shuffle(_all)
 ALL_COMBINATIONS = _all
 _cut = int(len(_all) * 0.9)
 TRAIN_COMBINATIONS, TEST_COMBINATIONS = _all[:_cut], _all[_cut:]

@@ -132,8 +132,13 @@ class LanguageTable:
 
     @property
     def pybullet_client(self):
-        """The reference hands out its Bullet client here (``:362``); there is no physics engine behind this environment."""
-        return None
+        """The reference hands out its Bullet client here (``:362``).  There is no physics engine behind this environment;
+        the object returned answers the body / joint queries and resets of that interface from the board and the
+        kinematic arm (``utils/board_client.py``), which is what ``ObjState.get_bullet_state / set_bullet_state`` need."""
+        if getattr(self, "_board_client", None) is None:
+            from language_table.environments.utils.board_client import BoardClient
+            self._board_client = BoardClient(self)
+        return self._board_client
 
     def calc_camera_params(self, image_size):
         """``(view matrix, projection matrix, position, look-at, up)`` of the table camera for ``image_size`` = (H, W), in
@@ -275,38 +280,34 @@ class LanguageTable:
         target effector pose), ``robot_end_effectors`` / ``targets`` = [], ``objects`` = one ObjState per block of the block
         mode (pose = ((x, y, z), quaternion); blocks that are off the table sit at the reference's parking height), plus the
         encoded instruction.  ``utils_pybullet.write_pybullet_state`` writes it to a file the reference can read."""
-        from scipy.spatial import transform
         from language_table.environments.utils import utils_pybullet as up
-        b = self._board
-        objects = []
-        for i, name in enumerate(self._all_blocks):
-            on = bool(b.block_mask[0, i])
-            xy = b.block_xy[0, i].tolist()
-            quat = transform.Rotation.from_euler("z", float(b.block_yaw[0, i])).as_quat().tolist()
-            objects.append(up.ObjState(obj_id=i, base_pose=((xy[0], xy[1], 0.0 if on else -1.0), tuple(quat))))
-        joints = self._robot.get_joint_positions().tolist() if self._robot is not None else []
-        target = self._effector_pose(b.effector_target[0].tolist())
-        robot = up.XarmState(obj_id=-1, base_pose=((0.0, 0.0, 0.0), (0.0, 0.0, 0.0, 1.0)), joint_state=[(q, 0.0) for q in joints],
-                             target_effector_pose=target, goal_translation=None)
+        client = self.pybullet_client
+        objects = [up.ObjState.get_bullet_state(client, i) for i in range(len(self._all_blocks))]
+        target = self._effector_pose(self._board.effector_target[0].tolist())
+        if self._robot is not None:
+            robot = up.XarmState.get_bullet_state(client, client.robot_id, target_effector_pose=target, goal_translation=None)
+        else:
+            robot = up.XarmState(obj_id=client.robot_id, base_pose=((0.0, 0.0, 0.0), (0.0, 0.0, 0.0, 1.0)),
+                                 target_effector_pose=target, goal_translation=None)
         return {"robots": [robot], "robot_end_effectors": [], "targets": [], "objects": objects,
                 "instruction": [int(v) for v in self._instruction.tolist()]}
 
     def import_pybullet_state(self, state: Dict[str, Any]) -> None:
         """Inverse of :meth:`export_pybullet_state` (block poses, arm joints, effector target, instruction)."""
-        from scipy.spatial import transform
         b = self._board
+        client = self.pybullet_client
         for i, obj in enumerate(state["objects"][:len(self._all_blocks)]):
-            (x, y, z), quat = obj.base_pose
-            b.block_xy[0, i] = torch.tensor([x, y], dtype=torch.float32)
-            b.block_yaw[0, i] = float(transform.Rotation.from_quat(quat).as_euler("xyz")[2])
-            b.block_mask[0, i] = z > -0.5
+            obj.set_bullet_state(client, i)
         robot = state["robots"][0]
         if robot.target_effector_pose is not None:
             xy = torch.tensor(np.asarray(robot.target_effector_pose.translation[:2], np.float32))
             b.effector_target[0] = xy
             b.effector[0] = xy
         if self._robot is not None and len(robot.joint_state):
-            self._robot.reset_joints([js[0] for js in robot.joint_state])
+            if len(robot.joint_info) == len(robot.joint_state):
+                robot.set_bullet_state(client, client.robot_id)
+            else:                                               # a record without joint info (older files): positions only
+                self._robot.reset_joints([js[0] for js in robot.joint_state])
         if state.get("instruction") is not None:
             self._instruction = np.asarray(state["instruction"], np.int32)
             self._instruction_str = self.decode_instruction(self._instruction)

@@ -96,6 +96,10 @@ class BlockToBlockRelativeLocationReward(base_reward.LanguageTableReward):
 
     instruction_for = _sample_instruction
 
+    def instruction_for(self, pushing_block, target_block, direction, blocks_on_table):
+        """A freshly sampled phrasing of a given (block, target block, direction) task (reference ``:274-277``)."""
+        return self._sample_instruction(pushing_block, target_block, direction, blocks_on_table)
+
     def reset(self, state, blocks_on_table):
         for _ in range(101):
             block, target_block = self._sample_objects(blocks_on_table)

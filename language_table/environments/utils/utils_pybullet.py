@@ -8,9 +8,12 @@
 import dataclasses
 import gzip
 import json
-from typing import Any, Dict, List, Optional
+from typing import Any, Dict, List, Optional, Tuple
 
 import numpy as np
+
+Vec3 = Tuple[float, float, float]
+Vec4 = Tuple[float, float, float, float]
 
 from rt1b200.envs import camera as _cam
 
@@ -71,13 +74,51 @@ def pixel_to_workspace(xy, viewm, projm, cam_width, cam_height):
     return ray_to_plane_test(o, d, *get_workspace())
 
 
+def _lists_to_tuple(obj):
+    return tuple(_lists_to_tuple(v) for v in obj) if isinstance(obj, (list, tuple)) else obj
+
+
 @dataclasses.dataclass
 class ObjState:
+    """One body of the scene: base pose ((x, y, z), quaternion), base velocity, and per joint its info tuple and state
+    tuple — read from / written to a Bullet-style client (reference ``utils_pybullet.py:252-332``;
+    ``board_client.BoardClient`` is the client of this environment, a real ``pybullet`` client works as well)."""
     obj_id: int
     base_pose: Any
     base_vel: Any = ((0, 0, 0), (0, 0, 0))
     joint_info: Any = ()
     joint_state: Any = ()
+
+    @staticmethod
+    def _get_joint_info(client, obj_id, joint_index):
+        return tuple(v.decode("utf-8") if isinstance(v, bytes) else v for v in client.getJointInfo(obj_id, joint_index))
+
+    @staticmethod
+    def get_bullet_state(client, obj_id) -> "ObjState":
+        n = client.getNumJoints(obj_id)
+        return ObjState(obj_id=obj_id, base_pose=client.getBasePositionAndOrientation(obj_id),
+                        base_vel=client.getBaseVelocity(obj_id),
+                        joint_info=tuple(ObjState._get_joint_info(client, obj_id, i) for i in range(n)),
+                        joint_state=tuple(client.getJointState(obj_id, i) for i in range(n)))
+
+    def set_bullet_state(self, client, obj_id) -> None:
+        """Hard-set the body to this record.  The joints must be the ones the record was taken from: count, order and
+        info tuples are checked before anything is written to a joint."""
+        xyz, quat = self.base_pose
+        client.resetBasePositionAndOrientation(obj_id, xyz, quat)
+        vel, ang_vel = self.base_vel if self.base_vel is not None else ((0, 0, 0), (0, 0, 0))
+        client.resetBaseVelocity(obj_id, vel, ang_vel)
+        n = client.getNumJoints(obj_id)
+        if n != len(self.joint_info) or n != len(self.joint_state):
+            raise ValueError("Incorrect number of joint info state pairs.")
+        for i, (info, state) in enumerate(zip(self.joint_info, self.joint_state)):
+            if info[0] != i:
+                raise ValueError("Joint index mismatch.")
+            current = ObjState._get_joint_info(client, obj_id, i)
+            if _lists_to_tuple(current) != _lists_to_tuple(info):
+                raise ValueError("joint_info mismatch %s vs %s (expected)" % (str(current), str(info)))
+        for i, state in enumerate(self.joint_state):
+            client.resetJointState(obj_id, i, targetValue=state[0], targetVelocity=state[1])
 
     def serialize(self) -> Dict[str, Any]:
         return {"obj_id": self.obj_id, "base_pose": _tolist(self.base_pose), "base_vel": _tolist(self.base_vel),
@@ -85,19 +126,39 @@ class ObjState:
 
     @staticmethod
     def deserialize(data: Dict[str, Any]) -> "ObjState":
-        return ObjState(data["obj_id"], data["base_pose"], data.get("base_vel"), data.get("joint_info", ()), data.get("joint_state", ()))
+        return ObjState(data["obj_id"], _lists_to_tuple(data["base_pose"]), _lists_to_tuple(data.get("base_vel")),
+                        _lists_to_tuple(data.get("joint_info", ())), _lists_to_tuple(data.get("joint_state", ())))
 
 
 @dataclasses.dataclass
 class XarmState(ObjState):
+    """The arm: an ``ObjState`` plus the controller's set point and the goal marker (reference ``:335-373``)."""
     target_effector_pose: Optional[Any] = None
     goal_translation: Optional[Any] = None
+
+    @staticmethod
+    def get_bullet_state(client, obj_id, target_effector_pose=None, goal_translation=None) -> "XarmState":
+        if goal_translation is not None:
+            goal_translation = tuple(np.asarray(goal_translation).tolist())
+        base = ObjState.get_bullet_state(client, obj_id)
+        return XarmState(obj_id=base.obj_id, base_pose=base.base_pose, base_vel=base.base_vel, joint_info=base.joint_info,
+                         joint_state=base.joint_state, target_effector_pose=target_effector_pose,
+                         goal_translation=goal_translation)
 
     def serialize(self) -> Dict[str, Any]:
         d = super().serialize()
         d["target_effector_pose"] = None if self.target_effector_pose is None else self.target_effector_pose.serialize()
-        d["goal_translation"] = None if self.goal_translation is None else _tolist(self.goal_translation)
+        d["goal_translation"] = [] if self.goal_translation is None else _tolist(self.goal_translation)
         return d
+
+    @staticmethod
+    def deserialize(data: Dict[str, Any]) -> "XarmState":
+        from language_table.environments.utils.pose3d import Pose3d
+        tep, goal = data.get("target_effector_pose"), data.get("goal_translation")
+        base = ObjState.deserialize(data)
+        return XarmState(obj_id=base.obj_id, base_pose=base.base_pose, base_vel=base.base_vel, joint_info=base.joint_info,
+                         joint_state=base.joint_state, target_effector_pose=None if tep is None else Pose3d.deserialize(tep),
+                         goal_translation=_lists_to_tuple(goal) if goal else None)
 
 
 def _tolist(x):
@@ -154,11 +215,7 @@ def _deserialize_pybullet_state(state):
         if "_serialized_obj_name" in state:
             name, data = state["_serialized_obj_name"], state["_serialized_data"]
             if name == XarmState.__name__:
-                from language_table.environments.utils.pose3d import Pose3d
-                tep = data.get("target_effector_pose")
-                return XarmState(data["obj_id"], data["base_pose"], data.get("base_vel"), data.get("joint_info", ()),
-                                 data.get("joint_state", ()), None if tep is None else Pose3d.deserialize(tep),
-                                 data.get("goal_translation"))
+                return XarmState.deserialize(data)
             if name == ObjState.__name__:
                 return ObjState.deserialize(data)
             raise ValueError("Unsupported: %s" % name)

@@ -13,6 +13,14 @@ import numpy as np
 from rt1b200.data.episodes import load_episode, synthetic_episode
 
 
+# where the published RLDS datasets live (reference ``dataset_example.py:31-34``); not reachable offline — convert a
+# local TFDS copy with ``rlds_np_convert.py --tfds_dir`` and pass the result as ``--dataset_dir``
+dataset_paths = {
+    "language_table": "gs://gresearch/robotics/language_table/0.0.1/",
+    "language_table_sim": "gs://gresearch/robotics/language_table_sim/0.0.1/",
+}
+
+
 def decode_inst(inst) -> str:
     """Instructions stored as zero-padded utf-8 byte arrays (the simulator's format) → string."""
     return bytes(int(x) for x in np.asarray(inst).tolist() if x != 0).decode("utf-8")

@@ -1,5 +1,6 @@
 """Local BC training of LAVA on simulated Language-Table data (reference
 ``language_table/train/configs/language_table_sim_local.py:28-81``), conv/max-pool image encoder."""
+from language_table.examples.dataset_example import dataset_paths  # noqa: F401  (the upstream buckets, for reference)
 from language_table.train.configs import ConfigDict
 
 
@@ -25,6 +26,8 @@ def get_config():
     config.agent_name = "bc"
     config.agent = ConfigDict()
     config.agent.learning_rate = 1e-3
+    # [(file, [(prefix in the file, prefix in the model)])]; the reference points this at a converted CLIP text tower
+    # (``download_clip_flax_ckpt.py``) when ``lava_lang_encoder = "clip"``
     config.agent.pretrained_checkpoints = []
     config.agent.freeze_keys = ["text_encoder"]
 
@@ -47,3 +50,9 @@ def get_config():
     config.seed = 42
     config.trial = 0
     return config
+
+
+def get_hyper(h):
+    """Sweep definition for a launcher (reference ``:84-89``): one trial.  ``h`` is any object with ``product`` and
+    ``sweep`` — ``language_table.train.configs.Hyper`` is the local one."""
+    return h.product([h.sweep("config.trial", range(1))])

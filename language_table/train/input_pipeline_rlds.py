@@ -3,14 +3,15 @@
 The reference reads RLDS/TFDS episodes from GCS; offline the same step dictionaries come from this repository's per-episode
 ``.npy`` files (``rt1b200.data.episodes``, the format ``rlds_np_convert.py`` writes) or from the synthetic generator.
 Kept behaviour: terminal steps dropped, episodes front-padded with copies of the first step so that every step ends a window
-of ``sequence_length`` frames (``:105-176``), random crop of ``random_crop_factor`` of the area shared by the frames of a
-window + bilinear resize to the target size (``:326-389``), photometric distortions (brightness / contrast / saturation,
-``:391-458``), rgb scaled to [0, 1], actions normalised with the dataset statistics, a 512-d language embedding per step
+of ``sequence_length`` frames (``:105-176``), one random crop window of ``random_crop_factor`` of each side shared by the frames of a
+sequence + bilinear resize to the target size (``:326-389``), photometric distortions (brightness / saturation / hue /
+contrast, one level per sequence, ``:391-458``), rgb scaled to [0, 1], actions normalised with the dataset statistics, a 512-d language embedding per step
 under ``clip_embedding`` (the stored sentence embedding; the reference computes CLIP tokens/embeddings).
 """
+import dataclasses
 import glob
 import os
-from typing import Dict, Iterator, List, Optional
+from typing import Dict, Iterator, List, Optional, Tuple
 
 import numpy as np
 import torch
@@ -24,25 +25,115 @@ def _windows(episode: List[Dict], sequence_length: int):
         yield padded[end - sequence_length + 1:end + 1]
 
 
-def random_resized_crop(frames: torch.Tensor, factor: float, out_hw, rng: np.random.Generator, train: bool) -> torch.Tensor:
-    """frames uint8/float [t, h, w, 3] → float [t, H, W, 3]; one crop window per sequence (random in training, central in eval)."""
-    t, h, w, _ = frames.shape
-    ch, cw = max(1, int(round(h * np.sqrt(factor)))), max(1, int(round(w * np.sqrt(factor))))
-    y0 = int(rng.integers(0, h - ch + 1)) if train else (h - ch) // 2
-    x0 = int(rng.integers(0, w - cw + 1)) if train else (w - cw) // 2
-    x = frames[:, y0:y0 + ch, x0:x0 + cw].permute(0, 3, 1, 2).float()
-    x = F.interpolate(x, size=tuple(out_hw), mode="bilinear", align_corners=False)
-    return x.permute(0, 2, 3, 1)
+def _decode_frames(frames) -> torch.Tensor:
+    """uint8 array / tensor [t, h, w, 3] as it is; a sequence of encoded images (JPEG / PNG bytes, the RLDS storage
+    format) through Pillow."""
+    if torch.is_tensor(frames):
+        return frames
+    if isinstance(frames, np.ndarray) and frames.dtype != object and frames.dtype.kind not in "SU":
+        return torch.from_numpy(frames)
+    import io
+    from PIL import Image
+    return torch.from_numpy(np.stack([np.asarray(Image.open(io.BytesIO(bytes(f))).convert("RGB")) for f in frames]))
+
+
+@dataclasses.dataclass(frozen=True)
+class DecodeAndRandomResizedCrop:
+    """Decode, cut one window of ``random_crop_factor`` × height by ``random_crop_factor`` × width (whole pixels, the same
+    window for every frame of the sequence, its corner uniform over the offsets that keep it inside), scale to [0, 1],
+    bilinear-resize to ``resize_size`` (reference ``input_pipeline_rlds.py:326-387``).  ``None`` keeps the whole frame.
+    ``train=False`` takes the central window (what the evaluation wrappers do)."""
+    random_crop_factor: Optional[float] = None
+    resize_size: Tuple[int, int] = (180, 320)
+
+    def window(self, h: int, w: int, rng: np.random.Generator, train: bool = True):
+        if self.random_crop_factor is None:
+            return 0, 0, h, w
+        ch, cw = max(1, int(h * self.random_crop_factor)), max(1, int(w * self.random_crop_factor))
+        if train:
+            y0 = int(rng.integers(0, max(1, h - ch)))          # upper bound exclusive, like the reference's uniform draw
+            x0 = int(rng.integers(0, max(1, w - cw)))
+        else:
+            y0, x0 = (h - ch) // 2, (w - cw) // 2
+        return y0, x0, ch, cw
+
+    def __call__(self, frames, rng: np.random.Generator, train: bool = True) -> torch.Tensor:
+        frames = _decode_frames(frames)
+        y0, x0, ch, cw = self.window(frames.shape[1], frames.shape[2], rng, train)
+        x = frames[:, y0:y0 + ch, x0:x0 + cw].permute(0, 3, 1, 2).float() / 255.0
+        x = F.interpolate(x, size=tuple(self.resize_size), mode="bilinear", align_corners=False)
+        return x.permute(0, 2, 3, 1)
+
+
+def rgb_to_hsv(x: torch.Tensor) -> torch.Tensor:
+    """[..., 3] in [0, 1] → hue (turns, [0, 1)), saturation, value."""
+    r, g, b = x.unbind(-1)
+    v, _ = x.max(-1)
+    c = v - x.min(-1)[0]
+    safe = torch.where(c > 0, c, torch.ones_like(c))
+    h = torch.where(v == r, ((g - b) / safe) % 6.0, torch.where(v == g, (b - r) / safe + 2.0, (r - g) / safe + 4.0))
+    h = torch.where(c > 0, h / 6.0, torch.zeros_like(h))
+    s = torch.where(v > 0, c / torch.where(v > 0, v, torch.ones_like(v)), torch.zeros_like(v))
+    return torch.stack([h, s, v], -1)
+
+
+def hsv_to_rgb(x: torch.Tensor) -> torch.Tensor:
+    h, s, v = x.unbind(-1)
+    k = (torch.tensor([5.0, 3.0, 1.0], device=x.device, dtype=x.dtype) + h.unsqueeze(-1) * 6.0) % 6.0
+    return v.unsqueeze(-1) - (v * s).unsqueeze(-1) * torch.clamp(torch.minimum(k, 4.0 - k), 0.0, 1.0)
+
+
+@dataclasses.dataclass(frozen=True)
+class PhotometricDistortions:
+    """Brightness, saturation, hue, contrast — in that order, each with ONE random level for the whole sequence
+    (reference ``input_pipeline_rlds.py:390-452``; the ranges are its defaults).  Brightness adds a constant; saturation
+    scales S of HSV (clipped to [0, 1]); hue rotates H by a fraction of a turn; contrast scales the distance to the
+    per-frame, per-channel mean.  Like the TF ops the result is not clipped to [0, 1]."""
+    brightness_max_delta: float = 0.1
+    contrast_lower: float = 0.8
+    contrast_upper: float = 1.2
+    hue_max_delta: float = 0.03
+    saturation_lower: float = 0.8
+    saturation_upper: float = 1.2
+
+    def sample(self, rng: np.random.Generator) -> Dict[str, float]:
+        return {"brightness": float(rng.uniform(-self.brightness_max_delta, self.brightness_max_delta)),
+                "saturation": float(rng.uniform(self.saturation_lower, self.saturation_upper)),
+                "hue": float(rng.uniform(-self.hue_max_delta, self.hue_max_delta)),
+                "contrast": float(rng.uniform(self.contrast_lower, self.contrast_upper))}
+
+    def apply(self, frames: torch.Tensor, brightness=0.0, saturation=1.0, hue=0.0, contrast=1.0) -> torch.Tensor:
+        x = frames
+        if self.brightness_max_delta != 0.0:
+            x = x + brightness
+        change_s = self.saturation_lower != 1.0 or self.saturation_upper != 1.0
+        change_h = self.hue_max_delta != 0.0
+        if change_s or change_h:
+            hsv = rgb_to_hsv(x)
+            h, s, v = hsv.unbind(-1)
+            if change_s:
+                s = (s * saturation).clamp(0.0, 1.0)
+            if change_h:
+                h = (h + hue) % 1.0
+            x = hsv_to_rgb(torch.stack([h, s, v], -1))
+        if self.contrast_lower != 1.0 or self.contrast_upper != 1.0:
+            mean = x.mean(dim=(-3, -2), keepdim=True)
+            x = (x - mean) * contrast + mean
+        return x
+
+    def __call__(self, frames: torch.Tensor, rng: np.random.Generator) -> torch.Tensor:
+        """frames float [t, h, w, 3] in [0, 1]."""
+        return self.apply(frames, **self.sample(rng))
+
+
+def random_resized_crop(frames: torch.Tensor, factor: Optional[float], out_hw, rng: np.random.Generator, train: bool) -> torch.Tensor:
+    """Functional form of ``DecodeAndRandomResizedCrop``; values stay in the input's scale ([0, 255] for uint8 input)."""
+    return DecodeAndRandomResizedCrop(factor, tuple(out_hw))(frames, rng, train) * 255.0
 
 
 def photometric_distortions(frames: torch.Tensor, rng: np.random.Generator) -> torch.Tensor:
-    """frames float [t, h, w, 3] in [0, 1]; the same random brightness / contrast / saturation for the whole window."""
-    x = frames + float(rng.uniform(-0.125, 0.125))
-    mean = x.mean(dim=(1, 2, 3), keepdim=True)
-    x = (x - mean) * float(rng.uniform(0.5, 1.5)) + mean
-    gray = x.mean(dim=-1, keepdim=True)
-    x = (x - gray) * float(rng.uniform(0.5, 1.5)) + gray
-    return x.clamp(0.0, 1.0)
+    """Functional form of ``PhotometricDistortions`` with the default ranges."""
+    return PhotometricDistortions()(frames, rng)
 
 
 class WindowDataset:
@@ -52,6 +143,8 @@ class WindowDataset:
                  photometric: bool = True, train: bool = True, seed: int = 0):
         self.windows = [w for ep in episodes for w in _windows(ep, sequence_length)]
         self.hw, self.factor, self.photometric, self.train = tuple(target_hw), random_crop_factor, photometric, train
+        self.crop = DecodeAndRandomResizedCrop(random_crop_factor, self.hw)
+        self.distort = PhotometricDistortions()
         self.rng = np.random.default_rng(seed)
 
     def __len__(self):
@@ -59,10 +152,11 @@ class WindowDataset:
 
     def example(self, i: int) -> Dict:
         win = self.windows[i]
-        rgb = torch.from_numpy(np.stack([np.asarray(s["rgb"]) for s in win]))
-        rgb = random_resized_crop(rgb, self.factor or 1.0, self.hw, self.rng, self.train and self.factor is not None) / 255.0
+        first = win[0]["rgb"]
+        encoded = isinstance(first, (bytes, bytearray, np.bytes_))
+        rgb = self.crop([s["rgb"] for s in win] if encoded else np.stack([np.asarray(s["rgb"]) for s in win]), self.rng, self.train)
         if self.train and self.photometric:
-            rgb = photometric_distortions(rgb, self.rng)
+            rgb = self.distort(rgb, self.rng)
         emb = torch.from_numpy(np.stack([np.asarray(s["instruction"], dtype=np.float32) for s in win]))
         eff = torch.from_numpy(np.stack([np.asarray(s.get("effector_translation", np.zeros(2)), dtype=np.float32) for s in win]))
         return {"observation": {"rgb": rgb, "clip_embedding": emb, "effector_translation": eff},

@@ -61,8 +61,7 @@ class ResNetVisualEncoder(nn.Module):
         return self
 
     def forward(self, rgb):
-        x = F.interpolate((rgb - self.mean) / self.std, size=(224, 224), mode="bilinear", align_corners=False)
-        feats = self.resnet(x)
+        feats = self.resnet(normalize_image_resnet(rgb, self.mean, self.std))
         pyramid = [feats[0], feats[1]]
         x = feats[-1]
         for conv in self.convs:
@@ -72,12 +71,49 @@ class ResNetVisualEncoder(nn.Module):
         return pyramid
 
 
+def normalize_image_resnet(images: torch.Tensor, mean=None, std=None) -> torch.Tensor:
+    """NCHW images in [0, 1] → ImageNet-normalised, bilinearly resized (no antialiasing) to 224 × 224: the input
+    convention of the pretrained ResNet (reference ``lava.py:90-98``, NHWC there)."""
+    if mean is None:
+        mean = torch.tensor(ResNetVisualEncoder.MEAN, device=images.device, dtype=images.dtype).view(1, 3, 1, 1)
+        std = torch.tensor(ResNetVisualEncoder.STD, device=images.device, dtype=images.dtype).view(1, 3, 1, 1)
+    return F.interpolate((images - mean) / std, size=(224, 224), mode="bilinear", align_corners=False)
+
+
 def sinusoid_1d(length: int, dim: int, max_timescale: float = 1.0e4) -> torch.Tensor:
     pos = torch.arange(length, dtype=torch.float32)[:, None]
     div = torch.exp(torch.arange(0, dim, 2, dtype=torch.float32) * -(math.log(max_timescale) / dim))
     pe = torch.zeros(length, dim)
     pe[:, 0::2], pe[:, 1::2] = torch.sin(pos * div), torch.cos(pos * div)
     return pe[None]
+
+
+def sinusoidal_init(max_len: int, max_timescale: float = 1.0e4):
+    """Initialiser-shaped access to ``sinusoid_1d``: ``sinusoidal_init(n)(key, shape, dtype)`` → ``[1, n, shape[-1]]``
+    (the calling convention of the reference's version, ``lava.py:101-143``; ``key`` is ignored — the table is fixed)."""
+    def init(key=None, shape=None, dtype=torch.float32):
+        return sinusoid_1d(max_len, shape[-1], max_timescale).to(dtype or torch.float32)
+    return init
+
+
+class Add1DPositionEmbedding(nn.Module):
+    """``[b, t, d]`` + the fixed sinusoidal code of the first ``t`` positions (reference ``lava.py:146-186``).  The table
+    has ``rescale_from[0]`` rows when given, else ``max_len``, else it is built for the input's length; nothing is learned."""
+
+    def __init__(self, rescale_from: Optional[Sequence[int]] = None, max_len: Optional[int] = None):
+        super().__init__()
+        self.rescale_from, self.max_len = rescale_from, max_len
+        self._table = None
+
+    def forward(self, inputs: torch.Tensor) -> torch.Tensor:
+        if inputs.dim() != 3:
+            raise ValueError("Number of dimensions should be 3, but it is: %d" % inputs.dim())
+        length, dim = inputs.shape[1], inputs.shape[2]
+        rows = self.rescale_from[0] if self.rescale_from else (self.max_len or length)
+        t = self._table
+        if t is None or t.shape[1] != rows or t.shape[2] != dim or t.device != inputs.device or t.dtype != inputs.dtype:
+            t = self._table = sinusoidal_init(rows)(None, (1, rows, dim), None).to(device=inputs.device, dtype=inputs.dtype)
+        return inputs + t[:, :length]
 
 
 def positional_encoding2d(d_model: int, height: int, width: int) -> torch.Tensor:
@@ -153,13 +189,13 @@ class TemporalTransformer(nn.Module):
     def __init__(self, num_layers: int, d_model: int, num_heads: int, dff: int, sequence_length: int):
         super().__init__()
         self.d_model, self.inp, self.drop = d_model, dense(d_model, d_model), nn.Dropout(0.1)
-        self.register_buffer("pos", sinusoid_1d(sequence_length, d_model), persistent=False)
+        self.pos = Add1DPositionEmbedding(max_len=sequence_length)
         self.layers = nn.ModuleList([PrenormEncoderLayer(d_model, num_heads, 0.1, 0.0, dff) for _ in range(num_layers)])
         self.norm = nn.LayerNorm(d_model)
 
     def forward(self, x):                              # [b, t, d]
         x = self.inp(x) * math.sqrt(self.d_model)
-        x = self.drop(x + self.pos[:, :x.shape[1]])
+        x = self.drop(self.pos(x))
         for layer in self.layers:
             x = layer(x)
         return self.norm(x.mean(dim=1))

@@ -13,6 +13,16 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 
+def Conv1x1(cin: int, cout: int, stride: int = 1) -> nn.Conv2d:
+    """Bias-free 1×1 convolution (the reference's ``Conv1x1`` partial, ``resnet_v1.py:33``)."""
+    return nn.Conv2d(cin, cout, 1, stride, 0, bias=False)
+
+
+def Conv3x3(cin: int, cout: int, stride: int = 1) -> nn.Conv2d:
+    """Bias-free 3×3 SAME convolution (``resnet_v1.py:34``)."""
+    return nn.Conv2d(cin, cout, 3, stride, 1, bias=False)
+
+
 def _bn(c: int, zero_scale: bool = False) -> nn.BatchNorm2d:
     bn = nn.BatchNorm2d(c, momentum=0.1, eps=1e-5)
     if zero_scale:
@@ -25,13 +35,13 @@ class ResNetBlock(nn.Module):
 
     def __init__(self, cin: int, filters: int, stride: int = 1):
         super().__init__()
-        self.conv1 = nn.Conv2d(cin, filters, 3, stride, 1, bias=False)
+        self.conv1 = Conv3x3(cin, filters, stride)
         self.bn1 = _bn(filters)
-        self.conv2 = nn.Conv2d(filters, filters, 3, 1, 1, bias=False)
+        self.conv2 = Conv3x3(filters, filters)
         self.bn2 = _bn(filters, zero_scale=True)
         self.proj_conv = self.proj_bn = None
         if stride != 1 or cin != filters:
-            self.proj_conv = nn.Conv2d(cin, filters, 1, stride, bias=False)
+            self.proj_conv = Conv1x1(cin, filters, stride)
             self.proj_bn = _bn(filters)
 
     def forward(self, x):
@@ -48,15 +58,15 @@ class BottleneckResNetBlock(nn.Module):
 
     def __init__(self, cin: int, filters: int, stride: int = 1):
         super().__init__()
-        self.conv1 = nn.Conv2d(cin, filters, 1, bias=False)
+        self.conv1 = Conv1x1(cin, filters)
         self.bn1 = _bn(filters)
-        self.conv2 = nn.Conv2d(filters, filters, 3, stride, 1, bias=False)
+        self.conv2 = Conv3x3(filters, filters, stride)
         self.bn2 = _bn(filters)
-        self.conv3 = nn.Conv2d(filters, 4 * filters, 1, bias=False)
+        self.conv3 = Conv1x1(filters, 4 * filters)
         self.bn3 = _bn(4 * filters)
         self.proj_conv = self.proj_bn = None
         if stride != 1 or cin != 4 * filters:
-            self.proj_conv = nn.Conv2d(cin, 4 * filters, 1, stride, bias=False)
+            self.proj_conv = Conv1x1(cin, 4 * filters, stride)
             self.proj_bn = _bn(4 * filters)
 
     def forward(self, x):
@@ -69,14 +79,24 @@ class BottleneckResNetBlock(nn.Module):
         return F.relu(r + y)
 
 
+class ResNetStage(nn.Sequential):
+    """``stage_size`` blocks of ``filters``; only the first one strides (reference ``resnet_v1.py:96-114``).  PyTorch
+    modules need their input width up front, hence ``cin``; ``out_channels`` is what the next stage gets."""
+
+    def __init__(self, cin: int, stage_size: int, filters: int, block_cls: Type[nn.Module], first_block_strides: int = 1):
+        blocks = []
+        for j in range(stage_size):
+            blocks.append(block_cls(cin, filters, stride=first_block_strides if j == 0 else 1))
+            cin = filters * block_cls.expansion
+        super().__init__(*blocks)
+        self.out_channels = cin
+
+
 def _stages(block_cls: Type[nn.Module], stage_sizes: Sequence[int], width: int):
     stages, cin = nn.ModuleList(), width
     for i, n in enumerate(stage_sizes):
-        filters, blocks = width * 2 ** i, []
-        for j in range(n):
-            blocks.append(block_cls(cin, filters, stride=(1 if i == 0 else 2) if j == 0 else 1))
-            cin = filters * block_cls.expansion
-        stages.append(nn.Sequential(*blocks))
+        stages.append(ResNetStage(cin, n, width * 2 ** i, block_cls, first_block_strides=1 if i == 0 else 2))
+        cin = stages[-1].out_channels
     return stages, cin
 
 

@@ -95,20 +95,28 @@ class StdDenormalizer(StdNormalizer):
         return out + self.mean if mean_offset else out
 
 
-class MinMaxNormalizer:
-    """Maps [vmin, vmax] to [-1, 1]."""
+class MinMaxNormalizerBase:
+    """Centre and half-width of ``[vmin, vmax]``; the half-width is floored at ``EPS`` so a constant feature does not
+    divide by zero (reference ``normalization.py:306-314``)."""
 
     def __init__(self, vmin, vmax):
         self.vmin, self.vmax = np.asarray(vmin, np.float32), np.asarray(vmax, np.float32)
-        self.range = np.maximum(self.vmax - self.vmin, EPS)
+        self.mean_range = (self.vmin + self.vmax) / 2.0
+        self.half_range = np.maximum(0.5 * (self.vmax - self.vmin), EPS)
+
+
+class MinMaxNormalizer(MinMaxNormalizerBase):
+    """Maps [vmin, vmax] to [-1, 1]."""
 
     def __call__(self, vector, **kwargs):
-        return 2.0 * (vector - self.vmin) / self.range - 1.0
+        return (vector - self.mean_range) / self.half_range
 
 
-class MinMaxDenormalizer(MinMaxNormalizer):
+class MinMaxDenormalizer(MinMaxNormalizerBase):
+    """Maps [-1, 1] back to [vmin, vmax]."""
+
     def __call__(self, vector, **kwargs):
-        return (vector + 1.0) * 0.5 * self.range + self.vmin
+        return vector * self.half_range + self.mean_range
 
 
 def construct_normalizers(obs_stats: Dict, act_stats: Dict, skip_keys: Sequence[str] = ("rgb", "instruction")):

@@ -414,3 +414,50 @@ def test_oriented_oracle_pushing_info():
     state["effector_target_translation"] = info.xy_pre_block
     assert abs(oracle.get_pushing_info(state).theta_error) < 1e-6
     assert np.allclose(oracle.rotate(np.pi / 2, [1.0, 0.0]), [0.0, 1.0]) and abs(oracle.get_theta_from_vector([0, 2]) - np.pi / 2) < 1e-9
+
+
+def test_board_client_and_bullet_state_records(tmp_path):
+    """ObjState / XarmState.get_bullet_state, set_bullet_state (reference utils_pybullet.py:264-315, :341-351) against the
+    Bullet-style client the environment hands out."""
+    env = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_4, block2block.BlockToBlockReward, seed=0)
+    env.reset()
+    client = env.pybullet_client
+    assert client is env.pybullet_client and client.getNumBodies() == len(env._all_blocks) + 1
+    on = [i for i in range(len(env._all_blocks)) if client.getBasePositionAndOrientation(i)[0][2] == 0.0]
+    assert len(on) == 4                                                               # the others are parked below the table
+    rec = utils_pybullet.ObjState.get_bullet_state(client, on[0])
+    assert rec.joint_info == () and len(rec.base_pose[0]) == 3 and len(rec.base_pose[1]) == 4
+    arm = utils_pybullet.XarmState.get_bullet_state(client, client.robot_id, env._effector_pose([0.3, 0.0]), np.array([0.1, 0.2, 0.0]))
+    assert len(arm.joint_info) == len(arm.joint_state) == 6 and arm.joint_info[0][1] == "joint1" and arm.goal_translation == (0.1, 0.2, 0.0)
+    # move things, then restore from the records
+    before_xy, before_q = env._board.block_xy[0, on[0]].clone(), env._robot.get_joint_positions().copy()
+    client.resetBasePositionAndOrientation(on[0], (0.4, 0.1, 0.0), (0.0, 0.0, 0.0, 1.0))
+    client.resetJointState(client.robot_id, 2, targetValue=0.5)
+    assert abs(client.getJointState(client.robot_id, 2)[0] - 0.5) < 1e-9
+    assert np.allclose(client.getBasePositionAndOrientation(on[0])[0], (0.4, 0.1, 0.0), atol=1e-6)
+    rec.set_bullet_state(client, on[0])
+    arm.set_bullet_state(client, client.robot_id)
+    assert torch.allclose(env._board.block_xy[0, on[0]], before_xy) and np.allclose(env._robot.get_joint_positions(), before_q)
+    # a record of another body does not fit: joint count / info are checked first
+    with pytest.raises(ValueError):
+        arm.set_bullet_state(client, on[0])
+    bad = dataclasses_replace(arm, joint_info=tuple((i,) + ("other",) + tuple(info[2:]) for i, info in enumerate(arm.joint_info)))
+    with pytest.raises(ValueError):
+        bad.set_bullet_state(client, client.robot_id)
+    with pytest.raises(ValueError):
+        client.getBasePositionAndOrientation(99)
+    # through the serialised form and back
+    again = utils_pybullet.XarmState.deserialize(json_roundtrip(arm.serialize()))
+    assert again.joint_info == arm.joint_info and again.goal_translation == arm.goal_translation
+    assert np.allclose(again.target_effector_pose.translation, arm.target_effector_pose.translation)
+    again.set_bullet_state(client, client.robot_id)
+
+
+def dataclasses_replace(obj, **kw):
+    import dataclasses
+    return dataclasses.replace(obj, **kw)
+
+
+def json_roundtrip(x):
+    import json
+    return json.loads(json.dumps(x))

@@ -111,6 +111,13 @@ def test_clip_bpe_tokenizer():
     ids = tok.tokenize("  Push   the RED block! ")
     assert ids[0] == enc["push</w>"] and ids[1] == enc["the</w>"]
     assert ids[-1] == enc["!</w>"]
+    # offsets point into the cleaned text, in bytes, piece by piece (multi-byte characters count their bytes)
+    ids2, begin, end = tok.tokenize_with_offsets("  Push   thé RED block! ")
+    clean = tok.clean("  Push   thé RED block! ").encode()
+    assert clean == "push thé red block!".encode() and len(ids2) == len(begin) == len(end)
+    assert (begin[0], end[0]) == (0, 4) and clean[begin[-1]:end[-1]] == b"!"
+    assert b"".join(clean[b:e] for b, e in zip(begin, end)) == clean.replace(b" ", b"")
+    assert all(b0 < e0 <= b1 for (b0, e0), b1 in zip(zip(begin, end), begin[1:] + [len(clean)]))
     out = clip_tokenizer.tokenize_text(["push the block", "push"], tok, vocab_size=len(enc))
     assert out.shape == (2, 77) and out[0, 0] == len(enc) - 2 and out[1, 2] == len(enc) - 1 and out[1, 3] == 0
 
@@ -217,3 +224,112 @@ def test_clip_checkpoint_conversion_script(tmp_path):
     out = conv.convert(str(tmp_path / "clip.pt"), str(tmp_path / "ckpt"))
     back = torch.load(out)
     assert set(back) == set(src.state_dict()) and all(torch.equal(back[k], v) for k, v in src.state_dict().items())
+
+
+def test_lava_train_state_metrics_and_multi_step(tmp_path):
+    """TrainState / TrainMetrics / flattened_traversal (reference train/bc.py:32-47, :237), pretrained-checkpoint key
+    replacement (bc.py:92-108), multi_train_step / merge_batch_stats / the run's side files (train/train.py)."""
+    import csv
+    import os
+    from language_table.train import bc
+    from language_table.train.configs import Hyper, apply_overrides
+    m = bc.TrainMetrics.single_from_model_output(loss=1.0, learning_rate=1e-3).merge(
+        bc.TrainMetrics.single_from_model_output(loss=3.0, learning_rate=5e-4))
+    out = m.compute()
+    assert out["loss"] == 2.0 and abs(out["loss_std"] - 1.0) < 1e-12 and out["learning_rate"] == 5e-4
+    assert bc.TrainMetrics.empty().merge(m).compute() == out
+    labels = bc.flattened_traversal(lambda path, v: "/".join(path) + ":" + str(v))({"a": {"b": 1, "c": {"d": 2}}, "e": 3})
+    assert labels == {"a": {"b": "a/b:1", "c": {"d": "a/c/d:2"}}, "e": "e:3"}
+
+    cfg = _small(language_table_sim_local.get_config())
+    cfg.num_train_steps, cfg.checkpoint_every_steps, cfg.log_loss_every_steps, cfg.num_steps_per_train_iter = 6, 3, 2, 2
+    res = train_lib.train(cfg, str(tmp_path / "run"), device="cpu", verbose=False)
+    agent = res["agent"]
+    assert res["steps"] == 6 and len(res["losses"]) == 6
+    rows = list(csv.DictReader(open(tmp_path / "run" / "metrics.csv")))
+    assert [int(r["step"]) for r in rows] == [2, 4, 6] and all(float(r["loss_std"]) >= 0 for r in rows)
+    assert abs(float(rows[0]["loss"]) - sum(res["losses"][:2]) / 2) < 1e-6
+    overview = open(tmp_path / "run" / "parameters.txt").read()
+    assert "trainable" in overview and f"total: {sum(p.numel() for p in agent.model.parameters()):,}" in overview
+    assert os.path.exists(tmp_path / "run" / "hparams.json")
+    assert sorted(os.listdir(tmp_path / "run" / "checkpoints")) == ["ckpt_3.pt", "ckpt_6.pt"]
+
+    state, initial = agent.create_train_state()
+    assert isinstance(state, bc.TrainState) and state.step == 6 and initial.count == 0
+    assert set(state.params) == {n for n, _ in agent.model.named_parameters()} and "observation_statistics" in state.norm_info
+    assert state.replace(step=7).step == 7 and state.step == 6
+    flat = [v for v in str(agent.frozen_labels()).replace("'", " ").split() if v in ("adam", "zero")]
+    assert len(flat) == len(state.params) and "adam" in flat
+    assert train_lib.merge_batch_stats(agent) is agent                       # one process: nothing to average
+
+    # a second agent picks up one sub-tree of the first run's checkpoint under another prefix
+    ck = train_lib.latest_checkpoint(str(tmp_path / "run"))
+    sd = torch.load(ck, weights_only=False)["params"]
+    prefix = next(k for k in sd if sd[k].dim() >= 2).split(".")[0]
+    renamed = {"old." + k: v for k, v in sd.items() if k.startswith(prefix + ".")}
+    torch.save(renamed, tmp_path / "part.pt")
+    model2 = train_lib.create_model(cfg)
+    agent2 = bc.BCAgent(model2, cfg.sequence_length, 1e-3, {}, {}, None, None,
+                        pretrained_checkpoints=[(str(tmp_path / "part.pt"), [("old." + prefix, prefix)])])
+    assert len(agent2.loaded_pretrained) == len(renamed)
+    sd2 = model2.state_dict()
+    assert all(torch.equal(sd2[k[4:]], v) for k, v in renamed.items())
+
+    sweep = language_table_sim_local.get_hyper(Hyper)
+    assert sweep == [{"config.trial": 0}] and apply_overrides(cfg, {"config.agent.learning_rate": 0.5}).agent.learning_rate == 0.5
+
+
+def test_lava_two_process_training(tmp_path):
+    """pmap / pmean of the reference as two gloo processes: tests/_lava_worker.py."""
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29641", os.path.join(here, "_lava_worker.py"), str(tmp_path / "run")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, OMP_NUM_THREADS="2"))
+    assert r.returncode == 0 and "LAVA_WORKER_OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_lava_image_transforms():
+    """DecodeAndRandomResizedCrop / PhotometricDistortions (reference train/input_pipeline_rlds.py:326-452)."""
+    import colorsys
+    import io
+    from PIL import Image
+    from language_table.train import input_pipeline_rlds as ip
+    rng = np.random.default_rng(0)
+    frames = np.random.default_rng(1).integers(0, 256, (3, 40, 60, 3), dtype=np.uint8)
+    crop = ip.DecodeAndRandomResizedCrop(0.95, (18, 32))
+    # the factor applies to each side, in whole pixels; offsets stay inside; one window for the whole sequence
+    for _ in range(50):
+        y0, x0, ch, cw = crop.window(40, 60, rng)
+        assert (ch, cw) == (38, 57) and 0 <= y0 < 2 and 0 <= x0 < 3
+    out = crop(frames, rng)
+    assert out.shape == (3, 18, 32, 3) and 0.0 <= float(out.min()) and float(out.max()) <= 1.0
+    assert crop.window(40, 60, rng, train=False) == (1, 1, 38, 57)
+    whole = ip.DecodeAndRandomResizedCrop(None, (40, 60))(frames, rng)
+    assert torch.allclose(whole, torch.from_numpy(frames).float() / 255.0, atol=1e-6)
+    # encoded frames (the RLDS storage format) are decoded first
+    def png(a):
+        buf = io.BytesIO()
+        Image.fromarray(a).save(buf, format="PNG")
+        return buf.getvalue()
+    assert torch.equal(ip.DecodeAndRandomResizedCrop(None, (40, 60))([png(f) for f in frames], rng), whole)
+
+    x = torch.rand(2, 6, 5, 3)
+    hsv = ip.rgb_to_hsv(x)
+    ref = torch.tensor([[[colorsys.rgb_to_hsv(*map(float, x[t, i, j])) for j in range(5)] for i in range(6)] for t in range(2)])
+    assert torch.allclose(hsv, ref, atol=1e-5) and torch.allclose(ip.hsv_to_rgb(hsv), x, atol=1e-5)
+    pd = ip.PhotometricDistortions()
+    assert torch.allclose(pd.apply(x), x, atol=1e-5)                                      # neutral levels: identity
+    assert torch.allclose(pd.apply(x, brightness=0.05), x + 0.05, atol=1e-5)
+    gray = pd.apply(x, saturation=0.0)
+    assert torch.allclose(gray, x.max(-1, keepdim=True)[0].expand_as(x), atol=1e-5)       # S = 0 leaves V on every channel
+    c = pd.apply(x, contrast=0.0)
+    assert torch.allclose(c, x.mean(dim=(1, 2), keepdim=True).expand_as(x), atol=1e-5)    # per-frame, per-channel mean
+    third = pd.apply(torch.tensor([[[[1.0, 0.0, 0.0]]]]), hue=1.0 / 3.0)
+    assert torch.allclose(third, torch.tensor([[[[0.0, 1.0, 0.0]]]]), atol=1e-5)          # red a third of a turn on: green
+    levels = [pd.sample(rng) for _ in range(200)]
+    assert all(abs(l["brightness"]) <= 0.1 and 0.8 <= l["contrast"] <= 1.2 and abs(l["hue"]) <= 0.03
+               and 0.8 <= l["saturation"] <= 1.2 for l in levels)
+    assert ip.PhotometricDistortions(0.0, 1.0, 1.0, 0.0, 1.0, 1.0)(x, rng) is x           # everything switched off
