@@ -1,5 +1,6 @@
 """RRT* in the plane with disc obstacles (reference ``environments/oracles/rrt_star.py:88``: pure-python RRT* used by the
 push oracle to route a block, and then the effector, around the other blocks)."""
+import collections
 import math
 from typing import List, Optional, Sequence, Tuple
 
@@ -90,7 +91,41 @@ def get_shortest_path_no_collisions(xy_start, xy_goal, x_range, y_range, obstacl
     return [p for p in path[::-1]], True
 
 
+class Node:
+    """A point with a parent link — the record the reference's planner is built on (``rrt_star.py:335-341``).  The
+    planner below keeps its tree in flat lists instead; ``RRTStar.node(i)`` builds these on request."""
+
+    def __init__(self, n):
+        self.x, self.y = float(n[0]), float(n[1])
+        self.parent = None
+
+
+class FIFOQueue:
+    """First in, first out (``rrt_star.py:344-357``); used to walk a re-parented subtree breadth first."""
+
+    def __init__(self):
+        self.queue = collections.deque()
+
+    def empty(self) -> bool:
+        return not self.queue
+
+    def put(self, node) -> None:
+        self.queue.append(node)
+
+    def get(self):
+        return self.queue.popleft()
+
+
 class RRTStar:
+    """RRT* over a flat tree: ``nodes[i]`` (a point), ``parent[i]`` (an index, -1 at the root), ``cost[i]`` (path length
+    from the root), ``children[i]``.  One iteration = sample (``get_random_node``) → nearest tree node
+    (``nearest_neighbor``) → step towards the sample (``new_state``) → neighbours inside the shrinking search ball that can
+    be reached without collision (``find_nearest_neighbors``) → cheapest parent among them (``choose_parent``) → re-parent
+    neighbours that get cheaper through the new node and push the saving down their subtrees (``rewire``,
+    ``update_cost``).  ``search_goal_parent`` picks the cheapest node one step from the goal, ``extract_path`` walks back
+    to the root.  The step names are the reference's (``rrt_star.py:122-272``); obstacles are discs ``(x, y, radius)``
+    with any clearance already added, the free region is the rectangle ``bounds``."""
+
     def __init__(self, start, goal, obstacles: Sequence[Tuple[float, float, float]], bounds, rng=None, expand_dis=0.03,
                  path_resolution=0.005, goal_sample_rate=0.1, max_iter=1024, connect_circle_dist=0.2, search_until_max_iter=False):
         self.start, self.goal = np.asarray(start, float), np.asarray(goal, float)
@@ -101,56 +136,138 @@ class RRTStar:
         self.max_iter, self.connect_dist, self.search_all = max_iter, connect_circle_dist, search_until_max_iter
         self.nodes: List[np.ndarray] = []
         self.parent: List[int] = []
-        self.cost: List[float] = []
+        self.cost_to: List[float] = []
+        self.children: List[List[int]] = []
+        self.path: Optional[np.ndarray] = None
+        self.success = False
 
+    # ------------------------------------------------------------------------------------------------ geometry
     def _free(self, a, b) -> bool:
         if len(self.obstacles) == 0:
             return True
         return bool((segment_distances(a, b, self.obstacles[:, :2]) > self.obstacles[:, 2]).all())
 
-    def _sample(self):
-        if self.rng.rand() < self.goal_rate:
+    @staticmethod
+    def get_distance_and_angle(node_start, node_end):
+        dx, dy = node_end[0] - node_start[0], node_end[1] - node_start[1]
+        return math.hypot(dx, dy), math.atan2(dy, dx)
+
+    @staticmethod
+    def nearest_neighbor(node_list, n) -> int:
+        """Index of the point of ``node_list`` closest to ``n``."""
+        return int(np.argmin(np.linalg.norm(np.asarray(node_list, float) - np.asarray(n, float), axis=1)))
+
+    def node(self, i: int) -> Node:
+        n = Node(self.nodes[i])
+        n.parent = None if self.parent[i] < 0 else Node(self.nodes[self.parent[i]])
+        return n
+
+    # ------------------------------------------------------------------------------------------------ one iteration
+    def get_random_node(self, goal_sample_rate: Optional[float] = None) -> np.ndarray:
+        rate = self.goal_rate if goal_sample_rate is None else goal_sample_rate
+        if self.rng.rand() < rate:
             return self.goal.copy()
         return np.array([self.rng.uniform(self.xmin, self.xmax), self.rng.uniform(self.ymin, self.ymax)])
 
-    def plan(self) -> Optional[np.ndarray]:
-        self.nodes, self.parent, self.cost = [self.start], [-1], [0.0]
-        best_goal = None
-        for it in range(self.max_iter):
-            rnd = self._sample()
-            pts = np.asarray(self.nodes)
-            near_i = int(np.argmin(np.linalg.norm(pts - rnd, axis=1)))
-            direction = rnd - pts[near_i]
-            dist = np.linalg.norm(direction)
-            if dist < 1e-9:
-                continue
-            new = pts[near_i] + direction / dist * min(self.expand_dis, dist)
-            if not self._free(pts[near_i], new):
-                continue
-            n = len(self.nodes) + 1
-            radius = min(self.connect_dist * math.sqrt(math.log(n) / n), self.expand_dis * 2.5)
-            neigh = np.where(np.linalg.norm(pts - new, axis=1) <= max(radius, self.expand_dis))[0]
-            parent, cost = near_i, self.cost[near_i] + np.linalg.norm(new - pts[near_i])
-            for j in neigh:                                     # choose the cheapest collision-free parent
-                c = self.cost[j] + np.linalg.norm(new - pts[j])
-                if c < cost and self._free(pts[j], new):
-                    parent, cost = int(j), c
-            self.nodes.append(new); self.parent.append(parent); self.cost.append(cost)
-            me = len(self.nodes) - 1
-            for j in neigh:                                     # rewire
-                c = cost + np.linalg.norm(new - pts[j])
-                if c < self.cost[j] and self._free(new, pts[j]):
-                    self.parent[j], self.cost[j] = me, c
-            if np.linalg.norm(new - self.goal) <= self.expand_dis and self._free(new, self.goal):
-                total = cost + np.linalg.norm(new - self.goal)
-                if best_goal is None or total < best_goal[1]:
-                    best_goal = (me, total)
-                if not self.search_all:
-                    break
-        if best_goal is None:
+    def new_state(self, node_start, node_goal) -> Optional[np.ndarray]:
+        """The point at most one step from ``node_start`` towards ``node_goal`` (``None`` when they coincide)."""
+        dist, theta = self.get_distance_and_angle(node_start, node_goal)
+        if dist < 1e-9:
             return None
-        path, i = [self.goal], best_goal[0]
+        step = min(self.expand_dis, dist)
+        return np.array([node_start[0] + step * math.cos(theta), node_start[1] + step * math.sin(theta)])
+
+    def find_nearest_neighbors(self, node_new) -> np.ndarray:
+        """Tree nodes inside the search ball — radius ``connect_circle_dist · sqrt(log n / n)``, capped at 2.5 steps and at
+        least one step — from which ``node_new`` is reachable in a straight line."""
+        n = len(self.nodes) + 1
+        radius = max(min(self.connect_dist * math.sqrt(math.log(n) / n), self.expand_dis * 2.5), self.expand_dis)
+        pts = np.asarray(self.nodes)
+        near = np.where(np.linalg.norm(pts - node_new, axis=1) <= radius)[0]
+        return np.array([j for j in near if self._free(pts[j], node_new)], dtype=np.int64)
+
+    def cost(self, node_p: int) -> float:
+        """Path length from the root to node ``node_p``."""
+        return self.cost_to[node_p]
+
+    def get_new_cost(self, node_start: int, node_end) -> float:
+        """Cost of ``node_end`` (a point) if reached through tree node ``node_start``."""
+        return self.cost_to[node_start] + float(np.linalg.norm(np.asarray(node_end) - self.nodes[node_start]))
+
+    def choose_parent(self, node_new, neighbor_index) -> Tuple[int, float]:
+        costs = [self.get_new_cost(int(j), node_new) for j in neighbor_index]
+        k = int(np.argmin(costs))
+        return int(neighbor_index[k]), costs[k]
+
+    def _attach(self, point, parent: int, cost: float) -> int:
+        self.nodes.append(np.asarray(point, float))
+        self.parent.append(parent)
+        self.cost_to.append(cost)
+        self.children.append([])
+        if parent >= 0:
+            self.children[parent].append(len(self.nodes) - 1)
+        return len(self.nodes) - 1
+
+    def update_cost(self, parent_node: int) -> None:
+        """Breadth-first refresh of the costs below ``parent_node`` after it was given a cheaper parent."""
+        queue = FIFOQueue()
+        queue.put(parent_node)
+        while not queue.empty():
+            i = queue.get()
+            for c in self.children[i]:
+                self.cost_to[c] = self.get_new_cost(i, self.nodes[c])
+                queue.put(c)
+
+    def rewire(self, node_new: int, neighbor_index) -> None:
+        for j in neighbor_index:
+            j = int(j)
+            c = self.get_new_cost(node_new, self.nodes[j])
+            if c < self.cost_to[j] and j != self.parent[node_new]:
+                self.children[self.parent[j]].remove(j)
+                self.parent[j], self.cost_to[j] = node_new, c
+                self.children[node_new].append(j)
+                self.update_cost(j)
+
+    def search_goal_parent(self) -> Optional[int]:
+        """The tree node within one step of the goal, with a free straight line to it, that gives the shortest total path."""
+        pts = np.asarray(self.nodes)
+        close = np.where(np.linalg.norm(pts - self.goal, axis=1) <= self.expand_dis)[0]
+        best, best_cost = None, float("inf")
+        for j in close:
+            c = self.get_new_cost(int(j), self.goal)
+            if c < best_cost and self._free(pts[j], self.goal):
+                best, best_cost = int(j), c
+        return best
+
+    def extract_path(self, node_end: int) -> np.ndarray:
+        """Start → ... → ``node_end`` → goal."""
+        path, i = [self.goal], node_end
         while i != -1:
             path.append(self.nodes[i])
             i = self.parent[i]
         return np.asarray(path[::-1])
+
+    # ------------------------------------------------------------------------------------------------ the search
+    def plan(self) -> Optional[np.ndarray]:
+        self.nodes, self.parent, self.cost_to, self.children = [], [], [], []
+        self._attach(self.start, -1, 0.0)
+        self.path, self.success = None, False
+        for _ in range(self.max_iter):
+            rnd = self.get_random_node()
+            near_i = self.nearest_neighbor(self.nodes, rnd)
+            new = self.new_state(self.nodes[near_i], rnd)
+            if new is None or not self._free(self.nodes[near_i], new):
+                continue
+            neighbors = self.find_nearest_neighbors(new)
+            if len(neighbors) == 0:
+                continue
+            parent, cost = self.choose_parent(new, neighbors)
+            me = self._attach(new, parent, cost)
+            self.rewire(me, neighbors)
+            if not self.search_all and np.linalg.norm(new - self.goal) <= self.expand_dis and self._free(new, self.goal):
+                break
+        end = self.search_goal_parent()
+        if end is None:
+            return None
+        self.path, self.success = self.extract_path(end), True
+        return self.path

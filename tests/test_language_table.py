@@ -461,3 +461,34 @@ def dataclasses_replace(obj, **kw):
 def json_roundtrip(x):
     import json
     return json.loads(json.dumps(x))
+
+
+def test_rrt_star_tree_invariants():
+    """After a full search every stored cost equals the parent's cost plus the edge (rewiring pushes savings down the
+    subtree), children mirror the parent links, every edge is collision free, and the steps compose as documented."""
+    planner = rrt_star.RRTStar([0.2, -0.2], [0.55, 0.2], [(0.35, 0.0, 0.07), (0.45, 0.15, 0.04)], ((0.15, -0.3), (0.6, 0.3)),
+                               rng=np.random.RandomState(3), max_iter=600, search_until_max_iter=True)
+    path = planner.plan()
+    assert planner.success and path is planner.path and np.allclose(path[-1], [0.55, 0.2])
+    for i, (p, par) in enumerate(zip(planner.nodes, planner.parent)):
+        if par < 0:
+            assert i == 0 and planner.cost(i) == 0.0
+            continue
+        assert abs(planner.cost(i) - planner.get_new_cost(par, p)) < 1e-9
+        assert i in planner.children[par] and planner._free(planner.nodes[par], p)
+    assert sum(len(c) for c in planner.children) == len(planner.nodes) - 1
+    length = float(np.linalg.norm(np.diff(path, axis=0), axis=1).sum())
+    end = planner.search_goal_parent()
+    assert abs(length - planner.get_new_cost(end, planner.goal)) < 1e-9
+    assert length < 1.35 * np.linalg.norm(np.array([0.55, 0.2]) - np.array([0.2, -0.2]))       # RRT* straightens the route
+    # the steps on their own
+    step = planner.new_state(np.array([0.0, 0.0]), np.array([1.0, 0.0]))
+    assert np.allclose(step, [planner.expand_dis, 0.0]) and planner.new_state(step, step) is None
+    assert rrt_star.RRTStar.nearest_neighbor([[0, 0], [1, 1], [2, 2]], [0.9, 1.2]) == 1
+    d, a = rrt_star.RRTStar.get_distance_and_angle([0, 0], [0, 2])
+    assert abs(d - 2) < 1e-12 and abs(a - np.pi / 2) < 1e-12
+    n = planner.node(end)
+    assert isinstance(n, rrt_star.Node) and (n.parent is None) == (planner.parent[end] < 0)
+    q = rrt_star.FIFOQueue()
+    q.put(1), q.put(2)
+    assert q.get() == 1 and not q.empty() and q.get() == 2 and q.empty()
