@@ -124,7 +124,7 @@ class LanguageTable:
     def succeeded(self) -> bool:
         if self._reward_calculator is None:
             return bool(self._board.succeeded[0])
-        return bool(self._reward_calculator.reward(self._compute_state(request_task_update=False))[1])
+        return bool(self._reward_calculator.reward(self._compute_state(request_task_update=False, render=False))[1])
 
     @property
     def instruction_str(self):
@@ -150,7 +150,10 @@ class LanguageTable:
         return self._control_frequency
 
     # ----------------------------------------------------------------------------------------- state / obs
-    def _compute_state(self, request_task_update=True) -> Dict[str, Any]:
+    def _compute_state(self, request_task_update=True, render=True) -> Dict[str, Any]:
+        """Everything the rewards, the oracles and the observation need, ``rgb`` last (the reference's ``_compute_state``
+        renders too, ``:418-478``).  The frame comes from a one-entry cache keyed on the rendered quantities, so asking for
+        the state of a scene that was just drawn costs no second rasterisation; ``render=False`` leaves ``rgb`` out."""
         b = self._board
         st = collections.OrderedDict(
             effector_translation=b.effector[0].cpu().numpy().astype(np.float32),
@@ -161,12 +164,12 @@ class LanguageTable:
             st["block_%s_translation" % name] = xy[i].astype(np.float32)
             st["block_%s_orientation" % name] = np.array([yaw[i]], np.float32)
             st["block_%s_mask" % name] = np.array([1.0 if mask[i] else 0.0], np.float32)
+        if render:
+            st["rgb"] = self._render_camera()
         return st
 
     def compute_state(self, request_task_update=True):
-        st = self._compute_state(request_task_update)
-        st["rgb"] = self._render_camera()
-        return st
+        return self._compute_state(request_task_update)
 
     def _compute_observation(self, state=None):
         st = state or self.compute_state()
@@ -174,7 +177,12 @@ class LanguageTable:
                                                               "instruction", "rgb"))
 
     def _render_camera(self) -> np.ndarray:
-        return self._board.render()[0].cpu().numpy()
+        b = self._board
+        key = tuple(t[0].cpu().numpy().tobytes() for t in (b.effector, b.block_xy, b.block_yaw, b.block_mask))
+        cached = getattr(self, "_frame_cache", None)
+        if cached is None or cached[0] != key:
+            cached = self._frame_cache = (key, b.render()[0].cpu().numpy())
+        return cached[1].copy()
 
     def render(self, mode="rgb_array"):
         frame = self._render_camera()
@@ -199,7 +207,10 @@ class LanguageTable:
             if reset_poses and self._robot is not None:
                 self._robot.reset_joints(constants.INITIAL_JOINT_POSITIONS)
                 self._robot.reset_joints(self._robot.inverse_kinematics(self._effector_pose(self._board.effector[0])))
-            state = self._compute_state()
+                # from here on the effector is wherever the joints put it (the IK residual is ~1e-6 m, but a saved
+                # joint vector must reproduce the scene exactly)
+                self._board.effector[0] = torch.as_tensor(np.asarray(self._robot.forward_kinematics().translation[:2], np.float32))
+            state = self._compute_state(render=False)
             if self._reward_calculator is None:
                 self._set_instruction("")
                 break
@@ -249,30 +260,61 @@ class LanguageTable:
         reward, done = (0.0, False)
         if self._reward_calculator is not None:
             reward, done = self._reward_calculator.reward(state)
-        state["rgb"] = self._render_camera()
         return self._compute_observation(state), reward, done, {}
 
     # ------------------------------------------------------------------------------------ save / restore
-    def get_pybullet_state(self):
-        """Full board state (name kept from the reference, ``:234-300``); nothing Bullet-specific is inside."""
+    def get_board_state(self):
+        """Snapshot of everything, the reward object and its task included (tensors, not serialisable): what a search or a
+        what-if roll-out needs to come back to exactly this point."""
         b = self._board
+        joints = None if self._robot is None else np.array(self._robot.get_joint_positions(), dtype=np.float64)
         return {"effector": b.effector.clone(), "effector_target": b.effector_target.clone(), "block_xy": b.block_xy.clone(),
                 "block_yaw": b.block_yaw.clone(), "block_mask": b.block_mask.clone(), "instruction": self._instruction.copy(),
-                "instruction_str": self._instruction_str, "blocks_on_table": list(self._blocks_on_table),
+                "instruction_str": self._instruction_str, "blocks_on_table": list(self._blocks_on_table), "joints": joints,
                 "reward": copy.deepcopy(self._reward_calculator), "task_info": copy.deepcopy(self._task_info)}
 
-    def set_pybullet_state(self, state):
+    def set_board_state(self, state):
         b = self._board
         b.effector, b.effector_target = state["effector"].clone(), state["effector_target"].clone()
         b.block_xy, b.block_yaw, b.block_mask = state["block_xy"].clone(), state["block_yaw"].clone(), state["block_mask"].clone()
         self._instruction, self._instruction_str = state["instruction"].copy(), state["instruction_str"]
         self._blocks_on_table = list(state["blocks_on_table"])
+        if state.get("joints") is not None and self._robot is not None:
+            self._robot.reset_joints(state["joints"])
+            self._robot.set_target_effector_pose(self._effector_pose(b.effector_target[0]))
         if state.get("reward") is not None:
             self._reward_calculator = copy.deepcopy(state["reward"])
             self._reward_calculator.seed(self._rng)
         self._task_info = copy.deepcopy(state.get("task_info"))
 
-    get_board_state, set_board_state = get_pybullet_state, set_pybullet_state
+    def get_pybullet_state(self):
+        """The scene as the reference saves it (``:234-294``): ``robots`` = [XarmState], ``robot_end_effectors`` /
+        ``targets`` = [], ``objects`` = one ObjState per block, the oracle's task fields and the instruction, every string
+        as its zero-padded byte code — plain data that ``utils_pybullet.write_pybullet_state`` can put in a file.  The
+        reward object is not part of it (nor is it upstream); ``get_board_state`` keeps that too."""
+        state = self.export_pybullet_state()
+        info = self._task_info
+        start = getattr(info, "block1", None) or getattr(info, "block", None) or getattr(info, "block_target", None)
+        for key, value in (("start_block", start), ("oracle_target_block", getattr(info, "block2", None) or getattr(info, "target_block", None)),
+                           ("target_absolute_location", getattr(info, "location", None)),
+                           ("target_relative_location", getattr(info, "direction", None))):
+            if isinstance(value, str):
+                state[key] = self.encode_instruction(value).tolist()
+        target = getattr(info, "target_translation", None)
+        if target is not None:
+            state["oracle_target_translation"] = np.asarray(target, np.float64).tolist()
+        if self._instruction_str is not None:
+            state["instruction_str"] = self.encode_instruction(self._instruction_str).tolist()
+        return state
+
+    def set_pybullet_state(self, state):
+        """Restore a ``get_pybullet_state`` record (or one read back from a state file).  An instruction stored with a
+        shorter code length is zero-padded to ``INSTRUCTION_LENGTH`` (reference ``:349-359``)."""
+        if "block_xy" in state:                                  # a get_board_state snapshot
+            return self.set_board_state(state)
+        self.import_pybullet_state(state)
+        if state.get("instruction_str"):
+            self._instruction_str = self.decode_instruction(np.asarray(state["instruction_str"]))
 
     # ------------------------------------------------- the reference's state layout (for its gz-JSON state files)
     def export_pybullet_state(self) -> Dict[str, Any]:
@@ -308,6 +350,12 @@ class LanguageTable:
                 robot.set_bullet_state(client, client.robot_id)
             else:                                               # a record without joint info (older files): positions only
                 self._robot.reset_joints([js[0] for js in robot.joint_state])
+            # the effector is where the restored joints put it (it lags the target within a control step)
+            b.effector[0] = torch.as_tensor(np.asarray(self._robot.forward_kinematics().translation[:2], np.float32))
+            if robot.target_effector_pose is not None:
+                self._robot.set_target_effector_pose(robot.target_effector_pose)
+        self._blocks_on_table = [n for n, m in zip(self._all_blocks, b.block_mask[0].tolist()) if m]
         if state.get("instruction") is not None:
-            self._instruction = np.asarray(state["instruction"], np.int32)
+            code = np.asarray(state["instruction"], np.int32)[:constants.INSTRUCTION_LENGTH]
+            self._instruction = np.pad(code, (0, constants.INSTRUCTION_LENGTH - len(code)))
             self._instruction_str = self.decode_instruction(self._instruction)

@@ -3,9 +3,12 @@
 ``pytorch_robotics_transformer`` here is a package of re-exports of ``rt1b200.models``; the reference's test files import the
 model through that path, so they can be pointed at our classes unchanged.  Each file is executed in a fresh interpreter whose
 ``sys.path`` has this repository first (the test asserts that the package that got imported is ours).  Runnable offline: the
-tokenizer, TokenLearner, decoder and TransformerNetwork tests (the causality test drives ``_transformer_call`` directly).  Not
-runnable here: the two EfficientNet tests (they need the ImageNet weight blob, which upstream does not ship either) and the
-Language-Table / LAVA tests (TensorFlow, clu, the ``clip`` package)."""
+tokenizer, TokenLearner, decoder and TransformerNetwork tests (the causality test drives ``_transformer_call`` directly), and
+three Language-Table files — the instruction-count test, the save / restore test of the environment and the xArm kinematics
+test.  Those three import TensorFlow only for ``tf.test.TestCase`` and (the arm test) PyBullet only to open a client that
+this implementation ignores; ``tests/shims`` supplies exactly that much (see its README).  Not runnable here: the two
+EfficientNet tests (they need the ImageNet weight blob, which upstream does not ship either), ``resnet_v1_test`` (Flax) and
+``clip_tokenizer_test`` (TF-Text and the ``clip`` package)."""
 import os
 import subprocess
 import sys
@@ -20,10 +23,14 @@ FILES = ["pytorch_robotics_transformer/tokenizers/action_tokenizer_test.py",
          "pytorch_robotics_transformer/transformer_test.py",
          "pytorch_robotics_transformer/transformer_network_test.py"]
 
+LT_FILES = ["language_table/environments/rewards/instructions_test.py",
+            "language_table/environments/language_table_test.py",
+            "language_table/environments/utils/xarm_sim_robot_test.py"]
+
 RUNNER = r"""
 import sys, runpy, unittest
 sys.argv = ['reference-test']
-import pytorch_robotics_transformer as pkg
+import PKG as pkg
 assert pkg.__file__.startswith(REPO), pkg.__file__
 mod = runpy.run_path(PATH, run_name='reference_test')
 suite = unittest.TestSuite()
@@ -55,9 +62,23 @@ def test_reference_unit_tests_pass_on_this_implementation(rel, tmp_path):
     except ImportError:
         pytest.skip("absl is not installed")
     env = dict(os.environ, PYTHONPATH=os.pathsep.join([REPO, os.path.join(REPO, "baseline", "shims")]), CUDA_VISIBLE_DEVICES="")
-    code = RUNNER.replace("REPO", repr(REPO)).replace("PATH", repr(path))
+    _run(path, "pytorch_robotics_transformer", env, tmp_path)
+
+
+def _run(path, pkg, env, tmp_path):
+    code = RUNNER.replace("REPO", repr(REPO)).replace("PATH", repr(path)).replace("PKG", pkg)
     r = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=900)
     line = [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT")]
     assert line, (r.stdout[-1500:], r.stderr[-1500:])
     ran, failures, errors = (int(x) for x in line[0].split()[1:])
     assert ran > 0 and failures == 0 and errors == 0, (r.stdout[-3000:], r.stderr[-1500:])
+    return ran
+
+
+@pytest.mark.parametrize("rel", LT_FILES)
+def test_reference_language_table_tests_pass_on_this_implementation(rel, tmp_path):
+    path = _find(rel)
+    if path is None:
+        pytest.skip("the reference's test files are not on this machine")
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([REPO, os.path.join(REPO, "tests", "shims")]), CUDA_VISIBLE_DEVICES="")
+    _run(path, "language_table", env, tmp_path)
