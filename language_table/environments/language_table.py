@@ -160,6 +160,7 @@ class LanguageTable:
             effector_target_translation=b.effector_target[0].cpu().numpy().astype(np.float32),
             instruction=self._instruction)
         xy, yaw, mask = b.block_xy[0].cpu().numpy(), b.block_yaw[0].cpu().numpy(), b.block_mask[0].cpu().numpy()
+        yaw = (yaw + np.pi) % (2.0 * np.pi) - np.pi              # reported like a quaternion's yaw: in [-pi, pi)
         for i, name in enumerate(self._all_blocks):
             st["block_%s_translation" % name] = xy[i].astype(np.float32)
             st["block_%s_orientation" % name] = np.array([yaw[i]], np.float32)

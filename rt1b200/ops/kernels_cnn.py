@@ -36,13 +36,19 @@ _DW_ACT_ON_LOAD = os.environ.get("RT1B200_DW_ACT_ON_LOAD", "1") != "0"
 
 
 class _ZeroArena:
-    """One pre-zeroed fp32 buffer per encoder pass from which the ~200 small statistics / accumulator tensors are carved:
-    a single fill launch instead of one per tensor (they were 184 launches and 0.4 ms of a 35 ms step).  Each pass gets
-    its own arena and the views keep it alive, so buffers saved for the backward never alias a later pass."""
+    """One pre-zeroed fp32 buffer per encoder pass from which the ~200 small statistics / accumulator tensors — and the
+    split-K weight-gradient accumulators of the backward — are carved: a single fill launch instead of one per tensor
+    (they were 184 launches and 0.4 ms of a 35 ms step).  Each pass gets its own arena and the views keep it alive, so
+    buffers saved for the backward never alias a later pass.  The size is learnt: a pass that outgrows its arena falls
+    back to separate allocations and records what it needed under ``key``; the next pass of that kind asks for that much."""
+    NEED = {}
 
-    def __init__(self, device, numel: int = 4 << 20):
+    def __init__(self, device, key=None, numel: int = 4 << 20):
+        self.key = (key, torch.device(device).index)
+        numel = max(numel, self.NEED.get(self.key, 0))
         self.buf = torch.zeros(numel, dtype=F32, device=device)
         self.off = 0
+        self.spilled = 0
 
     def take(self, shape):
         n = 1
@@ -50,10 +56,15 @@ class _ZeroArena:
             n *= int(d)
         n_al = (n + 63) // 64 * 64
         if self.off + n_al > self.buf.numel():
+            self.spilled += n_al
             return torch.zeros(*shape, dtype=F32, device=self.buf.device)
         out = self.buf[self.off:self.off + n].view(*shape)
         self.off += n_al
         return out
+
+    def close(self):
+        if self.spilled:
+            self.NEED[self.key] = max(self.NEED.get(self.key, 0), self.off + self.spilled)
 
 
 _ARENA = None       # set for the duration of _EncoderFn.forward / backward
@@ -181,7 +192,7 @@ class _EncoderFn(Function):
         global _ARENA, _STATS_EPOCH
         net = enc.net
         dev = x8.device
-        _ARENA = _ZeroArena(dev)
+        _ARENA = _ZeroArena(dev, ("fwd", tuple(x8.shape)))
         training = enc.training
         _STATS_EPOCH = getattr(enc, "_bn_stats_epoch", 0)
         N, H, W, _ = x8.shape
@@ -307,6 +318,7 @@ class _EncoderFn(Function):
         if training:
             enc._nbt_pending = getattr(enc, "_nbt_pending", 0) + 1
             enc._bn_stats_epoch = getattr(enc, "_bn_stats_epoch", 0) + 1
+        _ARENA.close()
         _ARENA = None
         return feats
 
@@ -316,7 +328,7 @@ class _EncoderFn(Function):
         enc, S, gb, film_off, GB = ctx.enc, ctx.S, ctx.gb, ctx.film_off, ctx.GB
         net = enc.net
         dev = dfeats.device
-        _ARENA = _ZeroArena(dev)
+        _ARENA = _ZeroArena(dev, ("bwd", tuple(dfeats.shape)))
         lane = wgrad_lane(dev)
         dfeats = dfeats.contiguous()
         N = dfeats.shape[0]
@@ -498,6 +510,7 @@ class _EncoderFn(Function):
             fl += [f._projection_add.weight, f._projection_add.bias, f._projection_mult.weight, f._projection_mult.bias]
         _ready(fl)
         ctx.S = ctx.head = ctx.stem = None
+        _ARENA.close()
         _ARENA = None
         return (None, None, None, None) + (None,) * (len(ctx.needs_input_grad) - 4)
 

@@ -148,6 +148,33 @@ show(frames[::3], "oracle_episode")
 """)
 
 md("""
+## Saving and restoring the scene
+
+`env.get_pybullet_state()` returns the scene in the upstream layout — an `XarmState` for the arm (joint vector, controller set
+point), one `ObjState` per block, the instruction — read through `env.pybullet_client`, a Bullet-style facade over the board.
+`utils_pybullet.write_pybullet_state` puts it in a gz-JSON state file (format version 2, readable by the upstream tools);
+`set_pybullet_state` brings an environment back to it, rendering included.
+""")
+
+code("""
+from language_table.environments.utils import utils_pybullet
+
+saved = env.get_pybullet_state()
+before = env._compute_state()
+state_file = os.path.join(OUT, "scene.json.gz")
+utils_pybullet.write_pybullet_state(state_file, saved, task="block2block", actions=[a.tolist() for _, a in episode[:3]])
+for _ in range(5):
+    env.step(np.array([-0.03, 0.01], np.float32))
+env.set_pybullet_state(utils_pybullet.read_pybullet_state(state_file)["pybullet_state"])
+after = env._compute_state()
+same = all(np.allclose(np.cos(before[k] - after[k]), 1.0, atol=1e-6) if k.endswith("_orientation")      # angles: modulo 2 pi
+           else np.allclose(before[k], after[k], atol=1e-3) for k in before if k != "rgb")
+print("restored:", same, "| mean pixel difference", float(np.abs(before["rgb"].astype(float) - after["rgb"]).mean()))
+block_id = 0
+print("block", block_id, "pose via the client:", env.pybullet_client.getBasePositionAndOrientation(block_id))
+""")
+
+md("""
 ## Episodes on disk
 
 Training reads one `.npy` file per episode (`<root>/{train,val,test}/episode_<n>.npy`, an object array of step dicts with
