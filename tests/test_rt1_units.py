@@ -165,3 +165,24 @@ def test_gpu_input_transform_cpu_statement_matches_pil(tmp_path):
                                    "natural_language_embedding": torch.zeros(1, 3, 512)}, "action_label": {}}
     tb = GpuCropResize(256, 456)(batch)
     assert tb["train_observation"]["image"].shape == (1, 3, 3, 256, 456) and "image_raw" not in tb["train_observation"]
+
+
+def test_zero_arena_learns_its_size():
+    """The per-pass arena of pre-zeroed accumulators (rt1b200/ops/kernels_cnn.py): carving, 64-element alignment, the
+    fall-back once it is full, and the next pass of the same kind asking for what the last one needed."""
+    from rt1b200.ops.kernels_cnn import _ZeroArena
+    _ZeroArena.NEED.pop((("unit", 1), None), None)
+    a = _ZeroArena("cpu", key=("unit", 1), numel=256)
+    x, y = a.take((3, 5)), a.take((64,))
+    assert x.shape == (3, 5) and a.off == 128 and x.data_ptr() != y.data_ptr() and float(x.abs().sum() + y.abs().sum()) == 0.0
+    assert x.untyped_storage().data_ptr() == a.buf.untyped_storage().data_ptr()          # a view of the arena
+    big = a.take((10, 100))                                                              # does not fit: its own allocation
+    assert big.untyped_storage().data_ptr() != a.buf.untyped_storage().data_ptr() and a.spilled == 1024 and float(big.sum()) == 0.0
+    z = a.take((64,))                                                                    # smaller requests still fit
+    assert z.untyped_storage().data_ptr() == a.buf.untyped_storage().data_ptr()
+    a.close()
+    b = _ZeroArena("cpu", key=("unit", 1), numel=256)
+    assert b.buf.numel() >= 128 + 64 + 1024
+    assert _ZeroArena("cpu", key=("unit", 2), numel=256).buf.numel() == 256              # another kind of pass: untouched
+    b.take((10, 100))
+    assert b.spilled == 0
