@@ -95,6 +95,8 @@ class LanguageTable:
         self._instruction = np.zeros(constants.INSTRUCTION_LENGTH, np.int32)
         self._instruction_str = None
         self._task_info = None
+        self._start_block = self._oracle_target_block = self._oracle_target_translation = None
+        self._target_absolute_location = self._target_relative_location = None
         self.action_space = spaces.Box(low=-0.1, high=0.1, shape=(2,), dtype=np.float32)
         self.observation_space = spaces.Dict(collections.OrderedDict(
             effector_translation=spaces.Box(low=constants.WORKSPACE_BOUNDS[0] - 0.1, high=constants.WORKSPACE_BOUNDS[1] + 0.1),
@@ -165,9 +167,69 @@ class LanguageTable:
             st["block_%s_translation" % name] = xy[i].astype(np.float32)
             st["block_%s_orientation" % name] = np.array([yaw[i]], np.float32)
             st["block_%s_mask" % name] = np.array([1.0 if mask[i] else 0.0], np.float32)
+        calc = self._reward_calculator
+        if request_task_update and self._task_info is not None and hasattr(calc, "get_current_task_info"):
+            # moving-target tasks (a side of another block, away from the others): the target follows the scene
+            self._set_task_info(calc.get_current_task_info(st))
+        self._update_obs_with_oracle_task_info(st)
         if render:
             st["rgb"] = self._render_camera()
         return st
+
+    def _update_obs_with_oracle_task_info(self, st):
+        """What the scripted oracle steers by (reference ``:509-540``): the block being pushed and the place it goes to, both
+        relative to the effector TARGET; the place is the task's target point when it has one, else the target block."""
+        e_target = st["effector_target_translation"]
+        zero2, zero1 = np.zeros(2, np.float32), np.zeros(1, np.float32)
+        if self._start_block is not None:
+            st["effector_target_to_start_block_translation"] = (st["block_%s_translation" % self._start_block] - e_target).astype(np.float32)
+            st["start_block_orientation"] = st["block_%s_orientation" % self._start_block]
+        else:
+            st["effector_target_to_start_block_translation"], st["start_block_orientation"] = zero2, zero1
+        if self._oracle_target_translation is not None:
+            st["effector_target_to_task_target_translation"] = (np.asarray(self._oracle_target_translation, np.float32) - e_target).astype(np.float32)
+            st["task_target_orientation"] = zero1
+        elif self._oracle_target_block is not None and "block_%s_translation" % self._oracle_target_block in st:
+            st["effector_target_to_task_target_translation"] = (st["block_%s_translation" % self._oracle_target_block] - e_target).astype(np.float32)
+            st["task_target_orientation"] = st["block_%s_orientation" % self._oracle_target_block]
+        else:
+            st["effector_target_to_task_target_translation"], st["task_target_orientation"] = zero2, zero1
+        return st
+
+    def _set_task_info(self, info):
+        """Cache what defines the task (reference ``:742-816``): the pushed block, and where to — another block, a fixed point, or
+        a point that moves with the scene — plus the instruction."""
+        T = task_info
+        target_block = location = direction = translation = None
+        if isinstance(info, T.Block2BlockTaskInfo):
+            start, target_block = info.block1, info.block2
+        elif isinstance(info, T.Block2LocationTaskInfo):
+            start, translation, location = info.block, info.target_translation, info.location
+        elif isinstance(info, T.Block2LineTaskInfo):
+            start, translation = info.block, info.target_translation
+        elif isinstance(info, T.Block2RelativeLocationTaskInfo):
+            start, translation, direction = info.block, info.target_translation, info.location
+        elif isinstance(info, T.Block2BlockRelativeLocationTaskInfo):
+            start, target_block, translation, direction = info.block, info.target_block, info.target_translation, info.direction
+        elif isinstance(info, T.SeparateBlocksTaskInfo):
+            start, translation = info.block, info.target_translation
+        elif isinstance(info, T.Point2BlockTaskInfo):
+            start = target_block = info.block_target
+        elif isinstance(info, T.Block2PoleTaskInfo):
+            start, target_block = info.block1, info.goal
+        elif isinstance(info, T.PlayTaskInfo):
+            start = None                                         # free-form instruction: nothing for an oracle to steer by
+        else:
+            raise ValueError("Unknown task info: %s" % (info,))
+        if target_block is None and translation is None and not isinstance(info, T.PlayTaskInfo):
+            raise ValueError("We are not providing the oracle with a target location to push a block to. Either the target block "
+                             "or the target translation must be set by the reward calculator.")
+        self._task_info = info
+        self._start_block, self._oracle_target_block = start, target_block
+        self._oracle_target_translation = None if translation is None else np.asarray(translation, np.float64)
+        self._target_absolute_location, self._target_relative_location = location, direction
+        if info.instruction != self._instruction_str:
+            self._set_instruction(info.instruction)
 
     def compute_state(self, request_task_update=True):
         return self._compute_state(request_task_update)
@@ -211,14 +273,13 @@ class LanguageTable:
                 # from here on the effector is wherever the joints put it (the IK residual is ~1e-6 m, but a saved
                 # joint vector must reproduce the scene exactly)
                 self._board.effector[0] = torch.as_tensor(np.asarray(self._robot.forward_kinematics().translation[:2], np.float32))
-            state = self._compute_state(render=False)
+            state = self._compute_state(request_task_update=False, render=False)
             if self._reward_calculator is None:
                 self._set_instruction("")
                 break
             info = self._reward_calculator.reset(state, self._blocks_on_table)
             if info != task_info.FAILURE:
-                self._task_info = info
-                self._set_instruction(info.instruction)
+                self._set_task_info(info)
                 break
         else:
             raise ValueError("could not sample a valid task for this board")
@@ -286,7 +347,9 @@ class LanguageTable:
         if state.get("reward") is not None:
             self._reward_calculator = copy.deepcopy(state["reward"])
             self._reward_calculator.seed(self._rng)
-        self._task_info = copy.deepcopy(state.get("task_info"))
+        self._task_info = None
+        if state.get("task_info") is not None:
+            self._set_task_info(copy.deepcopy(state["task_info"]))
 
     def get_pybullet_state(self):
         """The scene as the reference saves it (``:234-294``): ``robots`` = [XarmState], ``robot_end_effectors`` /
@@ -294,16 +357,13 @@ class LanguageTable:
         as its zero-padded byte code — plain data that ``utils_pybullet.write_pybullet_state`` can put in a file.  The
         reward object is not part of it (nor is it upstream); ``get_board_state`` keeps that too."""
         state = self.export_pybullet_state()
-        info = self._task_info
-        start = getattr(info, "block1", None) or getattr(info, "block", None) or getattr(info, "block_target", None)
-        for key, value in (("start_block", start), ("oracle_target_block", getattr(info, "block2", None) or getattr(info, "target_block", None)),
-                           ("target_absolute_location", getattr(info, "location", None)),
-                           ("target_relative_location", getattr(info, "direction", None))):
-            if isinstance(value, str):
-                state[key] = self.encode_instruction(value).tolist()
-        target = getattr(info, "target_translation", None)
-        if target is not None:
-            state["oracle_target_translation"] = np.asarray(target, np.float64).tolist()
+        for key, value in (("start_block", self._start_block), ("oracle_target_block", self._oracle_target_block),
+                           ("target_absolute_location", self._target_absolute_location),
+                           ("target_relative_location", self._target_relative_location)):
+            if value is not None:
+                state[key] = self.encode_instruction(str(value)).tolist()
+        if self._oracle_target_translation is not None:
+            state["oracle_target_translation"] = np.asarray(self._oracle_target_translation, np.float64).tolist()
         if self._instruction_str is not None:
             state["instruction_str"] = self.encode_instruction(self._instruction_str).tolist()
         return state
@@ -314,6 +374,13 @@ class LanguageTable:
         if "block_xy" in state:                                  # a get_board_state snapshot
             return self.set_board_state(state)
         self.import_pybullet_state(state)
+        for key, attr in (("start_block", "_start_block"), ("oracle_target_block", "_oracle_target_block"),
+                          ("target_absolute_location", "_target_absolute_location"),
+                          ("target_relative_location", "_target_relative_location")):
+            if key in state:
+                setattr(self, attr, self.decode_instruction(np.asarray(state[key])))
+        if "oracle_target_translation" in state:
+            self._oracle_target_translation = np.asarray(state["oracle_target_translation"], np.float64)
         if state.get("instruction_str"):
             self._instruction_str = self.decode_instruction(np.asarray(state["instruction_str"]))
 

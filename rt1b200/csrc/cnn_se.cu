@@ -17,39 +17,76 @@ __global__ void __launch_bounds__(SE_THREADS) se_fc_fwd_kernel(const float* __re
                                                                const bf16* __restrict__ w2, const bf16* __restrict__ b2,
                                                                float* __restrict__ z1_out, float* __restrict__ s_out, int C, int Cs) {
   pdl_enter();
-  extern __shared__ float sm[];  // pooled [C] | hid [Cs]
+  extern __shared__ __align__(16) float sm[];  // pooled [C] | hid [Cs]
   float* pooled = sm;
   float* hid = sm + C;
   const int n = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   for (int c = threadIdx.x; c < C; c += blockDim.x) pooled[c] = pooled_sum[(size_t)n * C + c] * inv_hw;
   __syncthreads();
-  for (int u = warp; u < Cs; u += nw) {
-    float acc = 0.f;
-    const bf16* wr = w1 + (size_t)u * C;
-#pragma unroll 4
-    for (int c = lane * 8; c < C; c += 256) {
-      float fw[8];
-      unpack8(*reinterpret_cast<const bf16x8*>(wr + c), fw);
+  // a warp owns rows warp, warp + nw, ...: their loads are issued together (the row-after-row loop waited on one L2 round trip
+  // per 256 channels and row — three rows deep at Cs = 96)
+  constexpr int RPW = SE_MAX_CS / 32;
+  {
+    float acc[RPW];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc = fmaf(fw[e], pooled[c + e], acc);
+    for (int j = 0; j < RPW; ++j) acc[j] = 0.f;
+#pragma unroll 2
+    for (int c = lane * 8; c < C; c += 256) {
+      bf16x8 wv[RPW];
+#pragma unroll
+      for (int j = 0; j < RPW; ++j) {
+        const int u = warp + j * nw;
+        if (u < Cs) wv[j] = *reinterpret_cast<const bf16x8*>(w1 + (size_t)u * C + c);
+      }
+      const float4 p0 = *reinterpret_cast<const float4*>(pooled + c), p1 = *reinterpret_cast<const float4*>(pooled + c + 4);
+      const float pv[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+      for (int j = 0; j < RPW; ++j) {
+        if (warp + j * nw < Cs) {
+          float fw[8];
+          unpack8(wv[j], fw);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[j] = fmaf(fw[e], pv[e], acc[j]);
+        }
+      }
     }
-    acc = warp_sum(acc);
-    if (lane == 0) {
-      const float z = acc + __bfloat162float(b1[u]);
-      z1_out[(size_t)n * Cs + u] = z;
-      hid[u] = silu_f(z);
+#pragma unroll
+    for (int j = 0; j < RPW; ++j) {
+      const int u = warp + j * nw;
+      if (u < Cs) {                                   // warp-uniform
+        const float a = warp_sum(acc[j]);
+        if (lane == 0) {
+          const float z = a + __bfloat162float(b1[u]);
+          z1_out[(size_t)n * Cs + u] = z;
+          hid[u] = silu_f(z);
+        }
+      }
     }
   }
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    float acc = __bfloat162float(b2[c]);
     const bf162* wr = reinterpret_cast<const bf162*>(w2 + (size_t)c * Cs);   // Cs is even: rows are 4-byte aligned
-#pragma unroll 8
-    for (int u = 0; u < Cs; u += 2) {
-      const float2 w = __bfloat1622float2(wr[u >> 1]);
-      acc = fmaf(w.x, hid[u], acc);
-      acc = fmaf(w.y, hid[u + 1], acc);
+    float a0 = __bfloat162float(b2[c]), a1 = 0.f, a2 = 0.f, a3 = 0.f;       // four chains: the adds do not serialise the loads
+    int u = 0;
+#pragma unroll 4
+    for (; u + 8 <= Cs; u += 8) {
+      const float2 w0 = __bfloat1622float2(wr[(u >> 1)]), w1v = __bfloat1622float2(wr[(u >> 1) + 1]);
+      const float2 w2v = __bfloat1622float2(wr[(u >> 1) + 2]), w3 = __bfloat1622float2(wr[(u >> 1) + 3]);
+      a0 = fmaf(w0.x, hid[u], a0);
+      a0 = fmaf(w0.y, hid[u + 1], a0);
+      a1 = fmaf(w1v.x, hid[u + 2], a1);
+      a1 = fmaf(w1v.y, hid[u + 3], a1);
+      a2 = fmaf(w2v.x, hid[u + 4], a2);
+      a2 = fmaf(w2v.y, hid[u + 5], a2);
+      a3 = fmaf(w3.x, hid[u + 6], a3);
+      a3 = fmaf(w3.y, hid[u + 7], a3);
     }
+    for (; u < Cs; u += 2) {
+      const float2 w = __bfloat1622float2(wr[u >> 1]);
+      a0 = fmaf(w.x, hid[u], a0);
+      a1 = fmaf(w.y, hid[u + 1], a1);
+    }
+    const float acc = (a0 + a1) + (a2 + a3);
     s_out[(size_t)n * C + c] = sigmoid_f(acc);
   }
 }

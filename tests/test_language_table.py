@@ -492,3 +492,44 @@ def test_rrt_star_tree_invariants():
     q = rrt_star.FIFOQueue()
     q.put(1), q.put(2)
     assert q.get() == 1 and not q.empty() and q.get() == 2 and q.empty()
+
+
+def test_state_carries_the_oracle_task_fields():
+    """effector_target_to_start_block_translation & co. (reference language_table.py:509-540), kept current for moving-target
+    tasks through get_current_task_info (``:457-466``), and carried by the saved state (``:265-284``)."""
+    env = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8, block2block.BlockToBlockReward, seed=2)
+    env.reset()
+    st = env._compute_state(render=False)
+    info = env._task_info
+    assert env._start_block == info.block1 and env._oracle_target_block == info.block2 and env._oracle_target_translation is None
+    tgt = st["effector_target_translation"]
+    assert np.allclose(st["effector_target_to_start_block_translation"], st["block_%s_translation" % info.block1] - tgt)
+    assert np.allclose(st["effector_target_to_task_target_translation"], st["block_%s_translation" % info.block2] - tgt)
+    assert np.allclose(st["start_block_orientation"], st["block_%s_orientation" % info.block1])
+    assert st["task_target_orientation"].shape == (1,) and list(st)[-1] != "rgb" and list(env._compute_state())[-1] == "rgb"
+
+    env = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8,
+                                       block2block_relative_location.BlockToBlockRelativeLocationReward, seed=2)
+    env.reset()
+    info = env._task_info
+    st = env._compute_state(render=False)
+    assert env._target_relative_location == info.direction and env._oracle_target_block == info.target_block
+    assert np.allclose(st["effector_target_to_task_target_translation"], np.asarray(info.target_translation) - st["effector_target_translation"], atol=1e-6)
+    # the target is defined relative to another block: move that block and the oracle's target follows
+    i = env._all_blocks.index(info.target_block)
+    env._board.block_xy[0, i] += torch.tensor([0.02, -0.01])
+    moved = env._compute_state(render=False)
+    delta = moved["effector_target_to_task_target_translation"] - st["effector_target_to_task_target_translation"]
+    assert np.allclose(delta, [0.02, -0.01], atol=1e-6)
+    # saved and restored with the scene
+    saved = env.get_pybullet_state()
+    assert env.decode_instruction(np.asarray(saved["start_block"])) == info.block
+    assert env.decode_instruction(np.asarray(saved["target_relative_location"])) == info.direction and "oracle_target_translation" in saved
+    other = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8, block2block.BlockToBlockReward, seed=5)
+    other.reset()
+    other.set_pybullet_state(saved)
+    assert other._start_block == info.block and other._oracle_target_block == info.target_block
+    back = other._compute_state(request_task_update=False, render=False)
+    assert np.allclose(back["effector_target_to_task_target_translation"], moved["effector_target_to_task_target_translation"], atol=1e-5)
+    with pytest.raises(ValueError):
+        env._set_task_info(object())
