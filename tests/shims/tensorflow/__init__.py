@@ -1,2 +1,2 @@
 """Test-harness stand-in: see ../README.md."""
-from . import test  # noqa: F401
+from . import io, test  # noqa: F401
