@@ -55,6 +55,24 @@ def main(path):
            "b2b_relative": {"DIRECTIONS": plain(block2block_relative_location.DIRECTIONS),
                             "tasks": plain(block2block_relative_location.UNIQUE_TASK_STRINGS)},
            "synonyms": {k: plain(getattr(synonyms, k)) for k in dir(synonyms) if k.isupper()}}
+    # the small functions around the tables
+    from language_table.environments.rewards import reward as reward_base
+    sets = {"fixed8": list(blocks.FIXED_8_COMBINATION), "fixed4": list(blocks.FIXED_4_COMBINATION),
+            "subset": list(blocks.TRAIN_COMBINATIONS[3])}
+    grid = [(round(x, 3), round(y, 3)) for x in np.linspace(0.1, 0.65, 12) for y in np.linspace(-0.35, 0.35, 15)]
+    rel_rng = np.random.RandomState(0)
+    pairs = [(rel_rng.uniform(0.2, 0.5, 2), None) for _ in range(200)]
+    pairs = [(a, a + rel_rng.uniform(-0.12, 0.12, 2)) for a, _ in pairs]
+    out["functions"] = {
+        "block_synonyms": {k: {b: plain(synonyms.get_block_synonyms(b, v)) for b in v} for k, v in sets.items()},
+        "count_color_shape": {k: plain([dict(c) for c in synonyms.count_color_shape(v)]) for k, v in sets.items()},
+        "color_shape": {b: plain(synonyms.get_color_shape(b)) for b in blocks.ALL_BLOCKS},
+        "block_set": {m: plain(sorted(blocks.get_block_set(getattr(modes, m)))) for m in ("BLOCK_4", "BLOCK_8", "N_CHOOSE_K")},
+        "block_pairs": {m: plain([list(p) for p in blocks.get_all_block_pairs(getattr(modes, m))]) for m in ("BLOCK_4", "BLOCK_8")},
+        "subsets": {"%s_%s" % (m, t): len(blocks.get_all_block_subsets(getattr(modes, m), t))
+                    for m in ("BLOCK_4", "BLOCK_8", "N_CHOOSE_K") for t in (True, False)},
+        "inside_bounds": [bool(reward_base.target_inside_bounds(np.array(p))) for p in grid],
+        "is_b2b_relative_pair": [bool(block2block_relative_location.is_block2block_relative_pair(a, b)) for a, b in pairs]}
     from language_table.environments.utils.pose3d import Pose3d
     from scipy.spatial import transform
     pose = Pose3d(rotation=transform.Rotation.from_euler("xyz", [0.1, -0.2, 0.3]), translation=np.array([1.0, 2.0, 3.0]))
