@@ -47,8 +47,11 @@ def resolve_contacts(eff: torch.Tensor, blocks: torch.Tensor, mask: torch.Tensor
 
 class BatchedLanguageTable:
     def __init__(self, num_envs: int, block_mode=blocks_module.LanguageTableBlockVariants.BLOCK_8, device="cpu", seed: int = 0,
-                 max_episode_steps: int = 80, image_hw=(256, 456), crop: float = 0.95, add_invisible_walls: bool = False):
+                 max_episode_steps: int = 80, image_hw=(256, 456), crop: float = 0.95, add_invisible_walls: bool = False,
+                 reset_buffer: float = C.WORKSPACE_BOUNDS_BUFFER):
         self.E = num_envs
+        # initial effector and block positions are drawn this far inside the workspace (reference language_table.py:837-840)
+        self.reset_buffer = float(reset_buffer)
         # The reference's experimental "invisible walls" (language_table.py:933-990): four static boxes of half-width 0.04 m
         # just outside the workspace that keep blocks from sliding off the board.  Here: block centres are clamped to the
         # rectangle the walls' inner faces leave, shrunk by the block radius.
@@ -82,13 +85,13 @@ class BatchedLanguageTable:
         n = len(ids)
         if n == 0:
             return
-        lo = torch.tensor([C.X_MIN + 0.04, C.Y_MIN + 0.04], device=self.device)
-        hi = torch.tensor([C.X_MAX - 0.04, C.Y_MAX - 0.04], device=self.device)
+        lo = torch.tensor([C.X_MIN + self.reset_buffer, C.Y_MIN + self.reset_buffer], device=self.device)
+        hi = torch.tensor([C.X_MAX - self.reset_buffer, C.Y_MAX - self.reset_buffer], device=self.device)
         eff = lo + self._rand(n, 2) * (hi - lo)
         xy = lo + self._rand(n, self.B, 2) * (hi - lo)
         for _ in range(30):                                    # resample offenders until every board is valid
             d = (xy[:, :, None] - xy[:, None, :]).norm(dim=-1) + torch.eye(self.B, device=self.device) * 10
-            bad = (d.min(dim=-1).values < 2 * C.BLOCK_RADIUS + 0.015) | ((xy - eff[:, None]).norm(dim=-1) < 0.06)
+            bad = (d.min(dim=-1).values < 2 * C.BLOCK_RADIUS + 0.015) | ((xy - eff[:, None]).norm(dim=-1) < C.ARM_DISTANCE_THRESHOLD)
             if not bool(bad.any()):
                 break
             xy = torch.where(bad[..., None], lo + self._rand(n, self.B, 2) * (hi - lo), xy)
