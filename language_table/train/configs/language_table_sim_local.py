@@ -21,7 +21,8 @@ AGENT = dict(learning_rate=1e-3, pretrained_checkpoints=[], freeze_keys=["text_e
 
 # data: directory with {train,val,test}/episode_N.npy (None → synthetic episodes), 320 × 180 frames, a 0.95 crop window and
 # photometric distortions in training, statistics over 32 batches, images and instructions not normalised
-DATA = dict(dataset_path=None, data_target_width=320, data_target_height=180, image_photometric_distortions=True,
+DATA = dict(dataset_path=None, clip_bpe_path=None,          # CLIP's bpe_simple_vocab_16e6.txt.gz, for lava_lang_encoder = "clip"
+            data_target_width=320, data_target_height=180, image_photometric_distortions=True,
             image_augment_crop=True, random_crop_factor=0.95, data_normalization_num_samples=32,
             data_skip_normalize_keys=["rgb", "instruction"], synthetic_data=False)
 

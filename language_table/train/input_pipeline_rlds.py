@@ -140,7 +140,12 @@ class WindowDataset:
     """Iterable over (observation, action) windows of a list of episodes."""
 
     def __init__(self, episodes: List[List[Dict]], sequence_length: int, target_hw=(180, 320), random_crop_factor: Optional[float] = 0.95,
-                 photometric: bool = True, train: bool = True, seed: int = 0):
+                 photometric: bool = True, train: bool = True, seed: int = 0, clip_tokenizer=None, clip_vocab_size: int = 49408):
+        """``clip_tokenizer`` (a ``common.clip_tokenizer.ClipTokenizer``): episodes whose ``instruction`` is still the
+        simulator's byte code (the "raw" tree of the converter) get ``instruction_tokenized_clip`` — [t, 77] CLIP BPE ids, what
+        ``lava_lang_encoder="clip"`` feeds its text tower (reference ``input_pipeline_rlds.py:236-262``) — instead of
+        ``clip_embedding``."""
+        self.clip_tokenizer, self.clip_vocab_size, self._token_cache = clip_tokenizer, clip_vocab_size, {}
         self.windows = [w for ep in episodes for w in _windows(ep, sequence_length)]
         self.hw, self.factor, self.photometric, self.train = tuple(target_hw), random_crop_factor, photometric, train
         self.crop = DecodeAndRandomResizedCrop(random_crop_factor, self.hw)
@@ -157,10 +162,25 @@ class WindowDataset:
         rgb = self.crop([s["rgb"] for s in win] if encoded else np.stack([np.asarray(s["rgb"]) for s in win]), self.rng, self.train)
         if self.train and self.photometric:
             rgb = self.distort(rgb, self.rng)
-        emb = torch.from_numpy(np.stack([np.asarray(s["instruction"], dtype=np.float32) for s in win]))
         eff = torch.from_numpy(np.stack([np.asarray(s.get("effector_translation", np.zeros(2)), dtype=np.float32) for s in win]))
-        return {"observation": {"rgb": rgb, "clip_embedding": emb, "effector_translation": eff},
-                "action": torch.from_numpy(np.asarray(win[-1]["action"], dtype=np.float32))}
+        obs = {"rgb": rgb, "effector_translation": eff}
+        inst = np.asarray(win[0]["instruction"])
+        if inst.dtype.kind in "iu" or inst.dtype.kind in "SU":       # byte-coded (or plain) text: tokens for the text tower
+            if self.clip_tokenizer is None:
+                raise ValueError("the episodes carry text instructions, not sentence embeddings: pass clip_tokenizer "
+                                 "(config.clip_bpe_path) or convert them with an embedding (rlds_np_convert.py)")
+            obs["instruction_tokenized_clip"] = torch.from_numpy(np.stack([self._tokens(s["instruction"]) for s in win]))
+        else:
+            obs["clip_embedding"] = torch.from_numpy(np.stack([np.asarray(s["instruction"], dtype=np.float32) for s in win]))
+        return {"observation": obs, "action": torch.from_numpy(np.asarray(win[-1]["action"], dtype=np.float32))}
+
+    def _tokens(self, instruction) -> np.ndarray:
+        from language_table.common import clip_tokenizer as ct
+        inst = np.asarray(instruction)
+        text = str(inst) if inst.dtype.kind in "SU" else bytes(inst[inst != 0].astype(np.uint8).tolist()).decode("utf-8")
+        if text not in self._token_cache:
+            self._token_cache[text] = ct.tokenize_text(text, self.clip_tokenizer, vocab_size=self.clip_vocab_size)[0]
+        return self._token_cache[text]
 
     def batches(self, batch_size: int, shuffle: bool = True, drop_last: bool = True) -> Iterator[Dict]:
         order = self.rng.permutation(len(self)) if shuffle else np.arange(len(self))
@@ -217,9 +237,13 @@ def create_datasets(config, seed: int = 0, normalization_path: str = None, proce
     ``train.py:81``)."""
     from . import normalization
     eps = load_episodes(getattr(config, "dataset_path", None), "train", synthetic=getattr(config, "synthetic_data", False), seed=seed)
+    tokenizer = None
+    if getattr(config, "clip_bpe_path", None):                   # CLIP's merge table (not shipped; see common/clip_tokenizer.py)
+        from language_table.common import clip_tokenizer as ct
+        tokenizer = ct.ClipTokenizer(*ct.create_vocab(bpe_path=config.clip_bpe_path))
     ds = WindowDataset(eps, config.sequence_length, (config.data_target_height, config.data_target_width),
                        config.random_crop_factor if config.image_augment_crop else None, config.image_photometric_distortions,
-                       train=True, seed=seed + process_index)
+                       train=True, seed=seed + process_index, clip_tokenizer=tokenizer)
     if normalization_path is not None and process_index != 0:
         return ds, _wait_for_norm_info(normalization_path)
     info = _load_norm_info(normalization_path) if normalization_path is not None else None
@@ -227,7 +251,7 @@ def create_datasets(config, seed: int = 0, normalization_path: str = None, proce
         stat_batches = ((b["observation"], b["action"]) for b in ds.batches(min(8, len(ds)), shuffle=False, drop_last=False))
         obs_stats, act_stats, amin, amax = normalization.compute_dataset_statistics(
             (({k: v.numpy() for k, v in o.items()}, a.numpy()) for o, a in stat_batches), config.data_normalization_num_samples,
-            skip_keys=tuple(config.data_skip_normalize_keys) + ("clip_embedding",))
+            skip_keys=tuple(config.data_skip_normalize_keys) + ("clip_embedding", "instruction_tokenized_clip"))
         info = {"observation_statistics": obs_stats, "action_statistics": act_stats, "action_min": amin, "action_max": amax}
         if normalization_path is not None:
             _save_norm_info(normalization_path, info)

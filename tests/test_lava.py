@@ -333,3 +333,52 @@ def test_lava_image_transforms():
     assert all(abs(l["brightness"]) <= 0.1 and 0.8 <= l["contrast"] <= 1.2 and abs(l["hue"]) <= 0.03
                and 0.8 <= l["saturation"] <= 1.2 for l in levels)
     assert ip.PhotometricDistortions(0.0, 1.0, 1.0, 0.0, 1.0, 1.0)(x, rng) is x           # everything switched off
+
+
+def test_lava_clip_tokens_from_raw_episodes(tmp_path):
+    """lava_lang_encoder="clip" end to end on the converter's RAW tree (instruction = the simulator's byte code): the input
+    pipeline BPE-tokenises it into ``instruction_tokenized_clip`` [t, 77] (reference input_pipeline_rlds.py:236-262) and the
+    frozen text tower turns that into the language embedding.  Tiny merge table and tower; the real ones are path arguments."""
+    import gzip
+    from language_table.environments.language_table import LanguageTable
+    from language_table.train import input_pipeline_rlds as ip
+    from language_table.train.networks.clip_text import ClipTextEncoder
+    from rt1b200.data.episodes import save_episode, synthetic_episode
+    rng = np.random.default_rng(0)
+    for i, text in enumerate(["push the red moon to the blue cube", "push the star left"]):
+        steps = synthetic_episode(rng, length=7, height=36, width=64)
+        for s in steps:
+            s["instruction"] = LanguageTable.encode_instruction(text)
+        save_episode(str(tmp_path / "raw" / "train" / f"episode_{i}.npy"), steps)
+    # a merge file in CLIP's format: a header line, then one merge per line
+    merges = [("p", "u"), ("s", "h</w>"), ("pu", "sh</w>"), ("t", "h"), ("th", "e</w>")]
+    bpe = tmp_path / "bpe.txt.gz"
+    with gzip.open(bpe, "wt", encoding="utf-8") as f:
+        f.write("#version: test\n" + "\n".join(" ".join(m) for m in merges) + "\n")
+
+    cfg = _small(language_table_sim_local.get_config())
+    cfg.synthetic_data, cfg.dataset_path, cfg.clip_bpe_path = False, str(tmp_path / "raw"), str(bpe)
+    cfg.model.lava_lang_encoder = "clip"
+    ds, info = ip.create_datasets(cfg, seed=0)
+    batch = next(ds.batches(2, shuffle=False))
+    tok = batch["observation"]["instruction_tokenized_clip"]
+    assert tok.shape == (2, cfg.sequence_length, 77) and tok.dtype == torch.int64 and "clip_embedding" not in batch["observation"]
+    vocab = 512 + len(merges) + 2
+    # framed by the start / end ids of the 49 408-entry vocabulary the tower expects (the tiny table's own ids sit below)
+    assert int(tok[0, 0, 0]) == 49408 - 2 and int(tok[0, 0].max()) == 49408 - 1 and int(tok[0, 0, 1]) == 512 + 2      # "push</w>"
+    assert vocab < 49408 and torch.equal(tok[0, 0], tok[0, -1])                     # one instruction per episode
+    # without a tokenizer the pipeline says what is wrong instead of feeding byte codes to the model
+    cfg2 = _small(language_table_sim_local.get_config())
+    cfg2.synthetic_data, cfg2.dataset_path = False, str(tmp_path / "raw")
+    with pytest.raises(ValueError, match="clip_tokenizer"):
+        next(ip.create_datasets(cfg2, seed=0)[0].batches(2))
+
+    tower = ClipTextEncoder(features=32, num_heads=2, num_layers=1, out_features=512).freeze()
+    from language_table.train.networks import lava                                    # (the 63 M-parameter default tower is not needed here)
+    model = lava.SequenceLAVMSE(action_size=2, text_encoder=tower, **dict(cfg.model))
+    out = model(batch["observation"])
+    assert out.shape == (2, 2) and torch.isfinite(out).all()
+    agent = train_lib.bc.BCAgent(model, cfg.sequence_length, 1e-3, {}, {}, None, None, freeze_keys=["text_encoder"])
+    before = tower.token_embedding.weight.clone()
+    loss = agent.train({"observation": batch["observation"], "action": batch["action"]})["loss"]
+    assert np.isfinite(loss) and torch.equal(tower.token_embedding.weight, before)    # the tower stays frozen
