@@ -348,6 +348,8 @@ class LanguageTable:
             self._reward_calculator = copy.deepcopy(state["reward"])
             self._reward_calculator.seed(self._rng)
         self._task_info = None
+        self._start_block = self._oracle_target_block = self._oracle_target_translation = None
+        self._target_absolute_location = self._target_relative_location = None
         if state.get("task_info") is not None:
             self._set_task_info(copy.deepcopy(state["task_info"]))
 
