@@ -52,6 +52,12 @@ def test_dataset_windows_and_collate(tmp_path):
     assert batch["train_observation"]["image"].shape == (2, T, 3, 64, 96)
     assert batch["action_label"]["terminate_episode"].dtype == torch.int64
     assert batch["train_observation"]["natural_language_embedding"].shape == (2, T, 512)
+    # the reference's "is my dataset ready" check: python load_np_dataset.py (README, "Convert Dataset")
+    import load_np_dataset
+    out = load_np_dataset.main(["--data_dir", os.path.join(root, "train"), "--window_length", str(T), "--batch_size", "4",
+                                "--width", "96", "--height", "64", "--save_image", str(tmp_path / "frame.png")])
+    assert out["train_observation"]["image"].shape == (4, T, 3, 64, 96) and out["action_label"]["action"].shape == (4, T, 2)
+    assert open(tmp_path / "frame.png", "rb").read(4) == b"\x89PNG"
 
 
 def test_dataset_matches_reference_loader(tmp_path, reference):
