@@ -82,3 +82,25 @@ def test_reference_language_table_tests_pass_on_this_implementation(rel, tmp_pat
         pytest.skip("the reference's test files are not on this machine")
     env = dict(os.environ, PYTHONPATH=os.pathsep.join([REPO, os.path.join(REPO, "tests", "shims")]), CUDA_VISIBLE_DEVICES="")
     _run(path, "language_table", env, tmp_path)
+
+
+def test_reference_environment_example_runs_on_this_implementation(tmp_path):
+    """The reference's ``examples/environment_example.py`` — build the BLOCK_8 block-to-block environment, reset, five random
+    actions from ``env.action_space``, save ``env.render()`` — executed unchanged against this package."""
+    path = _find("language_table/examples/environment_example.py")
+    if path is None:
+        pytest.skip("the reference's files are not on this machine")
+    try:
+        import absl.app  # noqa: F401
+    except ImportError:
+        pytest.skip("absl is not installed")
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([REPO, os.path.join(REPO, "tests", "shims")]), CUDA_VISIBLE_DEVICES="")
+    out = "/tmp/language_table_render.png"                                 # the path is fixed in the example
+    if os.path.exists(out):
+        os.remove(out)
+    code = ("import sys, runpy; import language_table as p; assert p.__file__.startswith(%r); sys.argv = ['example']; "
+            "runpy.run_path(%r, run_name='__main__')" % (REPO, path))
+    r = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    data = open(out, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n" and len(data) > 10_000       # the instruction band + the camera frame
