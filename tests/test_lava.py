@@ -100,6 +100,21 @@ def test_train_cli(tmp_path):
     cfg_path = os.path.join(os.path.dirname(train_main.__file__), "configs", "language_table_sim_local.py")
     cfg = train_main.load_config(cfg_path)
     assert cfg.model_name == "sequence_lav_mse" and cfg.sequence_length == 4 and cfg.per_device_batch_size == 4
+    # ml_collections-style overrides on the command line: --config.<path>=<literal>
+    train_main.apply_config_overrides(cfg, ["--config.agent.learning_rate=3e-4", "--config.model.lava_num_layers", "2",
+                                            "--config.data_skip_normalize_keys=['rgb']", "--config.model.lava_image_encoder=resnet"])
+    assert cfg.agent.learning_rate == 3e-4 and cfg.model.lava_num_layers == 2 and cfg.data_skip_normalize_keys == ["rgb"]
+    assert cfg.model.lava_image_encoder == "resnet"
+    for bad in (["--config.agent.learning_rat=1"], ["--config.nosuch.x=1"], ["--lr", "1"], ["--config.seed"]):
+        with pytest.raises(SystemExit):
+            train_main.apply_config_overrides(cfg, bad)
+    # the whole entry point, two steps of a shrunken model
+    rc = train_main.main(["--config", cfg_path, "--workdir", str(tmp_path / "cli"), "--synthetic_data", "--num_train_steps", "2",
+                          "--config.model.dense_resnet_width=64", "--config.model.lava_d_model=32", "--config.model.lava_num_layers=1",
+                          "--config.data_target_height=36", "--config.data_target_width=64", "--config.checkpoint_every_steps=2"])
+    assert rc == 0 and os.path.exists(tmp_path / "cli" / "checkpoints" / "ckpt_2.pt")
+    import json
+    assert json.load(open(tmp_path / "cli" / "hparams.json"))["model"]["lava_d_model"] == 32
 
 
 def test_clip_bpe_tokenizer():
