@@ -76,9 +76,9 @@ def main(argv=None):
     ap.add_argument("--num_evals_per_reward", type=int, default=50)
     ap.add_argument("--max_episode_steps", type=int, default=200)
     ap.add_argument("--device", default=None)
-    a = ap.parse_args(argv)
-    return evaluate_checkpoint(a.checkpoint_path, a.workdir, train_main.load_config(a.config), a.num_evals_per_reward,
-                               a.max_episode_steps, a.device)
+    a, extra = ap.parse_known_args(argv)
+    config = train_main.apply_config_overrides(train_main.load_config(a.config), extra)     # --config.<field>=<value>, as in training
+    return evaluate_checkpoint(a.checkpoint_path, a.workdir, config, a.num_evals_per_reward, a.max_episode_steps, a.device)
 
 
 if __name__ == "__main__":
