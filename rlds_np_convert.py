@@ -2,7 +2,8 @@
 
     python rlds_np_convert.py --out DIR --tfds_dir /data/language_table_blocktoblock_sim      # needs tensorflow_datasets
     python rlds_np_convert.py --out DIR --source EXPORT_DIR                                   # RLDS episodes exported as .npy
-    python rlds_np_convert.py --out DIR --synthetic                                           # synthetic Language-Table episodes
+    python rlds_np_convert.py --out DIR --oracle 200 --train 180 --val 10 --test 10            # scripted-oracle episodes from the simulator
+    python rlds_np_convert.py --out DIR --synthetic                                           # procedural stand-in frames (benchmarks, tests)
 
 Same output as the reference: the first 8 000 episodes split 7 800 / 100 / 100 into ``DIR/{train,val,test}/episode_<i>.npy``
 (pickled lists of flat step dicts) with the instruction replaced by a 512-d sentence embedding; ``--raw_out`` also writes the
@@ -65,6 +66,11 @@ def main(argv=None):
     p.add_argument("--tfds_dir", default=None, help="TFDS builder directory of a Language-Table RLDS dataset")
     p.add_argument("--source", default=None, help="directory of RLDS episodes exported as .npy (same nesting as RLDS)")
     p.add_argument("--synthetic", action="store_true")
+    p.add_argument("--oracle", type=int, default=0, metavar="N",
+                   help="collect N episodes of the scripted RRT* oracle in the simulator as the source (the offline stand-in for the "
+                        "published *_oracle_sim datasets; language_table/examples/collect_oracle_episodes.py)")
+    p.add_argument("--oracle_reward", default="block2block")
+    p.add_argument("--seed", type=int, default=0)
     p.add_argument("--encoder", choices=["hashed", "use"], default="hashed")
     p.add_argument("--use_path", default=None)
     p.add_argument("--train", type=int, default=7800)
@@ -76,7 +82,10 @@ def main(argv=None):
         write_synthetic_dataset(a.out, a.train, a.val, a.test)
         print(f"wrote synthetic dataset to {a.out}")
         return {"train": a.train, "val": a.val, "test": a.test}
-    if a.source:
+    if a.oracle:
+        from language_table.examples.collect_oracle_episodes import oracle_episodes
+        episodes = oracle_episodes(a.oracle, reward=a.oracle_reward, seed=a.seed, progress=25)
+    elif a.source:
         episodes = iter_exported_episodes(a.source)
     elif a.tfds_dir:
         try:
@@ -87,7 +96,7 @@ def main(argv=None):
         total = a.train + a.val + a.test
         episodes = tfds.builder_from_directory(builder_dir=a.tfds_dir).as_dataset(split=f"train[0:{total}]", shuffle_files=False)
     else:
-        raise SystemExit("give one of --tfds_dir, --source or --synthetic")
+        raise SystemExit("give one of --tfds_dir, --source, --oracle N or --synthetic")
     written = convert_rlds(episodes, a.out, _encoder(a.encoder, a.use_path), splits=splits, raw_root=a.raw_out)
     print(f"wrote {written} to {a.out}")
     return written

@@ -80,3 +80,33 @@ def test_cli_converts_an_exported_directory(tmp_path):
     assert written == {"train": 2, "val": 1, "test": 0}
     ep = E.load_episode(str(tmp_path / "out" / "val" / "episode_0.npy"))
     assert abs(float(np.linalg.norm(ep[0]["instruction"])) - 1.0) < 1e-4     # hashed stand-in embeddings are unit vectors
+
+
+def test_oracle_episodes_through_the_converter(tmp_path):
+    """``rlds_np_convert.py --oracle N``: scripted-oracle episodes from the simulator (the offline stand-in for the published
+    *_oracle_sim datasets) in RLDS nesting → the reference's per-episode .npy layout → the training dataset class."""
+    import rlds_np_convert
+    from language_table.examples.collect_oracle_episodes import oracle_episodes
+    from load_np_dataset import DecodeAndRandomResizedCrop, EmbodiedIntelligenceDataset
+    from rt1b200.data.episodes import load_episode
+    eps = list(oracle_episodes(2, seed=3, max_episode_steps=120))
+    again = list(oracle_episodes(1, seed=3, max_episode_steps=120))
+    assert len(eps) == 2 and len(eps[0]["steps"]) == len(again[0]["steps"])                      # seeded: reproducible
+    steps = eps[0]["steps"]
+    assert steps[0]["is_first"] and steps[-1]["is_last"] and steps[-1]["is_terminal"] and float(steps[-1]["reward"]) > 0
+    assert not any(s["is_last"] for s in steps[:-1]) and steps[0]["observation"]["rgb"].shape == (180, 320, 3)
+    assert all(np.abs(s["action"]).max() <= 0.03 + 1e-6 for s in steps) and np.abs(steps[0]["action"]).max() > 0
+    assert steps[0]["observation"]["instruction"].shape == (512,) and steps[0]["observation"]["instruction"].dtype == np.int32
+
+    written = rlds_np_convert.main(["--out", str(tmp_path / "ds"), "--raw_out", str(tmp_path / "raw"), "--oracle", "3", "--seed", "1",
+                                    "--train", "2", "--val", "1", "--test", "0"])
+    assert written == {"train": 2, "val": 1, "test": 0}
+    ep = load_episode(str(tmp_path / "ds" / "train" / "episode_0.npy"))
+    raw = load_episode(str(tmp_path / "raw" / "train" / "episode_0.npy"))
+    assert np.asarray(ep[0]["instruction"]).shape == (512,) and np.asarray(ep[0]["instruction"]).dtype == np.float32
+    assert np.asarray(raw[0]["instruction"]).dtype == np.int32 and len(ep) == len(raw)
+    text = bytes(int(v) for v in raw[0]["instruction"] if v).decode()
+    assert any(w in text for w in ("block", "moon", "star", "cube", "pentagon"))
+    ds = EmbodiedIntelligenceDataset(str(tmp_path / "ds" / "train"), [0, 1], 6, transform=DecodeAndRandomResizedCrop(0.95, (112, 64)))
+    sample = ds[len(ds) - 1]
+    assert sample["train_observation"]["image"].shape == (6, 3, 64, 112) and int(sample["action_label"]["terminate_episode"][-1]) == 1
