@@ -135,3 +135,30 @@ def test_rrt_planner_matches_the_reference_planner_on_the_same_problems(tmp_path
         assert b["waypoint_clearance"] > 0.03                               # disc radius 0.015 + clearance 0.015
     # not a pass criterion on a shared CPU, but worth seeing in the log: the array-based tree is the faster one
     print("planner seconds for 12 problems: reference %.2f, ours %.2f" % (sum(a["seconds"] for a in ref), sum(b["seconds"] for b in ours)))
+
+
+def test_camera_ray_helpers_equal_the_reference(tmp_path):
+    """Matrix layout conversion, pixel → view ray → world ray, ray / plane intersection and the rotation helpers of
+    ``utils_pybullet`` on fixed random cameras: the same numbers from both packages.  (``decompose_view_matrix`` of the
+    reference cannot be compared: it passes a 4x4 to ``Rotation.from_matrix``, which current scipy rejects; the position half
+    of its result is, and the quaternion returned here is checked to be a unit quaternion.)"""
+    import numpy as np
+    root = next((r for r in ROOTS if os.path.isdir(os.path.join(r, "language_table", "environments"))), None)
+    if root is None:
+        pytest.skip("the reference tree is not on this machine")
+    ref = _dump(root, str(tmp_path / "ref.json"), tmp_path, "_dump_ray_helpers.py")
+    ours = _dump(REPO, str(tmp_path / "ours.json"), tmp_path, "_dump_ray_helpers.py")
+    assert len(ref) == len(ours) == 9
+    compared = 0
+    for a, b in zip(ref, ours):
+        for k, v in a.items():
+            if v is None:
+                continue
+            if isinstance(v, list):
+                assert np.allclose(np.asarray(v, float), np.asarray(b[k], float), atol=1e-6), (k, v, b[k])
+            else:
+                assert v == b[k], (k, v, b[k])
+            compared += 1
+        if "quat" in b:
+            assert b["quat"] is not None and abs(np.linalg.norm(b["quat"]) - 1.0) < 1e-6
+    assert compared >= 45 and sum(a.get("hit") is not None for a in ref) >= 4
