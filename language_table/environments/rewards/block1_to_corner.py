@@ -2,8 +2,6 @@
 success within 0.08 m of a point 0.08 m inside the corner)."""
 import enum
 
-import numpy as np
-
 from language_table.environments import blocks as blocks_module
 from language_table.environments.rewards import block2absolutelocation as b2a, task_info
 
