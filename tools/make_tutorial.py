@@ -181,7 +181,8 @@ Training reads one `.npy` file per episode (`<root>/{train,val,test}/episode_<n>
 `rgb`, `instruction` (a 512-d sentence embedding), `action`, `is_first / is_last / is_terminal`, …) — the format
 `rlds_np_convert.py` writes from an RLDS / TFDS source.  TFDS and the GCS buckets of the upstream tutorial are not
 reachable offline; the converter takes any iterable of RLDS-shaped episodes, so the oracle episode above goes through the
-same code path:
+same code path.  (For a whole dataset: `python rlds_np_convert.py --out data --oracle 200 --train 180 --val 10 --test 10`
+collects successful oracle episodes with `language_table.examples.collect_oracle_episodes.oracle_episodes` and converts them.)
 """)
 
 code("""
