@@ -34,8 +34,19 @@ def get_ckpt_model(ckpt, device, dtype=None, height=256, width=456, seq_len=6):
     return module.eval()
 
 
+# the reward families of the reference's table (``main_rt1.py:105-116``: "blocktoblock" enabled, the next four commented out),
+# plus the single-block debugging task
+REWARDS = {"blocktoblock": ("block2block", "BlockToBlockReward"),
+           "blocktoabsolutelocation": ("block2absolutelocation", "BlockToAbsoluteLocationReward"),
+           "blocktoblockrelativelocation": ("block2block_relative_location", "BlockToBlockRelativeLocationReward"),
+           "blocktorelativelocation": ("block2relativelocation", "BlockToRelativeLocationReward"),
+           "separate": ("separate_blocks", "SeparateBlocksReward"),
+           "block1tocorner": ("block1_to_corner", "Block1ToCornerLocationReward")}
+
+
 def evaluate_checkpoint(workdir, ckpt=None, num_envs=1, episodes=10, max_episode_steps=80, device=None, seed=0,
-                        height=256, width=456, seq_len=6, use_oracle=False, video_format="png"):
+                        height=256, width=456, seq_len=6, use_oracle=False, video_format="png", rewards=("blocktoblock",),
+                        block_mode="BLOCK_8"):
     from rt1b200.utils.video import write_video
     device = device or ("cuda" if torch.cuda.is_available() else "cpu")
     dtype = torch.bfloat16 if device.startswith("cuda") else None
@@ -43,7 +54,14 @@ def evaluate_checkpoint(workdir, ckpt=None, num_envs=1, episodes=10, max_episode
     module.model._eval_center_crop = True          # deterministic evaluation (upstream's eval crop is random)
     os.makedirs(workdir, exist_ok=True)
     results = {}
-    if num_envs > 1 or device.startswith("cuda"):
+    rewards = tuple(rewards)
+    unknown = [r for r in rewards if r not in REWARDS]
+    if unknown:
+        raise ValueError(f"unknown reward families {unknown}; known: {sorted(REWARDS)}")
+    batched = num_envs > 1 or (device.startswith("cuda") and rewards == ("blocktoblock",) and block_mode == "BLOCK_8")
+    if batched and (rewards != ("blocktoblock",) or block_mode != "BLOCK_8"):
+        raise ValueError("the batched GPU boards implement the block-to-block task on BLOCK_8; use --num_envs 1 for other families")
+    if batched:
         from rt1b200.eval.closed_loop import run_closed_loop
         n_rounds = max(1, (episodes + num_envs - 1) // num_envs)
         res = run_closed_loop(module.model, num_envs=num_envs, episodes=n_rounds, max_episode_steps=max_episode_steps, device=device,
@@ -54,35 +72,39 @@ def evaluate_checkpoint(workdir, ckpt=None, num_envs=1, episodes=10, max_episode
         results["blocktoblock"] = res
     else:
         # reference-shaped single-environment loop through the wrapper stack and the policy adapter
+        import importlib
         from language_table.environments import blocks, language_table
         from language_table.environments.oracles import push_oracle_rrt_slowdown
-        from language_table.environments.rewards import block2block
         from language_table.eval import wrappers
         from language_table.train.policy import BCJaxPyPolicyRT1
-        env = language_table.LanguageTable(block_mode=blocks.LanguageTableBlockVariants.BLOCK_8,
-                                           reward_factory=block2block.BlockToBlockReward, seed=seed)
-        base = env
-        env = wrappers.HistoryWrapper(wrappers.CentralCropImageWrapper(wrappers.UseTokenWrapper(env), height, width, 0.95),
-                                      history_length=seq_len, tile_first_step_obs=True)
         policy = BCJaxPyPolicyRT1(module.model, device=device)
-        oracle = push_oracle_rrt_slowdown.ObstacleOrientedPushOracleBoard2dRRT(base, rng=np.random.RandomState(seed))
-        successes = 0
-        for ep in range(episodes):
-            policy.reset(1)
-            for _ in range(20):                       # re-sample the board until the oracle can plan it (upstream :162-172)
-                obs = env.reset()
-                oracle.reset()
-                if oracle.get_plan(base._compute_state()):
-                    break
-            frames = [base.render()]
-            for t in range(max_episode_steps):
-                obs, reward, done, _ = env.step(policy.action(obs))
-                frames.append(base.render())
-                if done:
-                    break
-            successes += int(base.succeeded)
-            write_video(os.path.join(workdir, f"blocktoblock_{ep}.{video_format}"), np.stack(frames), fps=10.0)
-        results["blocktoblock"] = {"episodes": episodes, "successes": successes, "success_rate": successes / max(1, episodes)}
+        for name in rewards:
+            mod, cls = REWARDS[name]
+            factory = getattr(importlib.import_module("language_table.environments.rewards." + mod), cls)
+            env = language_table.LanguageTable(block_mode=getattr(blocks.LanguageTableBlockVariants, block_mode),
+                                               reward_factory=factory, seed=seed)
+            base = env
+            env = wrappers.HistoryWrapper(wrappers.CentralCropImageWrapper(wrappers.UseTokenWrapper(env), height, width, 0.95),
+                                          history_length=seq_len, tile_first_step_obs=True)
+            oracle = push_oracle_rrt_slowdown.ObstacleOrientedPushOracleBoard2dRRT(base, rng=np.random.RandomState(seed))
+            successes = 0
+            for ep in range(episodes):
+                policy.reset(1)
+                for _ in range(20):                   # re-sample the board until the oracle can plan it (upstream :162-172)
+                    obs = env.reset()
+                    oracle.reset()
+                    if oracle.get_plan(base._compute_state(render=False)):
+                        break
+                frames = [base.render()]
+                for t in range(max_episode_steps):
+                    action = np.asarray(oracle.action(base._compute_state(render=False)), np.float32) if use_oracle else policy.action(obs)
+                    obs, reward, done, _ = env.step(action)
+                    frames.append(base.render())
+                    if done:
+                        break
+                successes += int(base.succeeded)
+                write_video(os.path.join(workdir, f"{name}_{ep}.{video_format}"), np.stack(frames), fps=10.0)
+            results[name] = {"episodes": episodes, "successes": successes, "success_rate": successes / max(1, episodes)}
     print(json.dumps(results))
     with open(os.path.join(workdir, "results.json"), "w") as f:
         json.dump(results, f, indent=1)
@@ -103,9 +125,12 @@ def main(argv=None):
     p.add_argument("--seq_len", type=int, default=6)
     p.add_argument("--oracle", action="store_true", help="drive the boards with the scripted oracle instead of the policy")
     p.add_argument("--video_format", choices=["png", "gif"], default="png", help="episode videos: animated PNG (lossless) or GIF")
+    p.add_argument("--rewards", default="blocktoblock",
+                   help="comma-separated task families (upstream's table: only blocktoblock enabled); known: " + ", ".join(sorted(REWARDS)))
+    p.add_argument("--block_mode", default="BLOCK_8", help="BLOCK_1 / BLOCK_4 / BLOCK_8 / N_CHOOSE_K (single-environment path)")
     a = p.parse_args(argv)
     return evaluate_checkpoint(a.workdir, a.ckpt, a.num_envs, a.episodes, a.max_episode_steps, a.device, a.seed, a.height, a.width,
-                               a.seq_len, a.oracle, a.video_format)
+                               a.seq_len, a.oracle, a.video_format, [r for r in a.rewards.split(",") if r], a.block_mode)
 
 
 if __name__ == "__main__":

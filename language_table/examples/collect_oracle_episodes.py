@@ -17,7 +17,8 @@ from typing import Dict, Iterator, Optional
 
 import numpy as np
 
-REWARDS = ("block2block", "block2absolutelocation", "block2relativelocation", "block2block_relative_location", "separate_blocks")
+REWARDS = ("block2block", "block2absolutelocation", "block2relativelocation", "block2block_relative_location", "separate_blocks",
+           "block1_to_corner")
 
 
 def _reward_factory(name: str):
@@ -25,7 +26,8 @@ def _reward_factory(name: str):
     mod = importlib.import_module("language_table.environments.rewards." + name)
     classes = {"block2block": "BlockToBlockReward", "block2absolutelocation": "BlockToAbsoluteLocationReward",
                "block2relativelocation": "BlockToRelativeLocationReward",
-               "block2block_relative_location": "BlockToBlockRelativeLocationReward", "separate_blocks": "SeparateBlocksReward"}
+               "block2block_relative_location": "BlockToBlockRelativeLocationReward", "separate_blocks": "SeparateBlocksReward",
+               "block1_to_corner": "Block1ToCornerLocationReward"}
     return getattr(mod, classes[name])
 
 

@@ -69,7 +69,8 @@ def main(argv=None):
     p.add_argument("--oracle", type=int, default=0, metavar="N",
                    help="collect N episodes of the scripted RRT* oracle in the simulator as the source (the offline stand-in for the "
                         "published *_oracle_sim datasets; language_table/examples/collect_oracle_episodes.py)")
-    p.add_argument("--oracle_reward", default="block2block")
+    p.add_argument("--oracle_reward", default="block2block", help="reward module name: block2block, block2absolutelocation, ..., block1_to_corner")
+    p.add_argument("--oracle_block_mode", default="BLOCK_8")
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--encoder", choices=["hashed", "use"], default="hashed")
     p.add_argument("--use_path", default=None)
@@ -84,7 +85,7 @@ def main(argv=None):
         return {"train": a.train, "val": a.val, "test": a.test}
     if a.oracle:
         from language_table.examples.collect_oracle_episodes import oracle_episodes
-        episodes = oracle_episodes(a.oracle, reward=a.oracle_reward, seed=a.seed, progress=25)
+        episodes = oracle_episodes(a.oracle, reward=a.oracle_reward, block_mode=a.oracle_block_mode, seed=a.seed, progress=25)
     elif a.source:
         episodes = iter_exported_episodes(a.source)
     elif a.tfds_dir:
