@@ -136,3 +136,22 @@ def test_fit_checkpoint_resume_and_reference_load(tmp_path, reference):
     ref.load_state_dict({k[len("model."):]: v for k, v in ck["state_dict"].items()}, strict=True)
     pol = load_policy_from_checkpoint(path)
     assert not pol.training and pol.cfg.num_layers == 1
+
+
+def test_open_loop_action_accuracy_tool(tmp_path):
+    """tools/eval_action_accuracy.py: a checkpoint of the full model against held-out episodes, with the mode / marginal baselines."""
+    import importlib.util
+    args = _args(tmp_path, height=64, width=96, seq_len=3)
+    tr = Trainer(RT1Module(args), args, device="cpu", loggers=[])
+    tr.epoch = 1
+    path = tr.save_checkpoint({"eval_loss": 0.5, "train_loss_epoch": 0.5})
+    root = write_synthetic_dataset(str(tmp_path / "ds"), 1, 1, 0, min_len=5, max_len=6, height=60, width=80)
+    spec = importlib.util.spec_from_file_location("eval_action_accuracy", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "eval_action_accuracy.py"))
+    tool = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(tool)
+    out = tool.main(["--ckpt", path, "--data_dir", os.path.join(root, "val"), "--height", "64", "--width", "96", "--seq_len", "3",
+                     "--batch_size", "2", "--max_batches", "2", "--device", "cpu"])
+    assert out["steps"] == 2 * 2 * 3 and 0.0 <= out["model"]["token_accuracy"] <= 1.0
+    # an untrained policy is near the uniform cross-entropy; the label marginal of a dozen steps is far below it
+    assert 3.0 < out["model"]["ce_per_token"] < 7.0 and out["marginal"]["ce_per_token"] < out["model"]["ce_per_token"]
+    assert out["mode"]["token_accuracy_within_2"] >= out["mode"]["token_accuracy"] > 0 and out["action_range_m"][0] < 0 < out["action_range_m"][1]
