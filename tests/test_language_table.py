@@ -1,4 +1,6 @@
 """Language-Table board, rewards, instruction grammar, oracles, wrappers and the closed-loop evaluator (CPU)."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -274,6 +276,14 @@ def test_wrappers_policy_and_entry_point(tmp_path):
     res = main_rt1.main(["--workdir", str(tmp_path), "--episodes", "1", "--max_episode_steps", "2", "--height", "64", "--width", "96",
                          "--seq_len", "2", "--device", "cpu"])
     assert res["blocktoblock"]["episodes"] == 1
+    # the other task families of the reference's table, driven by the oracle through the same loop; one video per episode
+    res = main_rt1.main(["--workdir", str(tmp_path / "fam"), "--episodes", "1", "--max_episode_steps", "80", "--height", "64", "--width", "96",
+                         "--seq_len", "2", "--device", "cpu", "--oracle", "--rewards", "block1tocorner,blocktoabsolutelocation",
+                         "--block_mode", "BLOCK_4", "--seed", "1"])
+    assert set(res) == {"block1tocorner", "blocktoabsolutelocation"} and res["block1tocorner"]["successes"] == 1
+    assert sorted(os.listdir(tmp_path / "fam")) == ["block1tocorner_0.png", "blocktoabsolutelocation_0.png", "results.json"]
+    with pytest.raises(ValueError):
+        main_rt1.main(["--workdir", str(tmp_path / "bad"), "--device", "cpu", "--rewards", "nosuchtask"])
 
 
 def test_batched_board_oracle_and_closed_loop_cpu():
