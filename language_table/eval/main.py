@@ -38,8 +38,13 @@ def evaluate_checkpoint(checkpoint_path, workdir, config, num_evals_per_reward=5
     results = collections.OrderedDict()
     for name, factory in REWARDS.items():
         base = language_table.LanguageTable(block_mode=blocks.LanguageTableBlockVariants.BLOCK_8, reward_factory=factory, seed=seed)
+        # language: the stored sentence embedding, or BPE ids for the in-graph CLIP tower (upstream's ClipTokenWrapper)
+        if config.model.get("lava_lang_encoder") == "clip":
+            worded = wrappers.ClipTokenWrapper(base, bpe_path=config.get("clip_bpe_path"))
+        else:
+            worded = wrappers.UseTokenWrapper(base)
         env = wrappers.HistoryWrapper(
-            wrappers.CentralCropImageWrapper(wrappers.UseTokenWrapper(base), config.data_target_height, config.data_target_width,
+            wrappers.CentralCropImageWrapper(worded, config.data_target_height, config.data_target_width,
                                              config.random_crop_factor),
             history_length=config.sequence_length, tile_first_step_obs=True)
         oracle = push_oracle_rrt_slowdown.ObstacleOrientedPushOracleBoard2dRRT(base, rng=np.random.RandomState(seed))

@@ -44,6 +44,30 @@ class UseTokenWrapper(_Wrapper):
         return obs
 
 
+class ClipTokenWrapper(_Wrapper):
+    """Adds ``instruction_tokenized_clip`` — int64 [77] CLIP BPE ids of the decoded instruction, framed by the start / end tokens —
+    what a LAVA model with ``lava_lang_encoder="clip"`` feeds its text tower.  Upstream Language-Table's evaluation script asks
+    for this wrapper (reference ``eval/main.py:85``); the fork's ``wrappers.py`` only carries ``UseTokenWrapper``.  ``tokenizer``: a
+    ``common.clip_tokenizer.ClipTokenizer``, or ``bpe_path`` to CLIP's merge file (not shipped)."""
+
+    def __init__(self, env, tokenizer=None, bpe_path=None, vocab_size: int = 49408, context_length: int = 77):
+        super().__init__(env)
+        from language_table.common import clip_tokenizer
+        if tokenizer is None:
+            if not bpe_path:
+                raise ValueError("ClipTokenWrapper needs a tokenizer or the path of CLIP's BPE merge file (bpe_simple_vocab_16e6.txt.gz)")
+            tokenizer = clip_tokenizer.ClipTokenizer(*clip_tokenizer.create_vocab(bpe_path=bpe_path))
+        self._tokenize = lambda text: clip_tokenizer.tokenize_text(text, tokenizer, vocab_size=vocab_size, context_length=context_length)[0]
+        self._current_tokens = None
+
+    def _process(self, obs, reset):
+        if reset or self._current_tokens is None:
+            self._current_tokens = self._tokenize(LanguageTable.decode_instruction(obs["instruction"]))
+        obs = collections.OrderedDict(obs)
+        obs["instruction_tokenized_clip"] = self._current_tokens
+        return obs
+
+
 def crop_test_image(images, random_crop_factor):
     """The centre crop that is the mean of the training-time random crop (reference ``wrappers.py:99-123``): a window of
     ``int(H * f) x int(W * f)`` at offset ``((H - H f) // 2, (W - W f) // 2)``.  ``images``: ``[H, W, C]`` or ``[N, H, W, C]``

@@ -56,9 +56,13 @@ class BCJaxPyPolicy:
         return cls(model.to(device) if device is not None else model, sd["norm_info"], device=device, **kw)
 
     def action(self, observation) -> np.ndarray:
-        """``observation``: history-stacked dict with ``rgb_sequence [T,H,W,3]`` in [0,1] and ``instruction_tokenized_use [T,512]``."""
-        obs = {"rgb": torch.from_numpy(np.ascontiguousarray(observation["rgb_sequence"]))[None].to(self.device, torch.float32),
-               "clip_embedding": torch.from_numpy(np.asarray(observation["instruction_tokenized_use"], np.float32))[None].to(self.device)}
+        """``observation``: history-stacked dict with ``rgb_sequence [T,H,W,3]`` in [0,1] and either ``instruction_tokenized_use
+        [T,512]`` (sentence embedding) or ``instruction_tokenized_clip [T,77]`` (BPE ids for a model with the in-graph CLIP tower)."""
+        obs = {"rgb": torch.from_numpy(np.ascontiguousarray(observation["rgb_sequence"]))[None].to(self.device, torch.float32)}
+        if "instruction_tokenized_clip" in observation:
+            obs["instruction_tokenized_clip"] = torch.from_numpy(np.asarray(observation["instruction_tokenized_clip"], np.int64))[None].to(self.device)
+        else:
+            obs["clip_embedding"] = torch.from_numpy(np.asarray(observation["instruction_tokenized_use"], np.float32))[None].to(self.device)
         with torch.no_grad():
             a = self.model(obs)[0].float().cpu().numpy()
         a = np.clip(a * self.std + self.mean, self.amin, self.amax)

@@ -397,3 +397,36 @@ def test_lava_clip_tokens_from_raw_episodes(tmp_path):
     before = tower.token_embedding.weight.clone()
     loss = agent.train({"observation": batch["observation"], "action": batch["action"]})["loss"]
     assert np.isfinite(loss) and torch.equal(tower.token_embedding.weight, before)    # the tower stays frozen
+
+
+def test_clip_token_wrapper_and_policy(tmp_path):
+    """ClipTokenWrapper (named by the reference's eval/main.py:85, absent from its wrappers.py): BPE ids of the environment's
+    instruction, history-stacked, consumed by the LAVA policy adapter of a model with the in-graph text tower."""
+    from language_table.environments import blocks, language_table
+    from language_table.environments.rewards import block2block
+    from language_table.eval import wrappers
+    from language_table.train.networks import lava
+    from language_table.train.networks.clip_text import ClipTextEncoder
+    from language_table.train.policy import BCJaxPyPolicy
+    merges = [("p", "u"), ("s", "h</w>"), ("pu", "sh</w>"), ("t", "h"), ("th", "e</w>")]
+    tok = clip_tokenizer.ClipTokenizer(*clip_tokenizer.create_vocab(merges=merges))
+    base = language_table.LanguageTable(blocks.LanguageTableBlockVariants.BLOCK_8, block2block.BlockToBlockReward, seed=0)
+    env = wrappers.HistoryWrapper(wrappers.CentralCropImageWrapper(wrappers.ClipTokenWrapper(base, tokenizer=tok), 36, 64, 0.95),
+                                  history_length=4, tile_first_step_obs=True)
+    obs = env.reset()
+    ids = obs["instruction_tokenized_clip"]
+    assert ids.shape == (4, 77) and ids.dtype == np.int64 and ids[0, 0] == 49406 and ids[0].max() == 49407
+    text = base.instruction_str
+    assert np.array_equal(ids[0], clip_tokenizer.tokenize_text(text, tok)[0]) and np.array_equal(ids[0], ids[3])
+    obs2, *_ = env.step(np.zeros(2, np.float32))
+    assert np.array_equal(obs2["instruction_tokenized_clip"][-1], ids[0])                  # cached until the next reset
+    with pytest.raises(ValueError, match="BPE merge file"):
+        wrappers.ClipTokenWrapper(base)
+    cfg = _small(language_table_sim_local.get_config())
+    cfg.model.lava_lang_encoder = "clip"
+    tower = ClipTextEncoder(features=32, num_heads=2, num_layers=1, out_features=512).freeze()
+    model = lava.SequenceLAVMSE(action_size=2, text_encoder=tower, **dict(cfg.model)).eval()
+    norm = {"action_statistics": {"mean": np.zeros(2, np.float32), "std": np.ones(2, np.float32)},
+            "action_min": -np.ones(2, np.float32) * 0.03, "action_max": np.ones(2, np.float32) * 0.03}
+    act = BCJaxPyPolicy(model, norm, device="cpu").action(obs)
+    assert act.shape == (2,) and np.all(np.abs(act) <= 0.03 + 1e-6)
