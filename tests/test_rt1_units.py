@@ -186,3 +186,28 @@ def test_zero_arena_learns_its_size():
     assert _ZeroArena("cpu", key=("unit", 2), numel=256).buf.numel() == 256              # another kind of pass: untouched
     b.take((10, 100))
     assert b.spilled == 0
+
+
+def test_header_library_and_bindings_agree():
+    """Every function ``include/rt1b200.h`` declares is exported by the built library and vice versa, and every ``call("rt1_…")``
+    in the Python bindings names an exported symbol (a header edit once dropped two declarations unnoticed)."""
+    import glob
+    import os
+    import re
+    import shutil
+    import subprocess
+
+    import pytest
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(repo, "rt1b200", "lib", "librt1b200.so")
+    if not os.path.exists(lib) or shutil.which("nm") is None:
+        pytest.skip("library not built here (python -c 'import __graft_entry__ as g; g.build()') or nm missing")
+    declared = set(re.findall(r"\b(rt1_[a-z0-9_]+)\s*\(", open(os.path.join(repo, "include", "rt1b200.h")).read()))
+    out = subprocess.run(["nm", "-D", "--defined-only", lib], capture_output=True, text=True, check=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if " T " in ln and ln.split()[-1].startswith("rt1_")}
+    assert declared == exported, (sorted(declared - exported), sorted(exported - declared))
+    called = set()
+    for f in glob.glob(os.path.join(repo, "rt1b200", "**", "*.py"), recursive=True) + glob.glob(os.path.join(repo, "tests", "*.py")) + \
+            glob.glob(os.path.join(repo, "tools", "*.py")):
+        called |= set(re.findall(r"""call\(\s*["'](rt1_[a-z0-9_]+)["']""", open(f).read()))
+    assert called and called <= exported, sorted(called - exported)
